@@ -1,0 +1,343 @@
+// crop.cu -- a3/a4/K9: box rounding + dilation + clamp, crop list construction,
+// fused crop + resize + normalise gather (patch-major bf16 for the ViT, or the reference's
+// fp32 CHW), and the per-image result records.
+//
+// Reference behaviour: README.md:86-124 + utils/trainClass.py:70-93 (dilation / crop),
+// app.py:39-42 (A.Resize(224,224,INTER_NEAREST) + A.Normalize(.5,.5)),
+// utils/trainClass.py:266 (HWC->CHW), YOLOTensorRT_yolodet_py_解读.md:93-116 (per-detection loop,
+// result tuples).
+#include "common.cuh"
+
+namespace {
+
+// floor division for a possibly negative numerator (python //), den > 0
+__device__ __forceinline__ int floordiv(int a, int d) {
+  int q = a / d, r = a % d;
+  return (r != 0 && ((r < 0) != (d < 0))) ? q - 1 : q;
+}
+
+__device__ __forceinline__ bool dilate_clamp(int x_min, int y_min, int x_max, int y_max, int W, int H,
+                                             int num, int den, int mode, int4 &o) {
+  int dx = floordiv((x_max - x_min) * num, den);
+  int dy = floordiv((y_max - y_min) * num, den);
+  if (mode == YV_DILATE_INFER_HALF) { dx = floordiv(dx, 2); dy = floordiv(dy, 2); }
+  o.z = min(W, x_max + dx);
+  o.x = max(0, x_min - dx);
+  o.w = min(H, y_max + dy);
+  o.y = max(0, y_min - dy);
+  return o.z > o.x && o.w > o.y;
+}
+
+__global__ void dilate_kernel(const int4 *__restrict__ in, int n, int W, int H, int num, int den, int mode,
+                              int4 *__restrict__ out, int32_t *__restrict__ valid) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  int4 b = in[i], o;
+  bool ok = dilate_clamp(b.x, b.y, b.z, b.w, W, H, num, den, mode, o);
+  out[i] = o;
+  valid[i] = ok ? 1 : 0;
+}
+
+// torch.round(x).to(int32): round half to even, then C-style truncating cast (values are integral)
+__device__ __forceinline__ int round_i32(float v) { return (int)rintf(v); }
+
+constexpr int BC_T = 1024;
+
+// One CTA.  Thread-per-image walk (<= max_det detections each), block scan of the per-image
+// valid counts, then the same walk writes the compacted crop list in (image, rank) order.
+__global__ void __launch_bounds__(BC_T)
+build_crops_kernel(const float4 *__restrict__ boxes, const float *__restrict__ scores,
+                   const int32_t *__restrict__ labels, const int32_t *__restrict__ anchors,
+                   const int32_t *__restrict__ keep, const int32_t *__restrict__ keep_counts, int B,
+                   int stride, int max_det, int W, int H, int num, int den, int mode,
+                   int4 *__restrict__ det_box, int4 *__restrict__ det_crop_box,
+                   float *__restrict__ det_score, int32_t *__restrict__ det_label,
+                   int32_t *__restrict__ det_anchor, int32_t *__restrict__ det_count,
+                   int32_t *__restrict__ det_crop, int4 *__restrict__ crop_box,
+                   int32_t *__restrict__ crop_img, int32_t *__restrict__ crop_det, int crop_cap,
+                   int32_t *__restrict__ n_crops) {
+  __shared__ int s_warp[BC_T / 32];
+  __shared__ int s_carry;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid == 0) s_carry = 0;
+  __syncthreads();
+  for (int b0 = 0; b0 < B; b0 += BC_T) {
+    const int b = b0 + tid;
+    int nk = 0, nvalid = 0;
+    if (b < B) {
+      nk = min(keep_counts[b], max_det);
+      det_count[b] = nk;
+      for (int k = 0; k < max_det; ++k) {
+        const size_t o = (size_t)b * max_det + k;
+        if (k < nk) {
+          const int id = keep[(size_t)b * stride + k];
+          const float4 f = boxes[(size_t)b * stride + id];
+          int4 q = make_int4(round_i32(f.x), round_i32(f.y), round_i32(f.z), round_i32(f.w));
+          int4 c;
+          const bool ok = dilate_clamp(q.x, q.y, q.z, q.w, W, H, num, den, mode, c);
+          det_box[o] = q;
+          det_crop_box[o] = c;
+          det_score[o] = scores[(size_t)b * stride + id];
+          det_label[o] = labels ? labels[(size_t)b * stride + id] : 0;
+          det_anchor[o] = anchors ? anchors[(size_t)b * stride + id] : id;
+          det_crop[o] = ok ? 0 : -1;   // provisional: rank filled in below
+          nvalid += ok ? 1 : 0;
+        } else {
+          det_box[o] = make_int4(0, 0, 0, 0);
+          det_crop_box[o] = make_int4(0, 0, 0, 0);
+          det_score[o] = 0.f;
+          det_label[o] = -1;
+          det_anchor[o] = -1;
+          det_crop[o] = -1;
+        }
+      }
+    }
+    // block exclusive scan of nvalid
+    int incl = nvalid;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      int t = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += t;
+    }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+      int v = s_warp[lane], inc2 = v;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        int t = __shfl_up_sync(0xffffffffu, inc2, d);
+        if (lane >= d) inc2 += t;
+      }
+      s_warp[lane] = inc2 - v;
+    }
+    __syncthreads();
+    int off = s_carry + s_warp[warp] + incl - nvalid;
+    if (b < B) {
+      for (int k = 0; k < nk; ++k) {
+        const size_t o = (size_t)b * max_det + k;
+        if (det_crop[o] == 0) {
+          if (off < crop_cap) {
+            crop_box[off] = det_crop_box[o];
+            crop_img[off] = b;
+            crop_det[off] = (int32_t)o;
+            det_crop[o] = off;
+          } else {
+            det_crop[o] = -1;
+          }
+          ++off;
+        }
+      }
+    }
+    __syncthreads();
+    if (tid == BC_T - 1) s_carry = off;   // the last thread's running offset = block total
+    __syncthreads();
+  }
+  if (tid == 0) n_crops[0] = s_carry;
+}
+
+// ----------------------------------------------------------------------------- crop gather
+struct AxisTap { int i0, i1; float f; };
+
+// bilinear, half-pixel centres, fp32, mirrors oracle.hotpath.crop_resize_norm.axis()
+__device__ __forceinline__ AxisTap bilinear_tap(int d, int n, int out) {
+  const float scale = __fdiv_rn((float)n, (float)out);
+  float s = __fsub_rn(__fmul_rn(__fadd_rn((float)d, 0.5f), scale), 0.5f);
+  s = fmaxf(s, 0.f);
+  const float fl = floorf(s);
+  AxisTap t;
+  t.f = __fsub_rn(s, fl);
+  int i0 = (int)fl;
+  i0 = min(i0, n - 1);
+  t.i0 = i0;
+  t.i1 = min(i0 + 1, n - 1);
+  return t;
+}
+// cv2 INTER_NEAREST: sx = min(floor(x * (1.0 / (dst / src))), src - 1), evaluated in fp64
+__device__ __forceinline__ int nearest_tap(int d, int n, int out) {
+  const double fx = (double)out / (double)n;
+  const double ifx = 1.0 / fx;
+  int s = (int)floor((double)d * ifx);
+  return min(s, n - 1);
+}
+
+__device__ __forceinline__ float normalise(float v) {
+  return __fmul_rn(__fsub_rn(v, 127.5f), (float)(1.0 / 127.5));
+}
+
+constexpr int CR_T = 256;
+constexpr int CR_PX = 8;     // output pixels per thread (one 16-byte bf16 store per channel)
+
+// One thread = 8 consecutive output x pixels of one output row, all 3 channels.
+// Thread order inside a crop is (patch, row-in-patch, 8-px segment) so that the 16-byte stores
+// of a warp are contiguous in the patch-major output (512 B per channel for patch 16).
+template <int INTERP, int LAYOUT>
+__global__ void __launch_bounds__(CR_T)
+crop_resize_kernel(const uint8_t *__restrict__ images, int H, int W, const int4 *__restrict__ crop_box,
+                   const int32_t *__restrict__ crop_img, int n, const int32_t *__restrict__ n_dev,
+                   int out, int patch, void *__restrict__ dst) {
+  const int crop = blockIdx.y;
+  if (crop >= n || (n_dev && crop >= *n_dev)) return;
+  const int segs_per_patch = patch * patch / CR_PX;
+  const int gp = out / patch;
+  const int work = gp * gp * segs_per_patch;
+  const int t = blockIdx.x * CR_T + threadIdx.x;
+  if (t >= work) return;
+  const int p = t / segs_per_patch, sp = t % segs_per_patch;
+  const int segs_per_row = patch / CR_PX;
+  const int iy = sp / segs_per_row, ix0 = (sp % segs_per_row) * CR_PX;
+  const int oy = (p / gp) * patch + iy, ox0 = (p % gp) * patch + ix0;
+
+  const int4 bx = crop_box[crop];
+  const int cw = bx.z - bx.x, ch = bx.w - bx.y;
+  const uint8_t *img = images + (size_t)crop_img[crop] * H * W * 3;
+  float v[3][CR_PX];
+
+  if (INTERP == YV_INTERP_NEAREST) {
+    const int sy = bx.y + nearest_tap(oy, ch, out);
+    const uint8_t *row = img + ((size_t)sy * W) * 3;
+#pragma unroll
+    for (int j = 0; j < CR_PX; ++j) {
+      const int sx = bx.x + nearest_tap(ox0 + j, cw, out);
+      const uint8_t *px = row + (size_t)sx * 3;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) v[c][j] = normalise((float)px[c]);
+    }
+  } else {
+    const AxisTap ty = bilinear_tap(oy, ch, out);
+    const uint8_t *r0 = img + ((size_t)(bx.y + ty.i0) * W) * 3;
+    const uint8_t *r1 = img + ((size_t)(bx.y + ty.i1) * W) * 3;
+#pragma unroll
+    for (int j = 0; j < CR_PX; ++j) {
+      const AxisTap tx = bilinear_tap(ox0 + j, cw, out);
+      const size_t xa = (size_t)(bx.x + tx.i0) * 3, xb = (size_t)(bx.x + tx.i1) * 3;
+#pragma unroll
+      for (int c = 0; c < 3; ++c) {
+        const float a00 = (float)r0[xa + c], a01 = (float)r0[xb + c];
+        const float a10 = (float)r1[xa + c], a11 = (float)r1[xb + c];
+        const float top = __fadd_rn(a00, __fmul_rn(tx.f, __fsub_rn(a01, a00)));
+        const float bot = __fadd_rn(a10, __fmul_rn(tx.f, __fsub_rn(a11, a10)));
+        v[c][j] = normalise(__fadd_rn(top, __fmul_rn(ty.f, __fsub_rn(bot, top))));
+      }
+    }
+  }
+
+  if (LAYOUT == YV_LAYOUT_PATCH_BF16) {
+    const int pp = patch * patch;
+    __nv_bfloat16 *o = (__nv_bfloat16 *)dst + ((size_t)crop * gp * gp + p) * (size_t)(3 * pp) + iy * patch + ix0;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      uint4 pk;
+      __nv_bfloat162 h0 = __floats2bfloat162_rn(v[c][0], v[c][1]);
+      __nv_bfloat162 h1 = __floats2bfloat162_rn(v[c][2], v[c][3]);
+      __nv_bfloat162 h2 = __floats2bfloat162_rn(v[c][4], v[c][5]);
+      __nv_bfloat162 h3 = __floats2bfloat162_rn(v[c][6], v[c][7]);
+      pk.x = *reinterpret_cast<unsigned *>(&h0);
+      pk.y = *reinterpret_cast<unsigned *>(&h1);
+      pk.z = *reinterpret_cast<unsigned *>(&h2);
+      pk.w = *reinterpret_cast<unsigned *>(&h3);
+      *reinterpret_cast<uint4 *>(o + (size_t)c * pp) = pk;
+    }
+  } else {
+    float *o = (float *)dst + (((size_t)crop * 3) * out + oy) * out + ox0;
+#pragma unroll
+    for (int c = 0; c < 3; ++c) {
+      float4 *q = reinterpret_cast<float4 *>(o + (size_t)c * out * out);
+      q[0] = make_float4(v[c][0], v[c][1], v[c][2], v[c][3]);
+      q[1] = make_float4(v[c][4], v[c][5], v[c][6], v[c][7]);
+    }
+  }
+}
+
+__global__ void pack_results_kernel(const int4 *__restrict__ det_box, const float *__restrict__ det_score,
+                                    const int32_t *__restrict__ det_anchor, const int32_t *__restrict__ det_count,
+                                    const int32_t *__restrict__ det_crop, const int32_t *__restrict__ top1, int B,
+                                    int max_det, float4 *__restrict__ rec) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= B * max_det) return;
+  const int b = i / max_det, k = i % max_det;
+  const bool have = k < det_count[b];
+  float4 r0 = make_float4(0.f, 0.f, 0.f, 0.f), r1 = make_float4(-1.f, 0.f, -1.f, 0.f);
+  if (have) {
+    const int4 q = det_box[i];
+    const int c = det_crop[i];
+    r0 = make_float4((float)q.x, (float)q.y, (float)q.z, (float)q.w);
+    r1 = make_float4((c >= 0 && top1) ? (float)top1[c] : -1.f, det_score[i], (float)det_anchor[i], 1.f);
+  }
+  rec[2 * (size_t)i] = r0;
+  rec[2 * (size_t)i + 1] = r1;
+}
+
+}  // namespace
+
+YV_EXPORT int yv_dilate_boxes(const int32_t *boxes_i32, int n, int W, int H, int num, int den, int mode,
+                              int32_t *out_boxes, int32_t *out_valid, yv_stream_t stream) {
+  YV_REQUIRE(n >= 0 && den > 0 && num >= 0 && W > 0 && H > 0, "yv_dilate_boxes: bad argument");
+  YV_REQUIRE(mode == YV_DILATE_FULL || mode == YV_DILATE_INFER_HALF, "yv_dilate_boxes: unknown mode %d", mode);
+  if (n == 0) return YV_OK;
+  YV_REQUIRE(boxes_i32 && out_boxes && out_valid, "yv_dilate_boxes: null pointer");
+  dilate_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>((const int4 *)boxes_i32, n, W, H, num, den, mode,
+                                                                   (int4 *)out_boxes, out_valid);
+  YV_LAUNCH_CHECK();
+  return YV_OK;
+}
+
+YV_EXPORT int yv_build_crops(const float *boxes, const float *scores, const int32_t *labels,
+                             const int32_t *anchors, const int32_t *keep, const int32_t *keep_counts, int B,
+                             int stride, int max_det, int W, int H, int num, int den, int mode,
+                             int32_t *det_box, int32_t *det_crop_box, float *det_score, int32_t *det_label,
+                             int32_t *det_anchor, int32_t *det_count, int32_t *det_crop, int32_t *crop_box,
+                             int32_t *crop_img, int32_t *crop_det, int crop_cap, int32_t *n_crops,
+                             yv_stream_t stream) {
+  YV_REQUIRE(B >= 1 && stride >= 1 && max_det >= 1 && crop_cap >= 1 && den > 0 && num >= 0 && W > 0 && H > 0,
+             "yv_build_crops: bad argument");
+  YV_REQUIRE(mode == YV_DILATE_FULL || mode == YV_DILATE_INFER_HALF, "yv_build_crops: unknown mode %d", mode);
+  YV_REQUIRE(boxes && scores && keep && keep_counts && det_box && det_crop_box && det_score && det_label &&
+                 det_anchor && det_count && det_crop && crop_box && crop_img && crop_det && n_crops,
+             "yv_build_crops: null pointer");
+  build_crops_kernel<<<1, BC_T, 0, (cudaStream_t)stream>>>(
+      (const float4 *)boxes, scores, labels, anchors, keep, keep_counts, B, stride, max_det, W, H, num, den, mode,
+      (int4 *)det_box, (int4 *)det_crop_box, det_score, det_label, det_anchor, det_count, det_crop, (int4 *)crop_box,
+      crop_img, crop_det, crop_cap, n_crops);
+  YV_LAUNCH_CHECK();
+  return YV_OK;
+}
+
+YV_EXPORT int yv_crop_resize(const uint8_t *images, int B, int H, int W, const int32_t *crop_box,
+                             const int32_t *crop_img, int n, const int32_t *n_dev, int interp, int out_size,
+                             int patch, int layout, void *out, yv_stream_t stream) {
+  YV_REQUIRE(B >= 1 && H >= 1 && W >= 1 && n >= 0, "yv_crop_resize: bad shape");
+  YV_REQUIRE(patch >= 8 && patch % 8 == 0 && out_size % patch == 0, "yv_crop_resize: need patch %% 8 == 0 and out %% patch == 0 (out=%d patch=%d)", out_size, patch);
+  YV_REQUIRE(interp == YV_INTERP_NEAREST || interp == YV_INTERP_BILINEAR, "yv_crop_resize: unknown interp %d", interp);
+  YV_REQUIRE(layout == YV_LAYOUT_PATCH_BF16 || layout == YV_LAYOUT_CHW_F32, "yv_crop_resize: unknown layout %d", layout);
+  if (n == 0) return YV_OK;
+  YV_REQUIRE(n <= 65535, "yv_crop_resize: n=%d exceeds 65535 crops per call", n);
+  YV_REQUIRE(images && crop_box && crop_img && out, "yv_crop_resize: null pointer");
+  YV_REQUIRE(((uintptr_t)out % 16) == 0, "yv_crop_resize: out must be 16-byte aligned");
+  const int work = out_size * out_size / CR_PX;
+  dim3 grid((work + CR_T - 1) / CR_T, n);
+  cudaStream_t s = (cudaStream_t)stream;
+  const int4 *cb = (const int4 *)crop_box;
+#define YV_CR(I, L) crop_resize_kernel<I, L><<<grid, CR_T, 0, s>>>(images, H, W, cb, crop_img, n, n_dev, out_size, patch, out)
+  if (interp == YV_INTERP_NEAREST) {
+    if (layout == YV_LAYOUT_PATCH_BF16) YV_CR(YV_INTERP_NEAREST, YV_LAYOUT_PATCH_BF16);
+    else YV_CR(YV_INTERP_NEAREST, YV_LAYOUT_CHW_F32);
+  } else {
+    if (layout == YV_LAYOUT_PATCH_BF16) YV_CR(YV_INTERP_BILINEAR, YV_LAYOUT_PATCH_BF16);
+    else YV_CR(YV_INTERP_BILINEAR, YV_LAYOUT_CHW_F32);
+  }
+#undef YV_CR
+  YV_LAUNCH_CHECK();
+  return YV_OK;
+}
+
+YV_EXPORT int yv_pack_results(const int32_t *det_box, const float *det_score, const int32_t *det_anchor,
+                              const int32_t *det_count, const int32_t *det_crop, const int32_t *top1, int B,
+                              int max_det, float *records, yv_stream_t stream) {
+  YV_REQUIRE(B >= 1 && max_det >= 1, "yv_pack_results: bad shape");
+  YV_REQUIRE(det_box && det_score && det_anchor && det_count && det_crop && records, "yv_pack_results: null pointer");
+  const int n = B * max_det;
+  pack_results_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+      (const int4 *)det_box, det_score, det_anchor, det_count, det_crop, top1, B, max_det, (float4 *)records);
+  YV_LAUNCH_CHECK();
+  return YV_OK;
+}

@@ -1,0 +1,248 @@
+// decode.cu -- K1: YOLOv8 head decode + confidence filter + order-preserving compaction.
+//
+// Replaces the per-anchor loop of the detector wrapper's post-processing
+// (docs/YOLO_TensorRT_Technical.md:243-267; YOLOTensorRT_yolodet_py_解读.md:89-94).
+//
+// Layout: head [B, 4+nc, A] fp32, channel-major.  A warp reads 32 x VEC consecutive
+// anchors of one channel row per load (LDG.128, streaming / no L1 allocate), so every
+// request is a fully coalesced 512 B run; each thread keeps UNROLL independent row loads
+// in flight.  A tile is NT*VEC anchors of one image.  Kept anchors are ranked inside the
+// tile with popc + warp shuffle scan (+ a 4-entry cross-warp scan) and staged tile-locally;
+// the LAST tile of an image to finish (threadfence + atomic ticket, no spinning) scans the
+// tile counts and moves the staged candidates to their final, ascending-anchor positions.
+// HBM-bound: algorithmic bytes = B*(4+nc)*A*4 read (+ 28 B per kept candidate).
+#include "common.cuh"
+
+namespace {
+
+constexpr int DEC_NT = 128;      // threads per tile
+constexpr int DEC_UNROLL = 8;    // class rows in flight per thread
+
+template <int VEC> struct RowVec;
+template <> struct RowVec<4> {
+  float v[4];
+  __device__ __forceinline__ void load(const float *p) {
+    float4 t = ld_stream_f4(p);
+    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+  }
+};
+template <> struct RowVec<1> {
+  float v[1];
+  __device__ __forceinline__ void load(const float *p) { v[0] = ld_stream_f1(p); }
+};
+
+struct DecodeStage {          // tile-local staging, SoA, capacity = tiles*TILE per image
+  float4 *box;
+  float *score;
+  int32_t *label;
+  int32_t *anchor;
+  int32_t *tile_count;        // [B*tiles]
+  unsigned *ticket;           // [B], zero before launch, reset by the last tile
+};
+
+template <int VEC>
+__global__ void __launch_bounds__(DEC_NT)
+decode_filter_kernel(const float *__restrict__ head, int nc, int A, float conf, int unletterbox,
+                     float ratio, float dw, float dh, int cap, DecodeStage st,
+                     float4 *__restrict__ out_box, float *__restrict__ out_score,
+                     int32_t *__restrict__ out_label, int32_t *__restrict__ out_anchor,
+                     int32_t *__restrict__ out_count) {
+  constexpr int TILE = DEC_NT * VEC;
+  const int tiles = gridDim.x;
+  const int tile = blockIdx.x, b = blockIdx.y;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int a0 = tile * TILE + tid * VEC;
+  const float *hp = head + (size_t)b * (size_t)(4 + nc) * (size_t)A;
+  // VEC == 4 requires A % 4 == 0, so a thread's 4 anchors are all in range or all out.
+  const bool in_range = a0 < A;
+
+  float best[VEC];
+  int lab[VEC];
+  RowVec<VEC> bx[4];
+#pragma unroll
+  for (int j = 0; j < VEC; ++j) { best[j] = 0.f; lab[j] = 0; }
+
+  if (in_range) {
+    const float *cp = hp + (size_t)4 * A + a0;
+    {  // class 0 initialises the running max (first max wins on ties: strict > below)
+      RowVec<VEC> r;
+      r.load(cp);
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) best[j] = r.v[j];
+    }
+    int c = 1;
+    for (; c + DEC_UNROLL <= nc; c += DEC_UNROLL) {
+      RowVec<VEC> r[DEC_UNROLL];
+#pragma unroll
+      for (int u = 0; u < DEC_UNROLL; ++u) r[u].load(cp + (size_t)(c + u) * A);
+#pragma unroll
+      for (int u = 0; u < DEC_UNROLL; ++u)
+#pragma unroll
+        for (int j = 0; j < VEC; ++j)
+          if (r[u].v[j] > best[j]) { best[j] = r[u].v[j]; lab[j] = c + u; }
+    }
+    for (; c < nc; ++c) {
+      RowVec<VEC> r;
+      r.load(cp + (size_t)c * A);
+#pragma unroll
+      for (int j = 0; j < VEC; ++j)
+        if (r.v[j] > best[j]) { best[j] = r.v[j]; lab[j] = c; }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) bx[k].load(hp + (size_t)k * A + a0);
+  }
+
+  // D4: keep iff not (score < conf)
+  unsigned flags = 0;
+  if (in_range) {
+#pragma unroll
+    for (int j = 0; j < VEC; ++j)
+      if (!(best[j] < conf)) flags |= 1u << j;
+  }
+  const int cnt = __popc(flags);
+
+  // tile-local exclusive rank: warp shuffle scan + cross-warp scan
+  int incl = cnt;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    int t = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += t;
+  }
+  __shared__ int s_wsum[DEC_NT / 32];
+  __shared__ int s_last;
+  if (lane == 31) s_wsum[warp] = incl;
+  __syncthreads();
+  int woff = 0, total = 0;
+#pragma unroll
+  for (int w = 0; w < DEC_NT / 32; ++w) {
+    int t = s_wsum[w];
+    if (w < warp) woff += t;
+    total += t;
+  }
+  int rank = woff + incl - cnt;
+
+  const size_t sbase = ((size_t)b * tiles + tile) * TILE;
+  if (flags) {
+#pragma unroll
+    for (int j = 0; j < VEC; ++j) {
+      if (flags & (1u << j)) {
+        float cx = bx[0].v[j], cy = bx[1].v[j], w = bx[2].v[j], h = bx[3].v[j];
+        float hw = __fmul_rn(0.5f, w), hh = __fmul_rn(0.5f, h);
+        float x0 = __fsub_rn(cx, hw), y0 = __fsub_rn(cy, hh);
+        float x1 = __fadd_rn(cx, hw), y1 = __fadd_rn(cy, hh);
+        if (unletterbox) {
+          x0 = __fdiv_rn(__fsub_rn(x0, dw), ratio);
+          x1 = __fdiv_rn(__fsub_rn(x1, dw), ratio);
+          y0 = __fdiv_rn(__fsub_rn(y0, dh), ratio);
+          y1 = __fdiv_rn(__fsub_rn(y1, dh), ratio);
+        }
+        st.box[sbase + rank] = make_float4(x0, y0, x1, y1);
+        st.score[sbase + rank] = best[j];
+        st.label[sbase + rank] = lab[j];
+        st.anchor[sbase + rank] = a0 + j;
+        ++rank;
+      }
+    }
+  }
+
+  // publish the tile, take a ticket; the last tile of the image gathers.
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) {
+    st.tile_count[b * tiles + tile] = total;
+    __threadfence();
+    unsigned prev = atomicAdd(&st.ticket[b], 1u);
+    s_last = (prev == (unsigned)(tiles - 1));
+  }
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+
+  // running offset over tiles (tiles is small: A/TILE); staged reads go through L2 (.cg)
+  int off = 0;
+  for (int t = 0; t < tiles; ++t) {
+    const int n = __ldcg(&st.tile_count[b * tiles + t]);
+    const size_t src = ((size_t)b * tiles + t) * TILE;
+    for (int i = tid; i < n; i += DEC_NT) {
+      const int dst = off + i;
+      if (dst < cap) {
+        const size_t o = (size_t)b * cap + dst;
+        out_box[o] = __ldcg(&st.box[src + i]);
+        out_score[o] = __ldcg(&st.score[src + i]);
+        out_label[o] = __ldcg(&st.label[src + i]);
+        out_anchor[o] = __ldcg(&st.anchor[src + i]);
+      }
+    }
+    off += n;
+  }
+  if (tid == 0) {
+    out_count[b] = off;
+    st.ticket[b] = 0u;   // ready for the next launch on this workspace
+  }
+}
+
+struct DecodeLayout {
+  int vec, tile, tiles;
+  size_t per_img;       // staged entries per image
+  size_t o_box, o_score, o_label, o_anchor, o_tcount, o_ticket, total;
+};
+
+DecodeLayout decode_layout(int B, int A) {
+  DecodeLayout L;
+  L.vec = (A % 4 == 0) ? 4 : 1;
+  L.tile = DEC_NT * L.vec;
+  L.tiles = (A + L.tile - 1) / L.tile;
+  L.per_img = (size_t)L.tiles * L.tile;
+  size_t n = (size_t)B * L.per_img, o = 0;
+  L.o_box = o;    o = yv_align_up(o + n * sizeof(float4), 256);
+  L.o_score = o;  o = yv_align_up(o + n * sizeof(float), 256);
+  L.o_label = o;  o = yv_align_up(o + n * sizeof(int32_t), 256);
+  L.o_anchor = o; o = yv_align_up(o + n * sizeof(int32_t), 256);
+  L.o_tcount = o; o = yv_align_up(o + (size_t)B * L.tiles * sizeof(int32_t), 256);
+  L.o_ticket = o; o = yv_align_up(o + (size_t)B * sizeof(unsigned), 256);
+  L.total = o;
+  return L;
+}
+
+}  // namespace
+
+YV_EXPORT size_t yv_decode_filter_workspace_bytes(int B, int nc, int A) {
+  (void)nc;
+  if (B <= 0 || A <= 0) return 0;
+  return decode_layout(B, A).total;
+}
+
+YV_EXPORT int yv_decode_filter(const float *head, int B, int nc, int A, float conf, int unletterbox,
+                               float ratio, float dw, float dh, int cap, float *boxes, float *scores,
+                               int32_t *labels, int32_t *anchors, int32_t *counts, void *ws,
+                               size_t ws_bytes, yv_stream_t stream) {
+  YV_REQUIRE(B >= 0 && nc >= 1 && A >= 1 && cap >= 1, "yv_decode_filter: bad shape B=%d nc=%d A=%d cap=%d", B, nc, A, cap);
+  if (B == 0) return YV_OK;
+  YV_REQUIRE(B <= 65535, "yv_decode_filter: B=%d exceeds 65535 (gridDim.y)", B);
+  YV_REQUIRE(head && boxes && scores && labels && anchors && counts && ws, "yv_decode_filter: null pointer");
+  YV_REQUIRE(((uintptr_t)head % 16) == 0 && ((uintptr_t)boxes % 16) == 0, "yv_decode_filter: head/boxes must be 16-byte aligned");
+  const DecodeLayout L = decode_layout(B, A);
+  if (ws_bytes < L.total) {
+    yv_set_error("yv_decode_filter: workspace %zu < required %zu", ws_bytes, L.total);
+    return YV_ENOMEM;
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  char *w = (char *)ws;
+  DecodeStage st;
+  st.box = (float4 *)(w + L.o_box);
+  st.score = (float *)(w + L.o_score);
+  st.label = (int32_t *)(w + L.o_label);
+  st.anchor = (int32_t *)(w + L.o_anchor);
+  st.tile_count = (int32_t *)(w + L.o_tcount);
+  st.ticket = (unsigned *)(w + L.o_ticket);
+  YV_CUDA(cudaMemsetAsync(st.ticket, 0, (size_t)B * sizeof(unsigned), s));
+  dim3 grid(L.tiles, B);
+  if (L.vec == 4)
+    decode_filter_kernel<4><<<grid, DEC_NT, 0, s>>>(head, nc, A, conf, unletterbox, ratio, dw, dh, cap, st,
+                                                    (float4 *)boxes, scores, labels, anchors, counts);
+  else
+    decode_filter_kernel<1><<<grid, DEC_NT, 0, s>>>(head, nc, A, conf, unletterbox, ratio, dw, dh, cap, st,
+                                                    (float4 *)boxes, scores, labels, anchors, counts);
+  YV_LAUNCH_CHECK();
+  return YV_OK;
+}
