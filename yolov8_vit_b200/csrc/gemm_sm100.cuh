@@ -1,0 +1,17 @@
+// gemm_sm100.cuh -- internal interface of the tcgen05 GEMM (gemm_sm100.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+
+struct GemmEpilogue {
+  void *out;                        // [rows, N] bf16 or f32 (row remapped when group_rows > 0)
+  const float *bias;                // [N] or null
+  const __nv_bfloat16 *residual;    // [rows, N] bf16 or null (indexed by the OUTPUT row; may alias out)
+  const float *pos;                 // patch-embed: [group_rows + 1, N] f32 position table (bias folded in)
+  int group_rows;                   // patch-embed: patches per crop (196); 0 = identity row map
+  bool gelu;
+  bool out_f32;
+};
+
+// D = A[M,K] * W[N,K]^T with the epilogue above.  K % 64 == 0, N % 8 == 0.
+int yv_gemm_launch(const void *A, const void *W, int M, int N, int K, const GemmEpilogue &ep, cudaStream_t s);
