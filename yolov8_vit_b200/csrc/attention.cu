@@ -1,0 +1,207 @@
+// attention.cu -- K7: softmax(Q K^T / sqrt(dh)) V for one (crop, head) per CTA.
+//
+// timm Attention.forward (vit_base_patch{16,8}_224; the arithmetic the reference reaches through
+// utils/utils.py:71-72): qkv [n, T, 3, heads, dh] -> per head softmax(q k^T * dh^-0.5) v.
+//
+// First tensor-core version: mma.sync.m16n8k16 (bf16 x bf16 -> f32) fed by ldmatrix from padded
+// shared memory; one warp owns 16 query rows, walks the keys in blocks of 64 with the online
+// softmax recurrence (running max / sum in registers, exp2 domain), P stays in registers as the
+// A operand of P.V.  Q, K, V of the head are staged once per CTA with 16-byte loads.
+// dh == 64, T <= 256 (ViT-B/16: T = 197 -> 13 warps, 4 key blocks).
+#include "common.cuh"
+#include "vit_ops.cuh"
+
+namespace {
+
+constexpr int ATT_DH = 64;
+constexpr int ATT_LD = 72;         // padded smem row (bf16 elements): 144 B, ldmatrix conflict-free
+constexpr int ATT_KB = 64;         // keys per block
+
+__device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], const void *p) {
+  const uint32_t a = (uint32_t)__cvta_generic_to_shared(p);
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(a));
+}
+__device__ __forceinline__ void ldsm_x4_t(uint32_t (&r)[4], const void *p) {
+  const uint32_t a = (uint32_t)__cvta_generic_to_shared(p);
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(a));
+}
+__device__ __forceinline__ void mma_bf16(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t *>(&h);
+}
+
+__global__ void __launch_bounds__(512, 1)
+attention_kernel(const __nv_bfloat16 *__restrict__ qkv, __nv_bfloat16 *__restrict__ out, int T, int heads,
+                 float scale_log2e) {
+  extern __shared__ __align__(16) uint8_t att_smem[];
+  const int nw = blockDim.x >> 5;                 // = ceil(T / 16)
+  const int nkb = (T + ATT_KB - 1) / ATT_KB;
+  const int qrows = nw * 16, krows = nkb * ATT_KB;
+  __nv_bfloat16 *Qs = reinterpret_cast<__nv_bfloat16 *>(att_smem);
+  __nv_bfloat16 *Ks = Qs + (size_t)qrows * ATT_LD;
+  __nv_bfloat16 *Vs = Ks + (size_t)krows * ATT_LD;
+
+  const int head = blockIdx.x, crop = blockIdx.y;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int D = heads * ATT_DH;
+  const __nv_bfloat16 *base = qkv + (size_t)crop * T * 3 * D + (size_t)head * ATT_DH;
+
+  // stage Q | K | V: 8 x 16-byte chunks per (row, matrix); padded rows are zero
+  const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
+  for (int i = tid; i < qrows * 8; i += blockDim.x) {
+    const int r = i >> 3, c = i & 7;
+    uint4 v = zero;
+    if (r < T) v = *reinterpret_cast<const uint4 *>(base + (size_t)r * 3 * D + c * 8);
+    *reinterpret_cast<uint4 *>(Qs + (size_t)r * ATT_LD + c * 8) = v;
+  }
+  for (int i = tid; i < krows * 8; i += blockDim.x) {
+    const int r = i >> 3, c = i & 7;
+    uint4 k = zero, v = zero;
+    if (r < T) {
+      k = *reinterpret_cast<const uint4 *>(base + (size_t)r * 3 * D + D + c * 8);
+      v = *reinterpret_cast<const uint4 *>(base + (size_t)r * 3 * D + 2 * D + c * 8);
+    }
+    *reinterpret_cast<uint4 *>(Ks + (size_t)r * ATT_LD + c * 8) = k;
+    *reinterpret_cast<uint4 *>(Vs + (size_t)r * ATT_LD + c * 8) = v;
+  }
+  __syncthreads();
+
+  // Q fragments of this warp's 16 rows: 4 k-steps of 16
+  uint32_t qf[4][4];
+  {
+    const int r = warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;
+    const int c = (lane >> 4) * 8;
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) ldsm_x4(qf[ks], Qs + (size_t)r * ATT_LD + ks * 16 + c);
+  }
+
+  float o[8][4];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f; }
+  float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+
+  for (int kb = 0; kb < nkb; ++kb) {
+    float s[8][4];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f; }
+    const __nv_bfloat16 *Kb = Ks + (size_t)kb * ATT_KB * ATT_LD;
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks) {
+#pragma unroll
+      for (int np = 0; np < 4; ++np) {          // n-tile pairs (2 x 8 keys)
+        uint32_t kf[4];
+        const int r = np * 16 + (lane & 7) + (lane >> 4) * 8;
+        const int c = ks * 16 + ((lane >> 3) & 1) * 8;
+        ldsm_x4(kf, Kb + (size_t)r * ATT_LD + c);
+        mma_bf16(s[2 * np], qf[ks], kf[0], kf[1]);
+        mma_bf16(s[2 * np + 1], qf[ks], kf[2], kf[3]);
+      }
+    }
+    // scale into the exp2 domain, mask keys >= T
+    const int key0 = kb * ATT_KB + (lane & 3) * 2;
+    float bm0 = -INFINITY, bm1 = -INFINITY;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int k = key0 + j * 8;
+      const bool v0 = k < T, v1 = (k + 1) < T;
+      s[j][0] = v0 ? s[j][0] * scale_log2e : -INFINITY;
+      s[j][1] = v1 ? s[j][1] * scale_log2e : -INFINITY;
+      s[j][2] = v0 ? s[j][2] * scale_log2e : -INFINITY;
+      s[j][3] = v1 ? s[j][3] * scale_log2e : -INFINITY;
+      bm0 = fmaxf(bm0, fmaxf(s[j][0], s[j][1]));
+      bm1 = fmaxf(bm1, fmaxf(s[j][2], s[j][3]));
+    }
+    bm0 = fmaxf(bm0, __shfl_xor_sync(0xffffffffu, bm0, 1));
+    bm0 = fmaxf(bm0, __shfl_xor_sync(0xffffffffu, bm0, 2));
+    bm1 = fmaxf(bm1, __shfl_xor_sync(0xffffffffu, bm1, 1));
+    bm1 = fmaxf(bm1, __shfl_xor_sync(0xffffffffu, bm1, 2));
+    const float mn0 = fmaxf(m0, bm0), mn1 = fmaxf(m1, bm1);
+    const float corr0 = exp2f(m0 - mn0), corr1 = exp2f(m1 - mn1);
+    m0 = mn0;
+    m1 = mn1;
+    float rs0 = 0.f, rs1 = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      s[j][0] = exp2f(s[j][0] - mn0);
+      s[j][1] = exp2f(s[j][1] - mn0);
+      s[j][2] = exp2f(s[j][2] - mn1);
+      s[j][3] = exp2f(s[j][3] - mn1);
+      rs0 += s[j][0] + s[j][1];
+      rs1 += s[j][2] + s[j][3];
+    }
+    l0 = l0 * corr0 + rs0;
+    l1 = l1 * corr1 + rs1;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      o[j][0] *= corr0; o[j][1] *= corr0;
+      o[j][2] *= corr1; o[j][3] *= corr1;
+    }
+    // O += P V
+    const __nv_bfloat16 *Vb = Vs + (size_t)kb * ATT_KB * ATT_LD;
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {               // k16 steps over the 64 keys of the block
+      uint32_t pf[4];
+      pf[0] = pack_bf16(s[2 * t][0], s[2 * t][1]);
+      pf[1] = pack_bf16(s[2 * t][2], s[2 * t][3]);
+      pf[2] = pack_bf16(s[2 * t + 1][0], s[2 * t + 1][1]);
+      pf[3] = pack_bf16(s[2 * t + 1][2], s[2 * t + 1][3]);
+#pragma unroll
+      for (int dp = 0; dp < 4; ++dp) {          // d n-tile pairs
+        uint32_t vf[4];
+        const int r = t * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;
+        const int c = dp * 16 + (lane >> 4) * 8;
+        ldsm_x4_t(vf, Vb + (size_t)r * ATT_LD + c);
+        mma_bf16(o[2 * dp], pf, vf[0], vf[1]);
+        mma_bf16(o[2 * dp + 1], pf, vf[2], vf[3]);
+      }
+    }
+  }
+
+  // finalise: row sums across the quad, normalise, store bf16
+  l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
+  l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+  l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
+  l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+  const float inv0 = 1.f / l0, inv1 = 1.f / l1;
+  const int r0 = warp * 16 + (lane >> 2), r1 = r0 + 8;
+  __nv_bfloat16 *ob = out + (size_t)crop * T * D + (size_t)head * ATT_DH + (lane & 3) * 2;
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    if (r0 < T) *reinterpret_cast<uint32_t *>(ob + (size_t)r0 * D + j * 8) = pack_bf16(o[j][0] * inv0, o[j][1] * inv0);
+    if (r1 < T) *reinterpret_cast<uint32_t *>(ob + (size_t)r1 * D + j * 8) = pack_bf16(o[j][2] * inv1, o[j][3] * inv1);
+  }
+}
+
+}  // namespace
+
+int yv_attention_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, int T, int heads, int dh,
+                        cudaStream_t s) {
+  YV_REQUIRE(dh == ATT_DH, "attention: head dim %d unsupported (need %d)", dh, ATT_DH);
+  YV_REQUIRE(n >= 1 && n <= 65535 && heads >= 1 && T >= 1, "attention: bad shape");
+  const int nw = (T + 15) / 16, nkb = (T + ATT_KB - 1) / ATT_KB;
+  YV_REQUIRE(nw <= 16, "attention: T=%d exceeds 256 tokens (needs the multi-block variant)", T);
+  const size_t smem = (size_t)(nw * 16 + 2 * nkb * ATT_KB) * ATT_LD * sizeof(__nv_bfloat16);
+  static bool attr_set = false;
+  if (!attr_set) {
+    YV_CUDA(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    attr_set = true;
+  }
+  dim3 grid(heads, n);
+  const float scale_log2e = (1.0f / sqrtf((float)dh)) * 1.4426950408889634f;
+  attention_kernel<<<grid, nw * 32, smem, s>>>(qkv, out, T, heads, scale_log2e);
+  YV_LAUNCH_CHECK();
+  return YV_OK;
+}
+
+YV_EXPORT int yv_attention_bf16(const void *qkv, void *out, int n, int T, int heads, int dh, yv_stream_t stream) {
+  YV_REQUIRE(qkv && out, "yv_attention_bf16: null pointer");
+  return yv_attention_launch((const __nv_bfloat16 *)qkv, (__nv_bfloat16 *)out, n, T, heads, dh, (cudaStream_t)stream);
+}

@@ -159,8 +159,17 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
             for (int j = 0; j < 32; ++j) if (j < ncols) v[j] += __ldg(pos_row + col0 + j);
           }
-          if (ep.residual) {
-            const uint4 *rp = reinterpret_cast<const uint4 *>(ep.residual + (size_t)drow * N + col0);
+          if (ep.residual && ep.res_f32) {
+            const float4 *rp = reinterpret_cast<const float4 *>((const float *)ep.residual + (size_t)drow * N + col0);
+#pragma unroll
+            for (int g = 0; g < 8; ++g) {
+              if (g * 4 < ncols) {
+                const float4 f = rp[g];
+                v[4 * g] += f.x; v[4 * g + 1] += f.y; v[4 * g + 2] += f.z; v[4 * g + 3] += f.w;
+              }
+            }
+          } else if (ep.residual) {
+            const uint4 *rp = reinterpret_cast<const uint4 *>((const __nv_bfloat16 *)ep.residual + (size_t)drow * N + col0);
 #pragma unroll
             for (int g = 0; g < 4; ++g) {
               if (g * 8 < ncols) {
@@ -284,7 +293,8 @@ YV_EXPORT int yv_gemm_bf16(const void *A, const void *W, const float *bias, cons
   GemmEpilogue ep;
   ep.out = D;
   ep.bias = bias;
-  ep.residual = (const __nv_bfloat16 *)residual;
+  ep.residual = residual;
+  ep.res_f32 = false;
   ep.pos = nullptr;
   ep.group_rows = 0;
   ep.gelu = (epi == YV_EPI_GELU);

@@ -6,11 +6,13 @@
 struct GemmEpilogue {
   void *out;                        // [rows, N] bf16 or f32 (row remapped when group_rows > 0)
   const float *bias;                // [N] or null
-  const __nv_bfloat16 *residual;    // [rows, N] bf16 or null (indexed by the OUTPUT row; may alias out)
+  const void *residual;             // [rows, N] bf16 (or f32 when res_f32) or null; indexed by the OUTPUT
+                                    // row; may alias out (each element is read then written by one thread)
   const float *pos;                 // patch-embed: [group_rows + 1, N] f32 position table (bias folded in)
   int group_rows;                   // patch-embed: patches per crop (196); 0 = identity row map
   bool gelu;
   bool out_f32;
+  bool res_f32;
 };
 
 // D = A[M,K] * W[N,K]^T with the epilogue above.  K % 64 == 0, N % 8 == 0.

@@ -1,0 +1,278 @@
+// vit.cu -- a5: ViT-B/{16,8} + Network_Wrapper head forward, composed from the tcgen05 GEMM
+// (gemm_sm100.cu) and the kernels in vit_ops.cu / attention.cu.
+//
+// Reference: utils/utils.py:59-87 (Network_Wrapper, build_model); the backbone arithmetic is
+// timm's vit_base_patch{16,8}_224 (third-party, unpinned, restated from its published
+// architecture: pre-norm blocks, LayerNorm eps 1e-6, erf-GELU, class token, learned position
+// embedding, final norm, class-token pooling, linear head).
+//
+// Data layout in HBM (per chunk of Cc crops, M = Cc * T token rows):
+//   x32  [M, dim]   f32   residual stream (kept fp32 so 24 residual adds do not accumulate bf16 rounding)
+//   y    [M, dim]   bf16  LayerNorm output / attention output (GEMM A operands)
+//   qkv  [M, 3 dim] bf16  timm packing (q | k | v, head-major)
+//   h    [M, mlp]   bf16  GELU(fc1)
+// Weights are packed once to bf16 [out, in] (K-major = the UMMA B operand as stored by torch).
+#include "common.cuh"
+#include "gemm_sm100.cuh"
+#include "vit_ops.cuh"
+
+#include <string>
+#include <unordered_map>
+#include <vector>
+
+namespace {
+
+struct Param {
+  size_t off;       // element offset into the bf16 or f32 arena
+  size_t numel;
+  bool bf16;
+  bool set;
+};
+
+__global__ void f32_to_bf16_kernel(const float *__restrict__ in, __nv_bfloat16 *__restrict__ out, size_t n) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t step = (size_t)gridDim.x * blockDim.x;
+  for (; i < n; i += step) out[i] = __float2bfloat16_rn(in[i]);
+}
+
+// pos_table[0] = cls + pos[0]; pos_table[t] = pos[t] + patch_bias  (t >= 1)
+__global__ void pos_table_kernel(const float *__restrict__ pos, const float *__restrict__ cls,
+                                 const float *__restrict__ pbias, float *__restrict__ table, int T, int dim) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= T * dim) return;
+  const int t = i / dim, e = i % dim;
+  table[i] = pos[i] + (t == 0 ? cls[e] : pbias[e]);
+}
+
+__global__ void gather_rows_f32_kernel(const float *__restrict__ in, size_t in_stride, float *__restrict__ out,
+                                       int rows, int dim) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= rows * dim) return;
+  out[i] = in[(size_t)(i / dim) * in_stride + (i % dim)];
+}
+
+}  // namespace
+
+struct yv_vit {
+  yv_vit_config cfg;
+  int T;                      // tokens per crop
+  int pdim;                   // 3 * patch * patch
+  std::unordered_map<std::string, Param> params;
+  __nv_bfloat16 *wb = nullptr;   // bf16 arena
+  float *wf = nullptr;           // f32 arena
+  size_t nb = 0, nf = 0;
+  size_t pos_table_off = 0;      // f32 arena: [T, dim]
+  bool finalized = false;
+
+  const __nv_bfloat16 *B(const std::string &k) const { return wb + params.at(k).off; }
+  const float *F(const std::string &k) const { return wf + params.at(k).off; }
+};
+
+namespace {
+
+void add_param(yv_vit *m, const std::string &name, size_t numel, bool bf16) {
+  Param p;
+  p.numel = numel;
+  p.bf16 = bf16;
+  p.set = false;
+  if (bf16) { p.off = m->nb; m->nb += (numel + 63) / 64 * 64; }      // 128-byte aligned rows for TMA
+  else { p.off = m->nf; m->nf += (numel + 63) / 64 * 64; }
+  m->params[name] = p;
+}
+
+struct VitWs {
+  float *x32;
+  __nv_bfloat16 *y, *qkv, *h, *cls_ln;
+  float *hidden;
+  size_t total;
+};
+
+VitWs vit_ws(const yv_vit *m, void *base, int chunk) {
+  const yv_vit_config &c = m->cfg;
+  const size_t M = (size_t)chunk * m->T;
+  size_t o = 0;
+  char *b = (char *)base;
+  VitWs w;
+  w.x32 = (float *)(b + o);            o = yv_align_up(o + M * c.dim * 4, 1024);
+  w.y = (__nv_bfloat16 *)(b + o);      o = yv_align_up(o + M * c.dim * 2, 1024);
+  w.qkv = (__nv_bfloat16 *)(b + o);    o = yv_align_up(o + M * 3 * c.dim * 2, 1024);
+  w.h = (__nv_bfloat16 *)(b + o);      o = yv_align_up(o + M * c.mlp * 2, 1024);
+  w.cls_ln = (__nv_bfloat16 *)(b + o); o = yv_align_up(o + (size_t)chunk * c.dim * 2, 1024);
+  w.hidden = (float *)(b + o);         o = yv_align_up(o + (size_t)chunk * c.head_out * 4, 1024);
+  w.total = o;
+  return w;
+}
+
+constexpr int VIT_DEFAULT_CHUNK = 256;
+
+int finalize(yv_vit *m, cudaStream_t s) {
+  if (m->finalized) return YV_OK;
+  const int miss = yv_vit_missing_params(m);
+  if (miss) {
+    yv_set_error("yv_vit_forward: %d parameters were never set", miss);
+    return YV_EINVAL;
+  }
+  const int n = m->T * m->cfg.dim;
+  pos_table_kernel<<<(n + 255) / 256, 256, 0, s>>>(m->F("model.pos_embed"), m->F("model.cls_token"),
+                                                   m->F("model.patch_embed.proj.bias"), m->wf + m->pos_table_off,
+                                                   m->T, m->cfg.dim);
+  YV_LAUNCH_CHECK();
+  m->finalized = true;
+  return YV_OK;
+}
+
+}  // namespace
+
+YV_EXPORT int yv_vit_create(const yv_vit_config *cfg, yv_vit_t **out) {
+  YV_REQUIRE(cfg && out, "yv_vit_create: null pointer");
+  const yv_vit_config &c = *cfg;
+  YV_REQUIRE(c.img > 0 && c.patch >= 8 && c.patch % 8 == 0 && c.img % c.patch == 0, "yv_vit_create: bad img/patch %d/%d", c.img, c.patch);
+  YV_REQUIRE(c.dim % 256 == 0 && c.dim <= 1024 && c.heads > 0 && c.dim == c.heads * 64, "yv_vit_create: dim=%d heads=%d (need dim %% 256 == 0, head dim 64)", c.dim, c.heads);
+  YV_REQUIRE(c.mlp % 64 == 0 && c.head_out % 8 == 0 && c.hidden >= 1 && c.num_classes >= 1 && c.depth >= 1, "yv_vit_create: bad mlp/head sizes");
+  YV_REQUIRE((3 * c.patch * c.patch) % 64 == 0, "yv_vit_create: 3*patch^2 must be a multiple of 64");
+  yv_vit *m = new yv_vit();
+  m->cfg = c;
+  const int g = c.img / c.patch;
+  m->T = g * g + 1;
+  m->pdim = 3 * c.patch * c.patch;
+  const size_t D = c.dim;
+  add_param(m, "model.cls_token", D, false);
+  add_param(m, "model.pos_embed", (size_t)m->T * D, false);
+  add_param(m, "model.patch_embed.proj.weight", D * m->pdim, true);
+  add_param(m, "model.patch_embed.proj.bias", D, false);
+  for (int i = 0; i < c.depth; ++i) {
+    const std::string p = "model.blocks." + std::to_string(i) + ".";
+    add_param(m, p + "norm1.weight", D, false);
+    add_param(m, p + "norm1.bias", D, false);
+    add_param(m, p + "attn.qkv.weight", 3 * D * D, true);
+    add_param(m, p + "attn.qkv.bias", 3 * D, false);
+    add_param(m, p + "attn.proj.weight", D * D, true);
+    add_param(m, p + "attn.proj.bias", D, false);
+    add_param(m, p + "norm2.weight", D, false);
+    add_param(m, p + "norm2.bias", D, false);
+    add_param(m, p + "mlp.fc1.weight", (size_t)c.mlp * D, true);
+    add_param(m, p + "mlp.fc1.bias", c.mlp, false);
+    add_param(m, p + "mlp.fc2.weight", D * c.mlp, true);
+    add_param(m, p + "mlp.fc2.bias", D, false);
+  }
+  add_param(m, "model.norm.weight", D, false);
+  add_param(m, "model.norm.bias", D, false);
+  add_param(m, "model.head.weight", (size_t)c.head_out * D, true);
+  add_param(m, "model.head.bias", c.head_out, false);
+  add_param(m, "fc.1.weight", (size_t)c.hidden * c.head_out, false);
+  add_param(m, "fc.1.bias", c.hidden, false);
+  add_param(m, "fc.3.weight", (size_t)c.num_classes * c.hidden, false);
+  add_param(m, "fc.3.bias", c.num_classes, false);
+  m->pos_table_off = m->nf;
+  m->nf += ((size_t)m->T * D + 63) / 64 * 64;
+  cudaError_t e = cudaMalloc(&m->wb, m->nb * sizeof(__nv_bfloat16));
+  if (e == cudaSuccess) e = cudaMalloc(&m->wf, m->nf * sizeof(float));
+  if (e != cudaSuccess) {
+    if (m->wb) cudaFree(m->wb);
+    delete m;
+    yv_cuda_fail(e, "cudaMalloc(ViT weights)", __FILE__, __LINE__);
+    return YV_ENOMEM;
+  }
+  *out = m;
+  return YV_OK;
+}
+
+YV_EXPORT void yv_vit_destroy(yv_vit_t *m) {
+  if (!m) return;
+  cudaFree(m->wb);
+  cudaFree(m->wf);
+  delete m;
+}
+
+YV_EXPORT int yv_vit_set_param(yv_vit_t *m, const char *name, const float *data, size_t numel, yv_stream_t stream) {
+  YV_REQUIRE(m && name && data, "yv_vit_set_param: null pointer");
+  auto it = m->params.find(name);
+  YV_REQUIRE(it != m->params.end(), "yv_vit_set_param: unknown parameter '%s'", name);
+  Param &p = it->second;
+  YV_REQUIRE(p.numel == numel, "yv_vit_set_param: '%s' has %zu elements, expected %zu", name, numel, p.numel);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (p.bf16) {
+    const int grid = (int)((numel + 255) / 256 < 4096 ? (numel + 255) / 256 : 4096);
+    f32_to_bf16_kernel<<<grid, 256, 0, s>>>(data, m->wb + p.off, numel);
+    YV_LAUNCH_CHECK();
+  } else {
+    YV_CUDA(cudaMemcpyAsync(m->wf + p.off, data, numel * sizeof(float), cudaMemcpyDeviceToDevice, s));
+  }
+  YV_CUDA(cudaStreamSynchronize(s));
+  p.set = true;
+  m->finalized = false;
+  return YV_OK;
+}
+
+YV_EXPORT int yv_vit_missing_params(const yv_vit_t *m) {
+  if (!m) return -1;
+  int miss = 0;
+  for (const auto &kv : m->params) miss += kv.second.set ? 0 : 1;
+  return miss;
+}
+
+YV_EXPORT size_t yv_vit_workspace_bytes(const yv_vit_t *m, int max_crops) {
+  if (!m || max_crops <= 0) return 0;
+  const int chunk = max_crops < VIT_DEFAULT_CHUNK ? max_crops : VIT_DEFAULT_CHUNK;
+  return vit_ws(m, nullptr, chunk).total;
+}
+
+YV_EXPORT int yv_vit_forward(yv_vit_t *m, const void *patches_bf16, int n, float *logits, int32_t *top1,
+                             float *hidden, void *ws, size_t ws_bytes, yv_stream_t stream) {
+  YV_REQUIRE(m && n >= 0, "yv_vit_forward: bad argument");
+  if (n == 0) return YV_OK;
+  YV_REQUIRE(patches_bf16 && logits && top1 && ws, "yv_vit_forward: null pointer");
+  cudaStream_t s = (cudaStream_t)stream;
+  int rc = finalize(m, s);
+  if (rc) return rc;
+  const yv_vit_config &c = m->cfg;
+  // largest chunk the workspace allows
+  int chunk = n < VIT_DEFAULT_CHUNK ? n : VIT_DEFAULT_CHUNK;
+  while (chunk > 1 && vit_ws(m, nullptr, chunk).total > ws_bytes) chunk = (chunk + 1) / 2;
+  if (vit_ws(m, nullptr, chunk).total > ws_bytes) {
+    yv_set_error("yv_vit_forward: workspace %zu too small (one crop needs %zu)", ws_bytes, vit_ws(m, nullptr, 1).total);
+    return YV_ENOMEM;
+  }
+  const VitWs w = vit_ws(m, ws, chunk);
+  const int T = m->T, D = c.dim, NP = T - 1;
+  const float *pos_table = m->wf + m->pos_table_off;
+
+  for (int c0 = 0; c0 < n; c0 += chunk) {
+    const int cc = (n - c0) < chunk ? (n - c0) : chunk;
+    const int M = cc * T;
+    const __nv_bfloat16 *patches = (const __nv_bfloat16 *)patches_bf16 + (size_t)c0 * NP * m->pdim;
+    GemmEpilogue ep;
+    // patch embedding: [cc*NP, pdim] x [D, pdim]^T -> token rows (+ position, + bias), f32 residual stream
+    ep = GemmEpilogue{w.x32, nullptr, nullptr, pos_table, NP, false, true, false};
+    if ((rc = yv_gemm_launch(patches, m->B("model.patch_embed.proj.weight"), cc * NP, D, m->pdim, ep, s))) return rc;
+    if ((rc = yv_cls_rows_launch(w.x32, pos_table, cc, T, D, s))) return rc;
+    for (int i = 0; i < c.depth; ++i) {
+      const std::string p = "model.blocks." + std::to_string(i) + ".";
+      if ((rc = yv_ln_launch(w.x32, true, D, m->F(p + "norm1.weight"), m->F(p + "norm1.bias"), w.y, M, D, c.eps, s))) return rc;
+      ep = GemmEpilogue{w.qkv, m->F(p + "attn.qkv.bias"), nullptr, nullptr, 0, false, false, false};
+      if ((rc = yv_gemm_launch(w.y, m->B(p + "attn.qkv.weight"), M, 3 * D, D, ep, s))) return rc;
+      if ((rc = yv_attention_launch(w.qkv, w.y, cc, T, c.heads, D / c.heads, s))) return rc;
+      ep = GemmEpilogue{w.x32, m->F(p + "attn.proj.bias"), w.x32, nullptr, 0, false, true, true};
+      if ((rc = yv_gemm_launch(w.y, m->B(p + "attn.proj.weight"), M, D, D, ep, s))) return rc;
+      if ((rc = yv_ln_launch(w.x32, true, D, m->F(p + "norm2.weight"), m->F(p + "norm2.bias"), w.y, M, D, c.eps, s))) return rc;
+      ep = GemmEpilogue{w.h, m->F(p + "mlp.fc1.bias"), nullptr, nullptr, 0, true, false, false};
+      if ((rc = yv_gemm_launch(w.y, m->B(p + "mlp.fc1.weight"), M, c.mlp, D, ep, s))) return rc;
+      ep = GemmEpilogue{w.x32, m->F(p + "mlp.fc2.bias"), w.x32, nullptr, 0, false, true, true};
+      if ((rc = yv_gemm_launch(w.h, m->B(p + "mlp.fc2.weight"), M, D, c.mlp, ep, s))) return rc;
+    }
+    // final norm on the class-token rows only, 1000-way head, wrapper MLP + argmax
+    if ((rc = yv_ln_launch(w.x32, true, (size_t)T * D, m->F("model.norm.weight"), m->F("model.norm.bias"), w.cls_ln, cc, D, c.eps, s))) return rc;
+    ep = GemmEpilogue{w.hidden, m->F("model.head.bias"), nullptr, nullptr, 0, false, true, false};
+    if ((rc = yv_gemm_launch(w.cls_ln, m->B("model.head.weight"), cc, c.head_out, D, ep, s))) return rc;
+    if ((rc = yv_wrapper_head_launch(w.hidden, c.head_out, m->F("fc.1.weight"), m->F("fc.1.bias"), m->F("fc.3.weight"),
+                                     m->F("fc.3.bias"), cc, c.head_out, c.hidden, c.num_classes,
+                                     logits + (size_t)c0 * c.num_classes, top1 + c0, s)))
+      return rc;
+    if (hidden) {
+      const int tot = cc * c.head_out;
+      gather_rows_f32_kernel<<<(tot + 255) / 256, 256, 0, s>>>(w.hidden, c.head_out, hidden + (size_t)c0 * c.head_out, cc, c.head_out);
+      YV_LAUNCH_CHECK();
+    }
+  }
+  return YV_OK;
+}

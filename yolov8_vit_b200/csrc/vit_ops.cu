@@ -1,0 +1,174 @@
+// vit_ops.cu -- the non-GEMM kernels of the ViT forward (architecture = timm
+// vit_base_patch{16,8}_224 as wrapped by utils/utils.py:59-72):
+//   K6  LayerNorm (fp32 statistics, one warp per token row, 16-byte vector I/O)
+//   K7  softmax attention per (crop, head) on tensor cores (mma.sync m16n8k16 bf16 -> f32,
+//       ldmatrix-fed, online softmax in registers)
+//   K8  class-token rows, and the Network_Wrapper head (ReLU -> 1000x128 -> ReLU -> 128x5) + argmax
+#include "common.cuh"
+#include "vit_ops.cuh"
+
+namespace {
+
+// ------------------------------------------------------------------------------------ LayerNorm
+constexpr int LN_WARPS = 8;
+constexpr int LN_MAXCH = 4;    // dim <= 1024 (chunks of 256 = 32 lanes x 8 elements)
+
+template <bool XF32>
+__global__ void __launch_bounds__(LN_WARPS * 32)
+layernorm_kernel(const void *__restrict__ xv, size_t in_stride, const float *__restrict__ gamma,
+                 const float *__restrict__ beta, __nv_bfloat16 *__restrict__ y, int rows, int dim, float eps) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * LN_WARPS + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int nch = dim >> 8;
+  float v[LN_MAXCH][8];
+#pragma unroll
+  for (int c = 0; c < LN_MAXCH; ++c) {
+    if (c < nch) {
+      const int e = c * 256 + lane * 8;
+      if (XF32) {
+        const float4 *p = reinterpret_cast<const float4 *>((const float *)xv + (size_t)row * in_stride + e);
+        const float4 a = p[0], b = p[1];
+        v[c][0] = a.x; v[c][1] = a.y; v[c][2] = a.z; v[c][3] = a.w;
+        v[c][4] = b.x; v[c][5] = b.y; v[c][6] = b.z; v[c][7] = b.w;
+      } else {
+        const uint4 u = *reinterpret_cast<const uint4 *>((const __nv_bfloat16 *)xv + (size_t)row * in_stride + e);
+        const __nv_bfloat162 *h = reinterpret_cast<const __nv_bfloat162 *>(&u);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const float2 f = __bfloat1622float2(h[k]);
+          v[c][2 * k] = f.x;
+          v[c][2 * k + 1] = f.y;
+        }
+      }
+    }
+  }
+  float sum = 0.f;
+#pragma unroll
+  for (int c = 0; c < LN_MAXCH; ++c)
+    if (c < nch)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) sum += v[c][k];
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, d);
+  const float mean = sum / (float)dim;
+  float sq = 0.f;
+#pragma unroll
+  for (int c = 0; c < LN_MAXCH; ++c)
+    if (c < nch)
+#pragma unroll
+      for (int k = 0; k < 8; ++k) { const float d = v[c][k] - mean; sq += d * d; }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, d);
+  const float rstd = rsqrtf(sq / (float)dim + eps);
+#pragma unroll
+  for (int c = 0; c < LN_MAXCH; ++c) {
+    if (c < nch) {
+      const int e = c * 256 + lane * 8;
+      const float4 g0 = *reinterpret_cast<const float4 *>(gamma + e), g1 = *reinterpret_cast<const float4 *>(gamma + e + 4);
+      const float4 b0 = *reinterpret_cast<const float4 *>(beta + e), b1 = *reinterpret_cast<const float4 *>(beta + e + 4);
+      const float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+      const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+      uint4 u;
+      __nv_bfloat162 h[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k)
+        h[k] = __floats2bfloat162_rn((v[c][2 * k] - mean) * rstd * g[2 * k] + bb[2 * k],
+                                     (v[c][2 * k + 1] - mean) * rstd * g[2 * k + 1] + bb[2 * k + 1]);
+      u.x = *reinterpret_cast<unsigned *>(&h[0]);
+      u.y = *reinterpret_cast<unsigned *>(&h[1]);
+      u.z = *reinterpret_cast<unsigned *>(&h[2]);
+      u.w = *reinterpret_cast<unsigned *>(&h[3]);
+      *reinterpret_cast<uint4 *>(y + (size_t)row * dim + e) = u;
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------ cls rows
+__global__ void cls_rows_kernel(float *__restrict__ x32, const float *__restrict__ cls_pos0, int n, int T, int dim) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n * dim) return;
+  const int c = i / dim, e = i % dim;
+  x32[(size_t)c * T * dim + e] = cls_pos0[e];
+}
+
+// ------------------------------------------------------------------------------------ wrapper head
+// One CTA per crop: relu(h) [head_out] -> hid (<= 256) -> ncls (<= 32); fp32 throughout.
+constexpr int WH_T = 256;
+__global__ void __launch_bounds__(WH_T)
+wrapper_head_kernel(const float *__restrict__ hidden, int ld, const float *__restrict__ w1,
+                    const float *__restrict__ b1, const float *__restrict__ w3, const float *__restrict__ b3,
+                    int head_out, int hid, int ncls, float *__restrict__ logits, int32_t *__restrict__ top1) {
+  extern __shared__ float sh[];
+  float *s_in = sh;                 // [head_out]
+  float *s_mid = sh + head_out;     // [hid]
+  float *s_out = s_mid + hid;       // [ncls]
+  const int c = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int i = tid; i < head_out; i += WH_T) s_in[i] = fmaxf(hidden[(size_t)c * ld + i], 0.f);
+  __syncthreads();
+  for (int j = warp; j < hid; j += WH_T / 32) {
+    const float *w = w1 + (size_t)j * head_out;
+    float acc = 0.f;
+    for (int i = lane; i < head_out; i += 32) acc += w[i] * s_in[i];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+    if (lane == 0) s_mid[j] = fmaxf(acc + b1[j], 0.f);
+  }
+  __syncthreads();
+  for (int j = warp; j < ncls; j += WH_T / 32) {
+    const float *w = w3 + (size_t)j * hid;
+    float acc = 0.f;
+    for (int i = lane; i < hid; i += 32) acc += w[i] * s_mid[i];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+    if (lane == 0) {
+      acc += b3[j];
+      s_out[j] = acc;
+      logits[(size_t)c * ncls + j] = acc;
+    }
+  }
+  __syncthreads();
+  if (tid == 0) {
+    int best = 0;
+    for (int j = 1; j < ncls; ++j)
+      if (s_out[j] > s_out[best]) best = j;
+    top1[c] = best;
+  }
+}
+
+}  // namespace
+
+int yv_ln_launch(const void *x, bool x_f32, size_t in_stride, const float *gamma, const float *beta,
+                 __nv_bfloat16 *y, int rows, int dim, float eps, cudaStream_t s) {
+  YV_REQUIRE(rows >= 1 && dim >= 256 && dim % 256 == 0 && dim <= 256 * LN_MAXCH, "layernorm: dim=%d must be a multiple of 256, <= %d", dim, 256 * LN_MAXCH);
+  YV_REQUIRE(x && gamma && beta && y, "layernorm: null pointer");
+  YV_REQUIRE(in_stride % 8 == 0, "layernorm: row stride must be a multiple of 8 elements");
+  const int grid = (rows + LN_WARPS - 1) / LN_WARPS;
+  if (x_f32) layernorm_kernel<true><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, gamma, beta, y, rows, dim, eps);
+  else layernorm_kernel<false><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, gamma, beta, y, rows, dim, eps);
+  YV_LAUNCH_CHECK();
+  return YV_OK;
+}
+
+int yv_cls_rows_launch(float *x32, const float *cls_pos0, int n, int T, int dim, cudaStream_t s) {
+  const int total = n * dim;
+  cls_rows_kernel<<<(total + 255) / 256, 256, 0, s>>>(x32, cls_pos0, n, T, dim);
+  YV_LAUNCH_CHECK();
+  return YV_OK;
+}
+
+int yv_wrapper_head_launch(const float *hidden, int ld_hidden, const float *w1, const float *b1, const float *w3,
+                           const float *b3, int n, int head_out, int hid, int ncls, float *logits, int32_t *top1,
+                           cudaStream_t s) {
+  YV_REQUIRE(n >= 1 && head_out >= 1 && hid >= 1 && ncls >= 1, "wrapper head: bad shape");
+  const size_t smem = (size_t)(head_out + hid + ncls) * sizeof(float);
+  YV_REQUIRE(smem <= 48 * 1024, "wrapper head: %zu bytes of shared memory exceed 48 KB", smem);
+  wrapper_head_kernel<<<n, WH_T, smem, s>>>(hidden, ld_hidden, w1, b1, w3, b3, head_out, hid, ncls, logits, top1);
+  YV_LAUNCH_CHECK();
+  return YV_OK;
+}
+
+YV_EXPORT int yv_layernorm_bf16(const void *x, const float *gamma, const float *beta, void *y, int rows, int dim,
+                                float eps, yv_stream_t stream) {
+  return yv_ln_launch(x, false, (size_t)dim, gamma, beta, (__nv_bfloat16 *)y, rows, dim, eps, (cudaStream_t)stream);
+}

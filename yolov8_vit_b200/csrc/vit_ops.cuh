@@ -1,0 +1,23 @@
+// vit_ops.cuh -- internal interface of the non-GEMM ViT kernels (vit_ops.cu).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+
+// y[r, :] = LayerNorm(x[r * in_stride : +dim]) * gamma + beta; fp32 statistics, bf16 output.
+// x is f32 (x_f32 = true, the residual stream) or bf16.  dim % 256 == 0, dim <= 1024.
+int yv_ln_launch(const void *x, bool x_f32, size_t in_stride, const float *gamma, const float *beta,
+                 __nv_bfloat16 *y, int rows, int dim, float eps, cudaStream_t s);
+
+// softmax(Q K^T / sqrt(dh)) V; qkv [n*T, 3*heads*dh] bf16 (timm packing: q | k | v, head-major),
+// out [n*T, heads*dh] bf16.  dh == 64, T <= 256.
+int yv_attention_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, int T, int heads, int dh,
+                        cudaStream_t s);
+
+// x32[c*T, :] = cls + pos[0]  (the class-token row of every crop)
+int yv_cls_rows_launch(float *x32, const float *cls_pos0, int n, int T, int dim, cudaStream_t s);
+
+// Network_Wrapper.fc on the backbone output: logits = W3 relu(W1 relu(h) + b1) + b3; top1 = first argmax
+int yv_wrapper_head_launch(const float *hidden, int ld_hidden, const float *w1, const float *b1, const float *w3,
+                           const float *b3, int n, int head_out, int hid, int ncls, float *logits, int32_t *top1,
+                           cudaStream_t s);
