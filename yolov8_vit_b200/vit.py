@@ -1,0 +1,123 @@
+"""ViT-B/{16,8} + Network_Wrapper head on the C-ABI (yv_vit_*).
+
+Mirrors utils/utils.py:59-87 of the reference: ``Network_Wrapper(model,
+num_class)`` whose ``forward(x)`` returns ``fc(model(x))`` logits, and
+``build_model(CFG, modelName, pretrained_path=...)``.  The arithmetic runs in
+libyv8vit.so (tcgen05 GEMMs, bf16 operands, fp32 accumulate).
+"""
+from __future__ import annotations
+
+import ctypes
+import re
+from dataclasses import dataclass
+
+import torch
+
+from . import ops
+from ._lib import VitConfigC, check, load, ptr, require_device, stream_ptr
+
+
+@dataclass(frozen=True)
+class ViTConfig:
+    """timm ``vit_base_patch{16,8}_224`` shape + the wrapper head (utils/utils.py:64-69)."""
+    img: int = 224
+    patch: int = 16
+    dim: int = 768
+    depth: int = 12
+    heads: int = 12
+    mlp: int = 3072
+    head_out: int = 1000
+    hidden: int = 128
+    num_classes: int = 5
+    eps: float = 1e-6
+
+    @property
+    def tokens(self) -> int:
+        return (self.img // self.patch) ** 2 + 1
+
+    @staticmethod
+    def from_name(model_name: str, num_classes: int = 5) -> "ViTConfig":
+        """Parses timm names like ``vit_base_patch8_224.augreg_in21k`` (utils/class_config.py:21)."""
+        m = re.match(r"vit_base_patch(\d+)_(\d+)", model_name)
+        if not m:
+            raise ValueError(f"unsupported modelName {model_name!r}: only vit_base_patch{{8,16}}_224 variants")
+        return ViTConfig(img=int(m.group(2)), patch=int(m.group(1)), num_classes=num_classes)
+
+
+class ViTModel:
+    """Device-resident packed weights + forward.  Not an nn.Module: inference only."""
+
+    def __init__(self, cfg: ViTConfig = ViTConfig(), device="cuda:0"):
+        self.cfg = cfg
+        self.device = torch.device(device)
+        require_device(torch.empty(1, device=self.device))
+        c = VitConfigC(cfg.img, cfg.patch, cfg.dim, cfg.depth, cfg.heads, cfg.mlp, cfg.head_out, cfg.hidden,
+                       cfg.num_classes, cfg.eps)
+        h = ctypes.c_void_p()
+        with torch.cuda.device(self.device):
+            check(load().yv_vit_create(ctypes.byref(c), ctypes.byref(h)), "yv_vit_create")
+        self._h = h
+        self._ws = None
+        self._ws_crops = 0
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h:
+            try:
+                load().yv_vit_destroy(h)
+            except Exception:
+                pass
+            self._h = None
+
+    def load_state_dict(self, sd: dict, strict: bool = True):
+        """``sd``: Network_Wrapper.state_dict() layout (``model.*`` timm names + ``fc.1.*``/``fc.3.*``)."""
+        lib = load()
+        with torch.cuda.device(self.device):
+            for k, v in sd.items():
+                t = v.detach().to(device=self.device, dtype=torch.float32).contiguous()
+                rc = lib.yv_vit_set_param(self._h, k.encode(), ptr(t), t.numel(), stream_ptr(self.device))
+                if rc != 0 and strict:
+                    check(rc, f"yv_vit_set_param({k})")
+        missing = lib.yv_vit_missing_params(self._h)
+        if strict and missing:
+            raise KeyError(f"{missing} ViT parameters missing from the state dict")
+        return self
+
+    def _workspace(self, n: int) -> torch.Tensor:
+        if self._ws is None or self._ws_crops < min(n, 256):
+            nb = load().yv_vit_workspace_bytes(self._h, n)
+            self._ws = torch.empty(nb, dtype=torch.uint8, device=self.device)
+            self._ws_crops = min(n, 256)
+        return self._ws
+
+    def forward_patches(self, patches: torch.Tensor, n: int, return_hidden: bool = False):
+        """patches: layout-0 output of ops.crop_resize for n crops -> (logits [n,C] f32, top1 [n] i32)."""
+        cfg = self.cfg
+        logits = torch.empty(n, cfg.num_classes, dtype=torch.float32, device=self.device)
+        top1 = torch.empty(n, dtype=torch.int32, device=self.device)
+        hidden = torch.empty(n, cfg.head_out, dtype=torch.float32, device=self.device) if return_hidden else None
+        if n == 0:
+            return (logits, top1, hidden) if return_hidden else (logits, top1)
+        assert patches.dtype == torch.bfloat16 and patches.is_contiguous()
+        ws = self._workspace(n)
+        with torch.cuda.device(self.device):
+            check(load().yv_vit_forward(self._h, ptr(patches), n, ptr(logits), ptr(top1), ptr(hidden), ptr(ws),
+                                        ws.numel(), stream_ptr(self.device)), "yv_vit_forward")
+        return (logits, top1, hidden) if return_hidden else (logits, top1)
+
+    def forward(self, x: torch.Tensor) -> torch.Tensor:
+        """x: f32 [n,3,img,img] normalised crops (the reference's transform output) -> logits [n,C]."""
+        require_device(x)
+        p = patchify_bf16(x.to(self.device, torch.float32), self.cfg.patch)
+        return self.forward_patches(p, x.shape[0])[0]
+
+    __call__ = forward
+
+
+def patchify_bf16(x: torch.Tensor, patch: int) -> torch.Tensor:
+    """[n,3,S,S] f32 -> patch-major bf16 [n*(S/p)^2, 3*p*p] (layout glue for callers that bring
+    their own CHW tensors; the pipeline's crop kernel writes this layout directly)."""
+    n, ch, S, _ = x.shape
+    g = S // patch
+    x = x.reshape(n, ch, g, patch, g, patch).permute(0, 2, 4, 1, 3, 5)
+    return x.reshape(n * g * g, ch * patch * patch).to(torch.bfloat16).contiguous()
