@@ -190,6 +190,16 @@ int yv_pack_results(const int32_t *det_box, const float *det_score,
                     const int32_t *det_crop, const int32_t *top1, int B,
                     int max_det, float *records, yv_stream_t stream);
 
+/* --- measurement hooks (bench.py) -------------------------------------------
+ * The library counts every kernel launch per kernel class.  With profiling on,
+ * each launch is additionally bracketed by CUDA events on its own stream, so
+ * bench.py can report per-kernel device time, launches and algorithmic work
+ * (bytes for the HBM-bound kernels, flops for the GEMM) for the roofline.     */
+int yv_prof_enable(int on);                 /* resets the counters              */
+int yv_prof_kinds(void);
+const char *yv_prof_kind_name(int kind);
+int yv_prof_read(double *ms, long long *launches, double *work); /* syncs      */
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,156 @@
+"""GPU parity tests (through the C-ABI) for decode / NMS / dilation / crop against the CPU oracle:
+bit-exact for every integer, index and pre-bf16 fp32 result."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import hotpath as O          # checker only
+from oracle import nms_c
+from yolov8_vit_b200 import ops, synth
+from yolov8_vit_b200.utils import utils as U
+
+DEV = "cuda:0"
+
+
+def _decode_check(head, conf=0.35, **kw):
+    bx, sc, lb, an, cnt = ops.decode_filter(head.to(DEV), conf, **kw)
+    cnt = cnt.cpu()
+    for b in range(head.shape[0]):
+        rb, rs, rl, ra = O.decode_head(head[b], conf, **kw)
+        k = int(cnt[b])
+        assert k == rb.shape[0], (b, k, rb.shape[0])
+        assert torch.equal(bx[b, :k].cpu(), rb) and torch.equal(sc[b, :k].cpu(), rs)
+        assert torch.equal(lb[b, :k].cpu(), rl) and torch.equal(an[b, :k].cpu(), ra)
+
+
+def test_decode_golden(golden):
+    g = golden("decode")
+    head = torch.from_numpy(g["head"])
+    bx, sc, lb, an, cnt = ops.decode_filter(head.to(DEV), 0.35)
+    bu, *_ = ops.decode_filter(head.to(DEV), 0.35, ratio=0.8, dwdh=(12.0, 4.0))
+    for b in range(3):
+        k = int(cnt[b])
+        assert k == len(g[f"plain{b}__anchors"])
+        assert np.array_equal(bx[b, :k].cpu().numpy(), g[f"plain{b}__boxes"])
+        assert np.array_equal(sc[b, :k].cpu().numpy(), g[f"plain{b}__scores"])
+        assert np.array_equal(lb[b, :k].cpu().numpy(), g[f"plain{b}__labels"])
+        assert np.array_equal(an[b, :k].cpu().numpy(), g[f"plain{b}__anchors"])
+        assert np.array_equal(bu[b, :k].cpu().numpy(), g[f"unl{b}__boxes"])
+
+
+def test_decode_cfg2_and_ragged():
+    _decode_check(synth.make_head(8, 80, 8400, seed=synth.SEED0 + 2))
+    _decode_check(synth.make_head(2, 5, 8400, n_obj=3, seed=9))            # nc=5 (the real detector)
+    _decode_check(synth.make_head(2, 7, 1001, n_obj=3, n_jit=5, seed=10))  # A % 4 != 0: scalar path
+    _decode_check(synth.make_head(1, 80, 33600, n_obj=4, img=1280, seed=11))
+    h = synth.make_head(2, 80, 8400, seed=12)
+    _decode_check(h, conf=2.0)     # nothing passes
+    _decode_check(h, conf=0.0)     # everything passes (count == A)
+
+
+def test_decode_workspace_reuse_is_idempotent():
+    h = synth.make_head(4, 80, 8400, seed=13).to(DEV)
+    a = ops.decode_filter(h)
+    b = ops.decode_filter(h)
+    assert all(torch.equal(x, y) for x, y in zip((a[4], a[3]), (b[4], b[3])))
+
+
+def test_nms_golden(golden):
+    g = golden("nms")
+    for name in g["names"]:
+        b, s, thr = g[f"{name}__boxes"], g[f"{name}__scores"], float(g[f"{name}__thr"])
+        keep = U.custom_nms(torch.from_numpy(b), torch.from_numpy(s), thr)
+        assert keep == g[f"{name}__keep"].tolist(), name
+
+
+def test_nms_cfg2_batched_bit_exact():
+    head = synth.make_head(64, 80, 8400, seed=synth.SEED0 + 2)
+    bx, sc, lb, an, cnt = ops.decode_filter(head.to(DEV))
+    keep, kc = ops.nms_batched(bx, sc, cnt, 0.45)
+    keep, kc, cnt_c, bxc, scc = keep.cpu(), kc.cpu(), cnt.cpu(), bx.cpu(), sc.cpu()
+    for b in range(64):
+        n = int(cnt_c[b])
+        ref = nms_c.nms(bxc[b, :n].numpy(), scc[b, :n].numpy(), 0.45)
+        assert keep[b, :int(kc[b])].tolist() == ref, b
+    for b in (0, 17):      # and the verbatim torch snippet on two images
+        n = int(cnt_c[b])
+        assert keep[b, :int(kc[b])].tolist() == O.custom_nms(bxc[b, :n], scc[b, :n], 0.45)
+    # max_keep truncates in score order
+    k10, c10 = ops.nms_batched(bx, sc, cnt, 0.45, max_keep=10)
+    for b in range(64):
+        assert k10[b, :int(c10[b])].tolist() == keep[b, :min(10, int(kc[b]))].tolist()
+
+
+@pytest.mark.parametrize("thr", [0.3, 0.5, 0.7])
+def test_nms_cfg5_stress_bit_exact(thr):
+    """cfg5 at full size per image (30k dense-overlap boxes), 4 images, against the C oracle."""
+    boxes, scores = synth.make_nms_stress(4, 30000, seed=synth.SEED0 + 5)
+    keep, kc = ops.nms_batched(boxes.to(DEV), scores.to(DEV), None, thr)
+    keep, kc = keep.cpu(), kc.cpu()
+    for b in range(4):
+        ref = nms_c.nms(boxes[b].numpy(), scores[b].numpy(), thr)
+        assert keep[b, :int(kc[b])].tolist() == ref, b
+
+
+def test_nms_properties_full_size():
+    """Size-independent properties at cfg5's full batch: idempotence (NMS of the keeps keeps all),
+    keeps are pairwise below the threshold, scores descend."""
+    from torchvision.ops import box_iou
+    boxes, scores = synth.make_nms_stress(32, 30000, seed=synth.SEED0 + 5)
+    bd, sd = boxes.to(DEV), scores.to(DEV)
+    keep, kc = ops.nms_batched(bd, sd, None, 0.5)
+    for b in (0, 31):
+        k = keep[b, :int(kc[b])].long()
+        kb, ks = bd[b, k], sd[b, k]
+        assert bool((ks[:-1] >= ks[1:]).all())
+        iou = box_iou(kb, kb).fill_diagonal_(0)
+        assert float(iou.max()) < 0.5
+        k2, c2 = ops.nms_batched(kb[None].contiguous(), ks[None].contiguous(), None, 0.5)
+        assert int(c2[0]) == k.numel() and k2[0, :int(c2[0])].tolist() == list(range(k.numel()))
+
+
+def test_dilate_golden(golden):
+    g = golden("dilate")
+    b = torch.from_numpy(g["boxes"]).to(DEV)
+    for mode in ("full", "infer_half"):
+        out, valid = ops.dilate_boxes(b, int(g["W"]), int(g["H"]), (1, 10), mode)
+        assert np.array_equal(out.cpu().numpy(), g[f"{mode}__out"])
+        assert np.array_equal(valid.cpu().numpy(), g[f"{mode}__valid"])
+    assert U.box_dilate(100, 200, 200, 300, 640, 480) == (90, 190, 210, 310, True)
+
+
+def test_crop_golden_both_interps_and_layouts(golden):
+    g = golden("crop")
+    imgs = torch.from_numpy(g["images"]).to(DEV)
+    boxes = torch.from_numpy(g["boxes"]).to(DEV)
+    idx = torch.from_numpy(g["img_idx"]).to(DEV)
+    for interp in ("nearest", "bilinear"):
+        for out, patch in ((32, 16), (32, 8), (224, 16)):
+            ref = torch.from_numpy(g[f"{interp}_{out}"])
+            n = ref.shape[0]
+            chw = ops.crop_resize(imgs, boxes, idx, n, interp, out, patch, "chw").cpu()
+            assert torch.equal(chw, ref), (interp, out)
+            pm = ops.crop_resize(imgs, boxes, idx, n, interp, out, patch, "patch").cpu()
+            assert torch.equal(pm, O.patchify(ref, patch).to(torch.bfloat16)), (interp, out, patch)
+
+
+def test_crop_cfg3_random_boxes_bit_exact():
+    imgs = synth.make_images(4, 640, 640, seed=synth.SEED0 + 3)
+    boxes = synth.make_boxes_int(32, seed=synth.SEED0 + 3)
+    dil, valid = ops.dilate_boxes(boxes.to(DEV), 640, 640)
+    assert bool(valid.all())
+    idx = (torch.arange(32) % 4).to(torch.int32)
+    for interp in ("bilinear", "nearest"):
+        got = ops.crop_resize(imgs.to(DEV), dil, idx.to(DEV), 32, interp, 224, 16, "chw").cpu()
+        for i in range(32):
+            ref = O.crop_resize_norm(imgs[idx[i]].numpy(), dil[i].cpu().numpy(), 224, interp)
+            assert np.array_equal(got[i].numpy(), ref), (interp, i)
+
+
+def test_crop_image_reference_surface():
+    img = synth.make_images(1, 200, 300, seed=5)[0].numpy()
+    t = U.crop_image(img, 50, 40, 150, 120)
+    x0, y0, x1, y1, ok = O.dilate_box(50, 40, 150, 120, 300, 200, 1, 10, "infer_half")
+    assert np.array_equal(t.cpu().numpy(), O.crop_resize_norm(img, (x0, y0, x1, y1), 224, "nearest"))

@@ -1,0 +1,122 @@
+"""GPU parity tests for LayerNorm, attention, the ViT forward and the whole path.
+ViT tolerance (north star): max|Δlogits| / max|ref logits| <= 1e-2 (bf16 operands, fp32 accumulate)
+with identical top-1."""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import hotpath as O          # checker only
+from yolov8_vit_b200 import HotPath, HotPathConfig, ViTConfig, ViTModel, ops, synth
+from yolov8_vit_b200.utils import utils as U
+
+DEV = "cuda:0"
+REL_TOL = 1e-2
+
+
+def rel_err(got, ref):
+    return float((got - ref).abs().max() / ref.abs().max())
+
+
+def test_layernorm():
+    x = (torch.randn(1000, 768) * 2 + 0.5).to(torch.bfloat16)
+    g, b = torch.rand(768) + 0.5, torch.randn(768) * 0.1
+    ref = torch.nn.functional.layer_norm(x.float(), (768,), g, b, 1e-6)
+    got = ops.layernorm_bf16(x.to(DEV), g.to(DEV), b.to(DEV), 1e-6).cpu().float()
+    assert float((got - ref).abs().max()) <= 2 ** -7 * float(ref.abs().max())
+
+
+@pytest.mark.parametrize("n,T", [(3, 197), (2, 64), (2, 5), (1, 256)])
+def test_attention(n, T):
+    heads, dh = 12, 64
+    qkv = (torch.randn(n, T, 3 * heads * dh) * 0.7).to(torch.bfloat16)
+    q, k, v = qkv.float().reshape(n, T, 3, heads, dh).permute(2, 0, 3, 1, 4)
+    ref = (torch.softmax(q @ k.transpose(-1, -2) * dh ** -0.5, -1) @ v).transpose(1, 2).reshape(n, T, heads * dh)
+    got = ops.attention_bf16(qkv.to(DEV), heads).cpu().float()
+    assert float((got - ref).abs().max()) <= 2e-2 * float(ref.abs().max())
+
+
+def test_vit_tiny_golden(golden):
+    g = golden("vit")
+    tiny = O.ViTConfig(img=32, patch=16, dim=256, depth=2, heads=4, mlp=512, head_out=64, hidden=16, num_classes=5)
+    sd = O.make_vit_weights(tiny, seed=synth.SEED0 + 13)
+    m = ViTModel(ViTConfig(**{k: getattr(tiny, k) for k in tiny.__dataclass_fields__}), DEV).load_state_dict(sd)
+    x = torch.from_numpy(g["tiny_x"])
+    logits, top1, hidden = m.forward_patches(O.patchify(x, 16).to(torch.bfloat16).to(DEV), 5, return_hidden=True)
+    assert rel_err(hidden.cpu(), torch.from_numpy(g["tiny_hidden"])) <= REL_TOL
+    assert rel_err(logits.cpu(), torch.from_numpy(g["tiny_logits"])) <= REL_TOL
+    assert top1.cpu().tolist() == g["tiny_logits"].argmax(1).tolist()
+
+
+@pytest.fixture(scope="module")
+def full_model():
+    sd = O.make_vit_weights(O.ViTConfig(), seed=synth.SEED0 + 3)
+    return ViTModel(ViTConfig(), DEV).load_state_dict(sd), sd
+
+
+def test_vit_b16_golden(golden, full_model):
+    g = golden("vit")
+    m, _ = full_model
+    gen = torch.Generator().manual_seed(int(g["full_x_seed"]))
+    _ = torch.rand(5, 3, 32, 32, generator=gen)              # the tiny case consumed the generator first
+    x = (torch.rand(3, 3, 224, 224, generator=gen) * 2 - 1).to(torch.bfloat16).to(torch.float32)
+    logits = U.Network_Wrapper(m, 5)(x.to(DEV)).cpu()
+    ref = torch.from_numpy(g["full_logits"])
+    assert rel_err(logits, ref) <= REL_TOL, rel_err(logits, ref)
+    assert logits.argmax(1).tolist() == ref.argmax(1).tolist()
+
+
+def test_vit_b16_chunking_and_odd_counts(full_model):
+    """300 crops (> one 256-crop chunk, M not a multiple of 128): chunked == unchunked rows."""
+    m, sd = full_model
+    imgs = synth.make_images(4, 640, 640, seed=3).to(DEV)
+    boxes = synth.make_boxes_int(300, seed=4).to(DEV)
+    dil, _ = ops.dilate_boxes(boxes, 640, 640)
+    idx = (torch.arange(300, device=DEV) % 4).to(torch.int32)
+    p = ops.crop_resize(imgs, dil, idx, 300, "bilinear", 224, 16, "patch")
+    la, ta = m.forward_patches(p, 300)
+    lb, tb = m.forward_patches(p[: 37 * 196].contiguous(), 37)
+    assert torch.allclose(la[:37], lb, rtol=1e-3, atol=1e-3)
+    # oracle on a few of them
+    chw = ops.crop_resize(imgs, dil, idx, 300, "bilinear", 224, 16, "chw")
+    sel = [0, 123, 255, 256, 299]
+    ref = O.vit_forward(sd, chw[sel].cpu())
+    assert rel_err(la[sel].cpu(), ref) <= REL_TOL
+    assert ta[sel].cpu().tolist() == ref.argmax(1).tolist()
+
+
+def test_pipeline_cfg1_golden(golden, full_model):
+    g = golden("pipeline_cfg1")
+    m, _ = full_model
+    head = synth.make_head(1, nc=80, A=8400, n_obj=int(g["n_obj"]), n_jit=int(g["n_jit"]), seed=int(g["seed"]))
+    img = synth.make_images(1, 640, 640, seed=int(g["seed"]))
+    r = HotPath(m, HotPathConfig())(head.to(DEV), img.to(DEV), keep_intermediates=True)
+    k = int(r.keep_counts[0])
+    assert r.keep[0, :k].cpu().tolist() == g["keep"].tolist()
+    n = int(r.det_count[0])
+    assert np.array_equal(r.crops.det_box[0, :n].cpu().numpy(), g["box"])
+    assert np.array_equal(r.crops.det_crop_box[0, :n].cpu().numpy(), g["crop_box"])
+    assert np.array_equal(r.crops.det_anchor[0, :n].cpu().numpy(), g["anchor"])
+    assert np.array_equal(r.crops.det_label[0, :n].cpu().numpy(), g["label"])
+    assert r.n_crops == int(g["valid"].sum())
+    assert rel_err(r.logits.cpu(), torch.from_numpy(g["logits"])) <= REL_TOL
+    assert r.top1.cpu().tolist() == g["cls"].tolist()
+    rec = r.records[0, :n].cpu()
+    assert rec[:, 4].int().tolist() == g["cls"].tolist() and bool((rec[:, 7] == 1).all())
+
+
+def test_pipeline_batch_against_oracle(full_model):
+    """8 images end to end: integer outputs bit-exact per image, classes identical."""
+    m, sd = full_model
+    head = synth.make_head(8, 80, 8400, n_obj=3, n_jit=12, seed=21)
+    imgs = synth.make_images(8, 640, 640, seed=22)
+    r = HotPath(m, HotPathConfig())(head.to(DEV), imgs.to(DEV), keep_intermediates=True)
+    rec = r.records.cpu()
+    for b in range(8):
+        ref = O.pipeline_image(head[b], imgs[b].numpy(), sd)
+        n = int(r.det_count[b])
+        assert n == len(ref["keep"])
+        assert np.array_equal(r.crops.det_box[b, :n].cpu().numpy(), ref["box"])
+        assert np.array_equal(r.crops.det_crop_box[b, :n].cpu().numpy(), ref["crop_box"])
+        assert rec[b, :n, 4].int().tolist() == ref["cls"].tolist(), b

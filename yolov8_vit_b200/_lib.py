@@ -24,6 +24,7 @@ SYMBOLS = [
     "yv_vit_create", "yv_vit_destroy", "yv_vit_set_param", "yv_vit_missing_params",
     "yv_vit_workspace_bytes", "yv_vit_forward",
     "yv_gemm_bf16", "yv_layernorm_bf16", "yv_attention_bf16", "yv_pack_results",
+    "yv_prof_enable", "yv_prof_kinds", "yv_prof_kind_name", "yv_prof_read",
 ]
 
 
@@ -79,8 +80,27 @@ def load() -> ctypes.CDLL:
     lib.yv_layernorm_bf16.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_float, c_void_p]
     lib.yv_attention_bf16.argtypes = [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p]
     lib.yv_pack_results.argtypes = [c_void_p] * 6 + [c_int, c_int, c_void_p, c_void_p]
+    lib.yv_prof_enable.argtypes = [c_int]
+    lib.yv_prof_kind_name.restype = c_char_p
+    lib.yv_prof_kind_name.argtypes = [c_int]
+    lib.yv_prof_read.argtypes = [c_void_p, c_void_p, c_void_p]
     _lib = lib
     return lib
+
+
+def prof_enable(on: bool) -> None:
+    check(load().yv_prof_enable(1 if on else 0), "yv_prof_enable")
+
+
+def prof_read() -> dict:
+    """{kernel class: {"ms": device ms (event-bracketed), "launches": n, "work": bytes or flops}}"""
+    lib = load()
+    k = lib.yv_prof_kinds()
+    ms = (ctypes.c_double * k)()
+    ln = (ctypes.c_longlong * k)()
+    wk = (ctypes.c_double * k)()
+    check(lib.yv_prof_read(ms, ln, wk), "yv_prof_read")
+    return {lib.yv_prof_kind_name(i).decode(): {"ms": ms[i], "launches": int(ln[i]), "work": wk[i]} for i in range(k)}
 
 
 def check(rc: int, what: str = "") -> None:

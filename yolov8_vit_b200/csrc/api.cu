@@ -40,3 +40,78 @@ YV_EXPORT int yv_check_device(int dev) {
   }
   return YV_OK;
 }
+
+// ---- launch accounting + optional event profiling ------------------------------------------------
+#include <mutex>
+#include <vector>
+namespace {
+struct ProfState {
+  std::mutex mu;
+  bool on = false;
+  long long launches[YV_K_COUNT] = {0};
+  double work[YV_K_COUNT] = {0};
+  std::vector<cudaEvent_t> ev[YV_K_COUNT];     // start, end, start, end, ...
+  std::vector<cudaEvent_t> pool;
+} g_prof;
+cudaEvent_t prof_event() {
+  if (!g_prof.pool.empty()) { cudaEvent_t e = g_prof.pool.back(); g_prof.pool.pop_back(); return e; }
+  cudaEvent_t e = nullptr;
+  cudaEventCreate(&e);
+  return e;
+}
+}  // namespace
+
+void yv_prof_begin(int kind, cudaStream_t s, double work) {
+  std::lock_guard<std::mutex> lk(g_prof.mu);
+  g_prof.launches[kind] += 1;
+  g_prof.work[kind] += work;
+  if (g_prof.on) {
+    cudaEvent_t e = prof_event();
+    cudaEventRecord(e, s);
+    g_prof.ev[kind].push_back(e);
+  }
+}
+void yv_prof_end(int kind, cudaStream_t s) {
+  std::lock_guard<std::mutex> lk(g_prof.mu);
+  if (g_prof.on && (g_prof.ev[kind].size() & 1)) {
+    cudaEvent_t e = prof_event();
+    cudaEventRecord(e, s);
+    g_prof.ev[kind].push_back(e);
+  }
+}
+
+// on != 0: reset counters and start bracketing every kernel launch with CUDA events; 0: stop.
+YV_EXPORT int yv_prof_enable(int on) {
+  std::lock_guard<std::mutex> lk(g_prof.mu);
+  for (int k = 0; k < YV_K_COUNT; ++k) {
+    for (cudaEvent_t e : g_prof.ev[k]) g_prof.pool.push_back(e);
+    g_prof.ev[k].clear();
+    g_prof.launches[k] = 0;
+    g_prof.work[k] = 0;
+  }
+  g_prof.on = on != 0;
+  return YV_OK;
+}
+YV_EXPORT int yv_prof_kinds(void) { return YV_K_COUNT; }
+YV_EXPORT const char *yv_prof_kind_name(int kind) {
+  static const char *names[YV_K_COUNT] = {"decode_filter", "nms", "build_crops", "crop_resize", "gemm_tcgen05",
+                                          "layernorm", "attention", "wrapper_head", "misc"};
+  return (kind >= 0 && kind < YV_K_COUNT) ? names[kind] : "?";
+}
+// Synchronises the device, then fills per-kind totals since yv_prof_enable: device milliseconds
+// (sum of event-bracketed launch durations; 0 when profiling was off), launches, work.
+YV_EXPORT int yv_prof_read(double *ms, long long *launches, double *work) {
+  YV_CUDA(cudaDeviceSynchronize());
+  std::lock_guard<std::mutex> lk(g_prof.mu);
+  for (int k = 0; k < YV_K_COUNT; ++k) {
+    double t = 0;
+    for (size_t i = 0; i + 1 < g_prof.ev[k].size(); i += 2) {
+      float f = 0;
+      if (cudaEventElapsedTime(&f, g_prof.ev[k][i], g_prof.ev[k][i + 1]) == cudaSuccess) t += f;
+    }
+    if (ms) ms[k] = t;
+    if (launches) launches[k] = g_prof.launches[k];
+    if (work) work[k] = g_prof.work[k];
+  }
+  return YV_OK;
+}

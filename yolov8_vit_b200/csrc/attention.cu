@@ -196,6 +196,7 @@ int yv_attention_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, int
   }
   dim3 grid(heads, n);
   const float scale_log2e = (1.0f / sqrtf((float)dh)) * 1.4426950408889634f;
+  YvProf prof(YV_K_ATTN, s, 4.0 * n * heads * (double)T * T * dh);
   attention_kernel<<<grid, nw * 32, smem, s>>>(qkv, out, T, heads, scale_log2e);
   YV_LAUNCH_CHECK();
   return YV_OK;

@@ -39,6 +39,18 @@ int yv_cuda_fail(cudaError_t e, const char *what, const char *file, int line);
 static inline size_t yv_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 int yv_num_sms();
 
+// ---- launch accounting / optional CUDA-event profiling (api.cu) ------------------------------
+enum YvKernelKind { YV_K_DECODE = 0, YV_K_NMS, YV_K_BUILD, YV_K_CROP, YV_K_GEMM, YV_K_LN, YV_K_ATTN, YV_K_HEAD, YV_K_MISC, YV_K_COUNT };
+void yv_prof_begin(int kind, cudaStream_t s, double work);
+void yv_prof_end(int kind, cudaStream_t s);
+// RAII: counts one launch of `kind` (always) and, when profiling is on, brackets it with CUDA
+// events on the launching stream.  `work` = algorithmic bytes (HBM-bound kernels) or flops (GEMM).
+struct YvProf {
+  int kind; cudaStream_t s;
+  YvProf(int k, cudaStream_t st, double work) : kind(k), s(st) { yv_prof_begin(k, st, work); }
+  ~YvProf() { yv_prof_end(kind, s); }
+};
+
 // ---- device helpers ------------------------------------------------------------
 __device__ __forceinline__ float4 ld_stream_f4(const float *p) {
   float4 r;

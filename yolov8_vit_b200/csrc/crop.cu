@@ -275,6 +275,7 @@ YV_EXPORT int yv_dilate_boxes(const int32_t *boxes_i32, int n, int W, int H, int
   YV_REQUIRE(mode == YV_DILATE_FULL || mode == YV_DILATE_INFER_HALF, "yv_dilate_boxes: unknown mode %d", mode);
   if (n == 0) return YV_OK;
   YV_REQUIRE(boxes_i32 && out_boxes && out_valid, "yv_dilate_boxes: null pointer");
+  YvProf prof(YV_K_MISC, (cudaStream_t)stream, 0.0);
   dilate_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>((const int4 *)boxes_i32, n, W, H, num, den, mode,
                                                                    (int4 *)out_boxes, out_valid);
   YV_LAUNCH_CHECK();
@@ -294,6 +295,7 @@ YV_EXPORT int yv_build_crops(const float *boxes, const float *scores, const int3
   YV_REQUIRE(boxes && scores && keep && keep_counts && det_box && det_crop_box && det_score && det_label &&
                  det_anchor && det_count && det_crop && crop_box && crop_img && crop_det && n_crops,
              "yv_build_crops: null pointer");
+  YvProf prof(YV_K_BUILD, (cudaStream_t)stream, 0.0);
   build_crops_kernel<<<1, BC_T, 0, (cudaStream_t)stream>>>(
       (const float4 *)boxes, scores, labels, anchors, keep, keep_counts, B, stride, max_det, W, H, num, den, mode,
       (int4 *)det_box, (int4 *)det_crop_box, det_score, det_label, det_anchor, det_count, det_crop, (int4 *)crop_box,
@@ -317,6 +319,7 @@ YV_EXPORT int yv_crop_resize(const uint8_t *images, int B, int H, int W, const i
   dim3 grid((work + CR_T - 1) / CR_T, n);
   cudaStream_t s = (cudaStream_t)stream;
   const int4 *cb = (const int4 *)crop_box;
+  YvProf prof(YV_K_CROP, s, (double)n * out_size * out_size * 3 * (layout == YV_LAYOUT_PATCH_BF16 ? 2 : 4));
 #define YV_CR(I, L) crop_resize_kernel<I, L><<<grid, CR_T, 0, s>>>(images, H, W, cb, crop_img, n, n_dev, out_size, patch, out)
   if (interp == YV_INTERP_NEAREST) {
     if (layout == YV_LAYOUT_PATCH_BF16) YV_CR(YV_INTERP_NEAREST, YV_LAYOUT_PATCH_BF16);
@@ -336,6 +339,7 @@ YV_EXPORT int yv_pack_results(const int32_t *det_box, const float *det_score, co
   YV_REQUIRE(B >= 1 && max_det >= 1, "yv_pack_results: bad shape");
   YV_REQUIRE(det_box && det_score && det_anchor && det_count && det_crop && records, "yv_pack_results: null pointer");
   const int n = B * max_det;
+  YvProf prof(YV_K_MISC, (cudaStream_t)stream, 0.0);
   pack_results_kernel<<<(n + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
       (const int4 *)det_box, det_score, det_anchor, det_count, det_crop, top1, B, max_det, (float4 *)records);
   YV_LAUNCH_CHECK();

@@ -237,6 +237,7 @@ YV_EXPORT int yv_decode_filter(const float *head, int B, int nc, int A, float co
   st.ticket = (unsigned *)(w + L.o_ticket);
   YV_CUDA(cudaMemsetAsync(st.ticket, 0, (size_t)B * sizeof(unsigned), s));
   dim3 grid(L.tiles, B);
+  YvProf prof(YV_K_DECODE, s, (double)B * (4 + nc) * A * 4.0);
   if (L.vec == 4)
     decode_filter_kernel<4><<<grid, DEC_NT, 0, s>>>(head, nc, A, conf, unletterbox, ratio, dw, dh, cap, st,
                                                     (float4 *)boxes, scores, labels, anchors, counts);

@@ -282,6 +282,7 @@ int yv_gemm_launch(const void *A, const void *W, int M, int N, int K, const Gemm
   if (rc) return rc;
   const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
   const int grid = tiles < yv_num_sms() ? tiles : yv_num_sms();
+  YvProf prof(YV_K_GEMM, s, 2.0 * M * (double)N * K);
   gemm_bf16_kernel<<<grid, GEMM_THREADS, SMEM_BYTES, s>>>(tmA, tmB, ep, M, N, K);
   YV_LAUNCH_CHECK();
   return YV_OK;

@@ -327,6 +327,7 @@ YV_EXPORT int yv_nms_batched(const float *boxes, const float *scores, const int3
     W.lidx[i] = (int32_t *)(w + L.o_lidx[i]);
     W.lbox[i] = (float4 *)(w + L.o_lbox[i]);
   }
+  YvProf prof(YV_K_NMS, (cudaStream_t)stream, counts ? 0.0 : (double)B * n_all * 20.0);
   nms_kernel<<<B, NMS_T, 0, (cudaStream_t)stream>>>((const float4 *)boxes, scores, counts, stride, n_all,
                                                     iou_thr, max_keep, keep, keep_counts, W);
   YV_LAUNCH_CHECK();

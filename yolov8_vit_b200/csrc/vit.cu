@@ -113,6 +113,7 @@ int finalize(yv_vit *m, cudaStream_t s) {
     return YV_EINVAL;
   }
   const int n = m->T * m->cfg.dim;
+  YvProf prof(YV_K_MISC, s, 0.0);
   pos_table_kernel<<<(n + 255) / 256, 256, 0, s>>>(m->F("model.pos_embed"), m->F("model.cls_token"),
                                                    m->F("model.patch_embed.proj.bias"), m->wf + m->pos_table_off,
                                                    m->T, m->cfg.dim);
@@ -270,6 +271,7 @@ YV_EXPORT int yv_vit_forward(yv_vit_t *m, const void *patches_bf16, int n, float
       return rc;
     if (hidden) {
       const int tot = cc * c.head_out;
+      YvProf prof(YV_K_MISC, s, 0.0);
       gather_rows_f32_kernel<<<(tot + 255) / 256, 256, 0, s>>>(w.hidden, c.head_out, hidden + (size_t)c0 * c.head_out, cc, c.head_out);
       YV_LAUNCH_CHECK();
     }

@@ -144,6 +144,7 @@ int yv_ln_launch(const void *x, bool x_f32, size_t in_stride, const float *gamma
   YV_REQUIRE(x && gamma && beta && y, "layernorm: null pointer");
   YV_REQUIRE(in_stride % 8 == 0, "layernorm: row stride must be a multiple of 8 elements");
   const int grid = (rows + LN_WARPS - 1) / LN_WARPS;
+  YvProf prof(YV_K_LN, s, (double)rows * dim * (x_f32 ? 6.0 : 4.0));
   if (x_f32) layernorm_kernel<true><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, gamma, beta, y, rows, dim, eps);
   else layernorm_kernel<false><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, gamma, beta, y, rows, dim, eps);
   YV_LAUNCH_CHECK();
@@ -152,6 +153,7 @@ int yv_ln_launch(const void *x, bool x_f32, size_t in_stride, const float *gamma
 
 int yv_cls_rows_launch(float *x32, const float *cls_pos0, int n, int T, int dim, cudaStream_t s) {
   const int total = n * dim;
+  YvProf prof(YV_K_MISC, s, 0.0);
   cls_rows_kernel<<<(total + 255) / 256, 256, 0, s>>>(x32, cls_pos0, n, T, dim);
   YV_LAUNCH_CHECK();
   return YV_OK;
@@ -163,6 +165,7 @@ int yv_wrapper_head_launch(const float *hidden, int ld_hidden, const float *w1, 
   YV_REQUIRE(n >= 1 && head_out >= 1 && hid >= 1 && ncls >= 1, "wrapper head: bad shape");
   const size_t smem = (size_t)(head_out + hid + ncls) * sizeof(float);
   YV_REQUIRE(smem <= 48 * 1024, "wrapper head: %zu bytes of shared memory exceed 48 KB", smem);
+  YvProf prof(YV_K_HEAD, s, 0.0);
   wrapper_head_kernel<<<n, WH_T, smem, s>>>(hidden, ld_hidden, w1, b1, w3, b3, head_out, hid, ncls, logits, top1);
   YV_LAUNCH_CHECK();
   return YV_OK;
