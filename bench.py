@@ -1,0 +1,168 @@
+"""bench.py -- images/sec of the second-stage hot path (BASELINE.json metric) on N B200s.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A "step" is one pass of the hot path over one batch of synthetic input on every rank:
+  head [B,84,8400] f32 -> conf 0.35 -> custom_nms 0.45 -> alpha=0.1 dilation -> 224x224 bilinear
+  crop -> ViT-B/16 + wrapper head -> per-image records (+ final NCCL all-gather when N > 1).
+Workload = the north star's single-GPU target "YOLOv8n-640 -> ViT-B/16 at batch 256": B = 256
+images per GPU, OBJ objects x 24 candidate boxes per image (cfg4's 4 objects/image).  Images are
+batch-sharded (weak scaling: per-GPU work fixed), no collective on the data path.
+
+`value`   : whole-job images/s, inputs resident in HBM, CUDA events, max over ranks.
+`e2e`     : same metric through the public HotPath API from pinned HOST buffers (H2D of head +
+            images and D2H of the records inside the timed region).
+`roofline`: the dominant kernel (tcgen05 GEMM): flops per launch / event-timed launch duration.
+`cpu_baseline` / `--impl reference`: the oracle (a verbatim restatement of the reference's torch
+            CPU path; the reference itself is not importable) on the host cores.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+B_PER_GPU = 256
+N_OBJ = 4
+N_JIT = 24
+NC = 80
+ANCHORS = 8400
+IMG = 640
+SEED = 20240410 + 1
+FLOP_PER_CROP = 35.128e9           # SURVEY.md §8d (ViT-B/16 + heads)
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--batch", type=int, default=B_PER_GPU, help="images per GPU")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d["hbm_gbs"], d["bf16_tflops"], d.get("bf16_tflops_sustained", d["bf16_tflops"]), "measured"
+    return 6650.0, 1590.0, 1400.0, "fallback"
+
+
+def workload_name(batch):
+    return (f"YOLOv8n-640 head [{batch},{4 + NC},{ANCHORS}] f32 + {batch} images {IMG}x{IMG} u8 per GPU, "
+            f"{N_OBJ} objects x {N_JIT} candidates/img -> conf .35 -> custom_nms .45 -> dilate a=0.1 -> "
+            f"224 bilinear crop -> ViT-B/16 (+wrapper head)")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index=0):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        self.t.join(timeout=2)
+        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i] == "Active" for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------ CPU
+def make_inputs(batch, seed):
+    from yolov8_vit_b200 import synth
+    head = synth.make_head(batch, nc=NC, A=ANCHORS, n_obj=N_OBJ, n_jit=N_JIT, img=IMG, seed=seed)
+    imgs = synth.make_images(batch, IMG, IMG, seed=seed + 1)
+    return head, imgs
+
+
+def vit_weights():
+    from oracle import hotpath as O      # only to GENERATE the seeded synthetic weights
+    return O.make_vit_weights(O.ViTConfig(), seed=SEED)
+
+
+def cpu_pipeline(head, imgs, sd, threads):
+    """The reference's CPU path (oracle restatement) on `head`/`imgs`; returns (seconds, crops)."""
+    import torch
+    from oracle import hotpath as O
+    torch.set_num_threads(threads)
+    t0 = time.perf_counter()
+    crops = 0
+    for b in range(head.shape[0]):
+        r = O.pipeline_image(head[b], imgs[b].numpy(), sd)
+        crops += int(r["valid"].sum())
+    return time.perf_counter() - t0, crops
+
+
+def cpu_baseline(sd, budget_s=15.0):
+    """Bounded sample of the same workload: images are added until ~budget_s of CPU work."""
+    cores = os.cpu_count() or 1
+    head, imgs = make_inputs(64, SEED)
+    cpu_pipeline(head[:1], imgs[:1], sd, cores)                      # warm-up
+    t, c = cpu_pipeline(head[1:3], imgs[1:3], sd, cores)
+    n = int(max(2, min(61, budget_s / max(t / 2, 1e-3))))
+    t, c = cpu_pipeline(head[3:3 + n], imgs[3:3 + n], sd, cores)
+    return {"value": n / t, "unit": "images/s", "cores": cores, "kind": "port",
+            "sample": f"{n} images ({c} crops) of the same synthetic workload, oracle pipeline fp32, "
+                      f"torch {cores} threads, {t:.1f} s"}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU implementation of the path (oracle port: custom_nms is a
+    markdown snippet upstream and timm is absent, so the reference itself cannot be imported)."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    sd = vit_weights()
+    per_step = 6
+    head, imgs = make_inputs(per_step * (args.steps + args.warmup), SEED)
+    crops = 0
+    for w in range(args.warmup):
+        cpu_pipeline(head[w * per_step:(w + 1) * per_step], imgs[w * per_step:(w + 1) * per_step], sd, cores)
+    t0 = time.perf_counter()
+    for s in range(args.warmup, args.warmup + args.steps):
+        _, c = cpu_pipeline(head[s * per_step:(s + 1) * per_step], imgs[s * per_step:(s + 1) * per_step], sd, cores)
+        crops += c
+    dt = time.perf_counter() - t0
+    val = per_step * args.steps / dt
+    sample = f"{per_step} images/step x {args.steps} steps ({crops} crops), oracle pipeline fp32, torch {cores} threads"
+    print(json.dumps({
+        "impl": "reference", "metric": "images/sec detect-post->NMS->crop->ViT-B/16", "value": val,
+        "unit": "images/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": {"workload": workload_name(args.batch), "sample": sample},
+        "cpu_baseline": {"value": val, "unit": "images/s", "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
