@@ -1,0 +1,14 @@
+#!/bin/bash
+# quick iteration: GEMM + ViT parity, then the bench line
+mkdir -p gpurun_out
+for f in test_gpu_gemm test_gpu_vit; do
+  timeout 600 python -m pytest tests/$f.py -q -m gpu --timeout=300 -p no:cacheprovider > gpurun_out/$f.log 2>&1
+  echo "$f exit $?"; tail -n 4 gpurun_out/$f.log
+done
+python bench.py --no-cpu-baseline > gpurun_out/bench_iter.json 2> gpurun_out/bench_iter.err; echo "bench exit $?"
+python - <<'PY'
+import json
+d=json.loads(open('gpurun_out/bench_iter.json').read().strip().splitlines()[-1])
+for k in ('value','ms_per_step','stages_ms_per_step','roofline','e2e','clocks'): print(k, d.get(k))
+PY
+tail -n 5 gpurun_out/bench_iter.err

@@ -6,8 +6,9 @@
 //     both operands through UMMA shared-memory descriptors;
 //   * the fp32 accumulator lives in TMEM, double buffered (2 x 256 columns = all 512), so the
 //     epilogue of tile i overlaps the MMAs of tile i+1;
-//   * 8 epilogue warps pull the accumulator back with tcgen05.ld (32 lanes x 32 columns),
-//     apply bias / erf-GELU / residual / position-embedding and store bf16 or fp32;
+//   * 8 epilogue warps pull the accumulator back with tcgen05.ld (32 lanes x 16 columns), transpose
+//     it through padded shared memory so that global I/O is row-contiguous, apply bias / erf-GELU /
+//     residual / position-embedding and store bf16 or fp32;
 //   * persistent: one CTA per SM walks the tile list (n fastest, so the A rows of an m-block
 //     are served from L2 to its n-tiles while the weights stay L2 resident).
 // This is the ViT's only dense contraction: QKV, proj, fc1, fc2,
@@ -33,10 +34,29 @@ constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
 constexpr int NUM_EPI_WARPS = 8;
 constexpr int GEMM_THREADS = (4 + NUM_EPI_WARPS) * 32;
 constexpr int TMEM_COLS = 512;         // 2 accumulator stages x BN
-constexpr size_t SMEM_BYTES = (size_t)STAGES * STAGE_BYTES + 1024 /*align slack*/ + 256 /*barriers*/;
+constexpr int BAR_BYTES = 256;          // mbarriers + TMEM slot
+constexpr int EPI_LD = 20;              // epilogue staging row: 16 fp32 + 4 pad (80 B: conflict-free 16-byte rows)
+constexpr int EPI_BYTES = NUM_EPI_WARPS * 32 * EPI_LD * 4;
+constexpr size_t SMEM_BYTES = (size_t)STAGES * STAGE_BYTES + 1024 /*align slack*/ + BAR_BYTES + EPI_BYTES;
 
-__device__ __forceinline__ float gelu_erf(float x) {
-  return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
+// erf-GELU, x * Phi(x), with erf(z) ~ z * P(z^2) on |z| <= 3 (degree-8 minimax fit, clamped beyond):
+// |gelu error| < 6e-5 absolute for every x (well under the bf16 rounding of the stored result),
+// 15 FMA-pipe instructions and no MUFU -- erff() costs ~30 issue slots per element, which made the
+// K=768 fc1 GEMM epilogue-bound (one 128x256 tile has only 6144 MMA cycles).
+__device__ __forceinline__ float gelu_fast(float x) {
+  float z = x * 0.70710678118654752440f;
+  z = fminf(fmaxf(z, -3.0f), 3.0f);
+  const float z2 = z * z;
+  float p = 4.074204153e-08f;
+  p = fmaf(p, z2, -1.944820304e-06f);
+  p = fmaf(p, z2, 4.106048667e-05f);
+  p = fmaf(p, z2, -5.110365571e-04f);
+  p = fmaf(p, z2, 4.235425968e-03f);
+  p = fmaf(p, z2, -2.510285741e-02f);
+  p = fmaf(p, z2, 1.110793300e-01f);
+  p = fmaf(p, z2, -3.753148727e-01f);
+  p = fmaf(p, z2, 1.128268428e+00f);
+  return x * fmaf(0.5f * z, p, 0.5f);
 }
 
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
@@ -116,98 +136,89 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
     }
   } else if (warp >= 4) {
-    // ===================== epilogue: TMEM -> registers -> global =====================
+    // ===================== epilogue: TMEM -> registers -> smem transpose -> global =====================
+    // tcgen05.ld hands every thread one accumulator ROW (32 lanes x 16 columns per load).  Storing
+    // that directly would make each warp instruction touch 32 rows; instead the 32 x 16 fp32 block
+    // goes through a per-warp padded smem buffer and comes back with 4 lanes per row, so every
+    // global access (bias, residual, position table, output) is a run of 64 contiguous bytes per
+    // row and all per-column operands (bias) live in registers.
     const int ew = warp - 4;
     const int q = warp & 3;                        // TMEM lane quarter this warp may access
     const int half = ew >> 2;                      // column half of the tile
+    float *stg = reinterpret_cast<float *>(smem + (size_t)STAGES * STAGE_BYTES + BAR_BYTES) + ew * (32 * EPI_LD);
+    const int trow = lane >> 2, tseg = lane & 3;   // transposed role: row-in-group, 16-byte segment
     uint32_t it = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
       const uint32_t as = it & 1u, aph = (it >> 1) & 1u;
       const int m0 = (tile / n_tiles) * BM, n0 = (tile % n_tiles) * BN;
       mbar_wait(&tfull[as], aph);
       tc_fence_after();
-      const int row = m0 + q * 32 + lane;
-      const bool row_ok = row < M;
-      long long drow = row;
-      const float *pos_row = nullptr;
-      if (ep.group_rows > 0) {                     // patch-embed: token row = r + r/196 + 1, + pos[1 + r%196]
-        const int g = row / ep.group_rows;
-        drow = (long long)row + g + 1;
-        pos_row = ep.pos + (size_t)(row - g * ep.group_rows + 1) * N;
+      // the 4 rows this thread stores (per 16-column chunk)
+      long long drow[4];
+      const float *pos_row[4];
+      bool rok[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int row = m0 + q * 32 + i * 8 + trow;
+        rok[i] = row < M;
+        drow[i] = row;
+        pos_row[i] = nullptr;
+        if (ep.group_rows > 0) {                   // patch-embed: token row = r + r/196 + 1, + pos[1 + r%196]
+          const int g = row / ep.group_rows;
+          drow[i] = (long long)row + g + 1;
+          pos_row[i] = ep.pos + (size_t)(row - g * ep.group_rows + 1) * N;
+        }
       }
 #pragma unroll 1
-      for (int ch = 0; ch < BN / 2 / 32; ++ch) {
-        const int cbase = half * (BN / 2) + ch * 32;
-        uint32_t r[32];
-        tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + cbase, r);
+      for (int ch = 0; ch < BN / 2 / 16; ++ch) {
+        const int cbase = half * (BN / 2) + ch * 16;
+        uint32_t r[16];
+        tmem_ld_32x16(tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + cbase, r);
         tmem_ld_wait();
-        const int col0 = n0 + cbase;
-        if (row_ok && col0 < N) {
-          float v[32];
+        float4 *srow = reinterpret_cast<float4 *>(stg + lane * EPI_LD);
 #pragma unroll
-          for (int j = 0; j < 32; ++j) v[j] = __uint_as_float(r[j]);
-          const int ncols = min(32, N - col0);     // multiple of 8
-          if (ep.bias) {
+        for (int j = 0; j < 4; ++j)
+          srow[j] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
+                                __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+        __syncwarp();
+        const int col = n0 + cbase + tseg * 4;
+        if (col < N) {
+          float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (ep.bias) bias4 = __ldg(reinterpret_cast<const float4 *>(ep.bias + col));
 #pragma unroll
-            for (int j = 0; j < 32; ++j) if (j < ncols) v[j] += __ldg(ep.bias + col0 + j);
-          }
-          if (ep.gelu) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) v[j] = gelu_erf(v[j]);
-          }
-          if (pos_row) {
-#pragma unroll
-            for (int j = 0; j < 32; ++j) if (j < ncols) v[j] += __ldg(pos_row + col0 + j);
-          }
-          if (ep.residual && ep.res_f32) {
-            const float4 *rp = reinterpret_cast<const float4 *>((const float *)ep.residual + (size_t)drow * N + col0);
-#pragma unroll
-            for (int g = 0; g < 8; ++g) {
-              if (g * 4 < ncols) {
-                const float4 f = rp[g];
-                v[4 * g] += f.x; v[4 * g + 1] += f.y; v[4 * g + 2] += f.z; v[4 * g + 3] += f.w;
+          for (int i = 0; i < 4; ++i) {
+            if (!rok[i]) continue;
+            float4 v = *reinterpret_cast<const float4 *>(stg + (i * 8 + trow) * EPI_LD + tseg * 4);
+            v.x += bias4.x; v.y += bias4.y; v.z += bias4.z; v.w += bias4.w;
+            if (ep.gelu) { v.x = gelu_fast(v.x); v.y = gelu_fast(v.y); v.z = gelu_fast(v.z); v.w = gelu_fast(v.w); }
+            if (pos_row[i]) {
+              const float4 p = __ldg(reinterpret_cast<const float4 *>(pos_row[i] + col));
+              v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w;
+            }
+            const size_t o = (size_t)drow[i] * N + col;
+            if (ep.residual) {
+              if (ep.res_f32) {
+                const float4 f = *reinterpret_cast<const float4 *>((const float *)ep.residual + o);
+                v.x += f.x; v.y += f.y; v.z += f.z; v.w += f.w;
+              } else {
+                const uint2 u = *reinterpret_cast<const uint2 *>((const __nv_bfloat16 *)ep.residual + o);
+                const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&u.x));
+                const float2 f1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&u.y));
+                v.x += f0.x; v.y += f0.y; v.z += f1.x; v.w += f1.y;
               }
             }
-          } else if (ep.residual) {
-            const uint4 *rp = reinterpret_cast<const uint4 *>((const __nv_bfloat16 *)ep.residual + (size_t)drow * N + col0);
-#pragma unroll
-            for (int g = 0; g < 4; ++g) {
-              if (g * 8 < ncols) {
-                const uint4 u = rp[g];
-                const __nv_bfloat162 *h = reinterpret_cast<const __nv_bfloat162 *>(&u);
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                  const float2 f = __bfloat1622float2(h[e]);
-                  v[g * 8 + 2 * e] += f.x;
-                  v[g * 8 + 2 * e + 1] += f.y;
-                }
-              }
-            }
-          }
-          if (ep.out_f32) {
-            float4 *op = reinterpret_cast<float4 *>((float *)ep.out + (size_t)drow * N + col0);
-#pragma unroll
-            for (int g = 0; g < 8; ++g)
-              if (g * 4 < ncols) op[g] = make_float4(v[4 * g], v[4 * g + 1], v[4 * g + 2], v[4 * g + 3]);
-          } else {
-            uint4 *op = reinterpret_cast<uint4 *>((__nv_bfloat16 *)ep.out + (size_t)drow * N + col0);
-#pragma unroll
-            for (int g = 0; g < 4; ++g) {
-              if (g * 8 < ncols) {
-                uint4 u;
-                __nv_bfloat162 h0 = __floats2bfloat162_rn(v[8 * g], v[8 * g + 1]);
-                __nv_bfloat162 h1 = __floats2bfloat162_rn(v[8 * g + 2], v[8 * g + 3]);
-                __nv_bfloat162 h2 = __floats2bfloat162_rn(v[8 * g + 4], v[8 * g + 5]);
-                __nv_bfloat162 h3 = __floats2bfloat162_rn(v[8 * g + 6], v[8 * g + 7]);
-                u.x = *reinterpret_cast<unsigned *>(&h0);
-                u.y = *reinterpret_cast<unsigned *>(&h1);
-                u.z = *reinterpret_cast<unsigned *>(&h2);
-                u.w = *reinterpret_cast<unsigned *>(&h3);
-                op[g] = u;
-              }
+            if (ep.out_f32) {
+              *reinterpret_cast<float4 *>((float *)ep.out + o) = v;
+            } else {
+              __nv_bfloat162 h0 = __floats2bfloat162_rn(v.x, v.y), h1 = __floats2bfloat162_rn(v.z, v.w);
+              uint2 u;
+              u.x = *reinterpret_cast<unsigned *>(&h0);
+              u.y = *reinterpret_cast<unsigned *>(&h1);
+              *reinterpret_cast<uint2 *>((__nv_bfloat16 *)ep.out + o) = u;
             }
           }
         }
+        __syncwarp();
       }
       tc_fence_before();
       __syncwarp();
