@@ -1,10 +1,11 @@
 #!/bin/bash
-# quick iteration: GEMM + ViT parity, then the bench line
+# quick iteration: GEMM + ViT parity, per-shape GEMM timing, then the bench line
 mkdir -p gpurun_out
 for f in test_gpu_gemm test_gpu_vit; do
   timeout 600 python -m pytest tests/$f.py -q -m gpu --timeout=300 -p no:cacheprovider > gpurun_out/$f.log 2>&1
-  echo "$f exit $?"; tail -n 4 gpurun_out/$f.log
+  echo "$f exit $?"; tail -n 6 gpurun_out/$f.log
 done
+timeout 300 python tools/gemm_bench.py 2>&1 | tee gpurun_out/gemm_bench.log | tail -n 8
 python bench.py --no-cpu-baseline > gpurun_out/bench_iter.json 2> gpurun_out/bench_iter.err; echo "bench exit $?"
 python - <<'PY'
 import json

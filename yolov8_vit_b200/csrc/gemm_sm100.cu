@@ -1,9 +1,11 @@
 // gemm_sm100.cu -- K5: D[M,N] = A[M,K] * W[N,K]^T with fused epilogues, bf16 operands, fp32
 // accumulation, hand-written for sm_100a:
-//   * operands arrive by TMA (cp.async.bulk.tensor.2d, 128-byte swizzle) into a 4-stage
+//   * operands arrive by TMA (cp.async.bulk.tensor.2d, 128-byte swizzle) into a 6-stage
 //     shared-memory ring, completion on mbarriers;
-//   * ONE elected thread issues tcgen05.mma (cta_group::1, kind::f16, 128 x 256 x 16) reading
-//     both operands through UMMA shared-memory descriptors;
+//   * CTA PAIRS (cluster 2x1x1, cta_group::2): ONE elected thread of the leader CTA issues
+//     tcgen05.mma kind::f16 256 x 256 x 16 over both SMs; each CTA stages its 128 rows of A and its
+//     128 of the 256 rows of W, so a 256 x 256 tile costs 32 KB of L2->SM traffic per CTA per 64-wide
+//     k-block instead of 48 KB for a 128 x 256 tile (the 1-CTA version measured L2-feed-bound);
 //   * the fp32 accumulator lives in TMEM, double buffered (2 x 256 columns = all 512), so the
 //     epilogue of tile i overlaps the MMAs of tile i+1;
 //   * 8 epilogue warps pull the accumulator back with tcgen05.ld (32 lanes x 16 columns), transpose
@@ -23,13 +25,15 @@ using namespace sm100;
 
 namespace {
 
-constexpr int BM = 128;
+constexpr int BM = 128;                // accumulator rows per CTA (the pair's MMA is 256 x 256)
+constexpr int PM = 2 * BM;             // rows per tile of the CTA pair
 constexpr int BN = 256;
+constexpr int BNH = BN / 2;            // B rows each CTA of the pair stages
 constexpr int BK = 64;                 // 64 bf16 = 128 B = one swizzle atom row
-constexpr int STAGES = 4;
+constexpr int STAGES = 6;
 constexpr int UMMA_K = 16;
 constexpr int A_BYTES = BM * BK * 2;   // 16 KB
-constexpr int B_BYTES = BN * BK * 2;   // 32 KB
+constexpr int B_BYTES = BNH * BK * 2;  // 16 KB
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
 constexpr int NUM_EPI_WARPS = 8;
 constexpr int GEMM_THREADS = (4 + NUM_EPI_WARPS) * 32;
@@ -59,7 +63,7 @@ __device__ __forceinline__ float gelu_fast(float x) {
   return x * fmaf(0.5f * z, p, 0.5f);
 }
 
-__global__ void __launch_bounds__(GEMM_THREADS, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const GemmEpilogue ep, int M, int N, int K) {
   extern __shared__ uint8_t smem_raw[];
@@ -70,24 +74,29 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   uint32_t *tmem_slot = (uint32_t *)(bars + 2 * STAGES + 4);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m_tiles = (M + BM - 1) / BM, n_tiles = (N + BN - 1) / BN;
+  const int m_tiles = (M + PM - 1) / PM, n_tiles = (N + BN - 1) / BN;
   const int num_tiles = m_tiles * n_tiles, kblocks = K / BK;
+  const uint32_t rank = cluster_ctarank();            // 0 = leader of the CTA pair (issues the MMAs)
+  const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmB);
   }
   if (warp == 1 && lane == 0) {
-    for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 1); mbar_init(&empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], NUM_EPI_WARPS); }
+    // full: one arrive per producer of the pair (+ the bytes of both); empty / tfull: one multicast
+    // tcgen05.commit; tempty (leader's copy is the one waited on): every epilogue warp of both CTAs
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 2); mbar_init(&empty[i], 1); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 2 * NUM_EPI_WARPS); }
     fence_barrier_init();
   }
   if (warp == 2) {
-    tmem_alloc(tmem_slot, TMEM_COLS);
-    tmem_relinquish();
+    tmem_alloc_pair(tmem_slot, TMEM_COLS);
+    tmem_relinquish_pair();
   }
   tc_fence_before();
   __syncthreads();
+  cluster_sync_all();                                  // peer barriers / TMEM exist before any remote signal
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
@@ -96,25 +105,27 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int m0 = (tile / n_tiles) * BM, n0 = (tile % n_tiles) * BN;
+      for (int tile = pair; tile < num_tiles; tile += npairs) {
+        // this CTA stages its 128 rows of A and its 128 (of 256) rows of W
+        const int m0 = (tile / n_tiles) * PM + (int)rank * BM, n0 = (tile % n_tiles) * BN + (int)rank * BNH;
         for (int kb = 0; kb < kblocks; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1u);
           uint8_t *sa = smem + (size_t)stage * STAGE_BYTES, *sb = sa + A_BYTES;
-          mbar_arrive_expect_tx(&full[stage], STAGE_BYTES);
-          tma_load_2d(sa, &tmA, &full[stage], kb * BK, m0);
-          tma_load_2d(sb, &tmB, &full[stage], kb * BK, n0);
+          if (rank == 0) mbar_arrive_expect_tx(&full[stage], 2 * STAGE_BYTES);   // bytes of both CTAs
+          tma_load_2d_pair(sa, &tmA, &full[stage], kb * BK, m0);
+          tma_load_2d_pair(sb, &tmB, &full[stage], kb * BK, n0);
+          if (rank != 0) mbar_arrive_remote(&full[stage], 0);
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
       }
     }
-  } else if (warp == 1) {
-    // ===================== MMA issuer (one elected lane) =====================
+  } else if (warp == 1 && rank == 0) {
+    // ===================== MMA issuer (one elected lane of the leader CTA) =====================
     if (elect_one()) {
-      constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
+      constexpr uint32_t idesc = umma_idesc_bf16(PM, BN);
       int stage = 0;
       uint32_t phase = 0, it = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+      for (int tile = pair; tile < num_tiles; tile += npairs, ++it) {
         const uint32_t as = it & 1u, aph = (it >> 1) & 1u;
         mbar_wait(&tempty[as], aph ^ 1u);          // epilogue has drained this accumulator
         tc_fence_after();
@@ -127,12 +138,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k) {
             // advance 16 elements (32 B) along K inside the swizzle atom: +2 in the addr>>4 field
-            umma_bf16(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (uint32_t)((kb | k) != 0));
+            umma_bf16_pair(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (uint32_t)((kb | k) != 0));
           }
-          umma_commit(&empty[stage]);              // smem slot free once these MMAs retire
+          umma_commit_pair(&empty[stage]);         // both CTAs' smem slots free once these MMAs retire
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
-        umma_commit(&tfull[as]);                   // accumulator complete -> epilogue
+        umma_commit_pair(&tfull[as]);              // accumulator complete -> both CTAs' epilogues
       }
     }
   } else if (warp >= 4) {
@@ -148,9 +159,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     float *stg = reinterpret_cast<float *>(smem + (size_t)STAGES * STAGE_BYTES + BAR_BYTES) + ew * (32 * EPI_LD);
     const int trow = lane >> 2, tseg = lane & 3;   // transposed role: row-in-group, 16-byte segment
     uint32_t it = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++it) {
+    for (int tile = pair; tile < num_tiles; tile += npairs, ++it) {
       const uint32_t as = it & 1u, aph = (it >> 1) & 1u;
-      const int m0 = (tile / n_tiles) * BM, n0 = (tile % n_tiles) * BN;
+      const int m0 = (tile / n_tiles) * PM + (int)rank * BM, n0 = (tile % n_tiles) * BN;
       mbar_wait(&tfull[as], aph);
       tc_fence_after();
       // the 4 rows this thread stores (per 16-column chunk)
@@ -222,13 +233,17 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty[as]);     // this warp is done with the accumulator
+      if (lane == 0) {                             // this warp is done with the accumulator (leader's barrier)
+        if (rank == 0) mbar_arrive(&tempty[as]);
+        else mbar_arrive_remote(&tempty[as], 0);
+      }
     }
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) tmem_dealloc(tmem_base, TMEM_COLS);
+  cluster_sync_all();                                  // the peer may still be reading our smem / signalling us
+  if (warp == 2) tmem_dealloc_pair(tmem_base, TMEM_COLS);
 }
 
 // ---- host side: tensor maps ----------------------------------------------------------------
@@ -289,10 +304,11 @@ int yv_gemm_launch(const void *A, const void *W, int M, int N, int K, const Gemm
   CUtensorMap tmA, tmB;
   int rc = make_tmap(&tmA, A, (uint64_t)M, (uint64_t)K, BM);
   if (rc) return rc;
-  rc = make_tmap(&tmB, W, (uint64_t)N, (uint64_t)K, BN);
+  rc = make_tmap(&tmB, W, (uint64_t)N, (uint64_t)K, BNH);
   if (rc) return rc;
-  const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
-  const int grid = tiles < yv_num_sms() ? tiles : yv_num_sms();
+  const int tiles = ((M + PM - 1) / PM) * ((N + BN - 1) / BN);
+  const int pairs = yv_num_sms() / 2;
+  const int grid = 2 * (tiles < pairs ? tiles : pairs);
   YvProf prof(YV_K_GEMM, s, 2.0 * M * (double)N * K);
   gemm_bf16_kernel<<<grid, GEMM_THREADS, SMEM_BYTES, s>>>(tmA, tmB, ep, M, N, K);
   YV_LAUNCH_CHECK();
