@@ -9,6 +9,7 @@
 // Data layout in HBM (per chunk of Cc crops, M = Cc * T token rows):
 //   x32  [M, dim]   f32   residual stream (kept fp32 so 24 residual adds do not accumulate bf16 rounding)
 //   y    [M, dim]   bf16  LayerNorm output / attention output (GEMM A operands)
+//   d    [M, dim]   bf16  proj / fc2 output (+bias): the residual delta the next LayerNorm adds to x32
 //   qkv  [M, 3 dim] bf16  timm packing (q | k | v, head-major)
 //   h    [M, mlp]   bf16  GELU(fc1)
 // Weights are packed once to bf16 [out, in] (K-major = the UMMA B operand as stored by torch).
@@ -82,7 +83,7 @@ void add_param(yv_vit *m, const std::string &name, size_t numel, bool bf16) {
 
 struct VitWs {
   float *x32;
-  __nv_bfloat16 *y, *qkv, *h, *cls_ln;
+  __nv_bfloat16 *y, *d, *qkv, *h, *cls_ln;
   float *hidden;
   size_t total;
 };
@@ -95,6 +96,7 @@ VitWs vit_ws(const yv_vit *m, void *base, int chunk) {
   VitWs w;
   w.x32 = (float *)(b + o);            o = yv_align_up(o + M * c.dim * 4, 1024);
   w.y = (__nv_bfloat16 *)(b + o);      o = yv_align_up(o + M * c.dim * 2, 1024);
+  w.d = (__nv_bfloat16 *)(b + o);      o = yv_align_up(o + M * c.dim * 2, 1024);
   w.qkv = (__nv_bfloat16 *)(b + o);    o = yv_align_up(o + M * 3 * c.dim * 2, 1024);
   w.h = (__nv_bfloat16 *)(b + o);      o = yv_align_up(o + M * c.mlp * 2, 1024);
   w.cls_ln = (__nv_bfloat16 *)(b + o); o = yv_align_up(o + (size_t)chunk * c.dim * 2, 1024);
@@ -247,22 +249,26 @@ YV_EXPORT int yv_vit_forward(yv_vit_t *m, const void *patches_bf16, int n, float
     ep = GemmEpilogue{w.x32, nullptr, nullptr, pos_table, NP, false, true, false};
     if ((rc = yv_gemm_launch(patches, m->B("model.patch_embed.proj.weight"), cc * NP, D, m->pdim, ep, s))) return rc;
     if ((rc = yv_cls_rows_launch(w.x32, pos_table, cc, T, D, s))) return rc;
+    // Residual adds are fused into the NEXT LayerNorm (x32 += d, fp32), so proj / fc2 store a plain
+    // bf16 delta d: same HBM traffic, but no global loads on the GEMM epilogue's critical path.
+    const __nv_bfloat16 *pending = nullptr;            // delta not yet added to x32
     for (int i = 0; i < c.depth; ++i) {
       const std::string p = "model.blocks." + std::to_string(i) + ".";
-      if ((rc = yv_ln_launch(w.x32, true, D, m->F(p + "norm1.weight"), m->F(p + "norm1.bias"), w.y, M, D, c.eps, s))) return rc;
+      if ((rc = yv_ln_launch(w.x32, true, D, pending, D, true, m->F(p + "norm1.weight"), m->F(p + "norm1.bias"), w.y, M, D, c.eps, s))) return rc;
       ep = GemmEpilogue{w.qkv, m->F(p + "attn.qkv.bias"), nullptr, nullptr, 0, false, false, false};
       if ((rc = yv_gemm_launch(w.y, m->B(p + "attn.qkv.weight"), M, 3 * D, D, ep, s))) return rc;
       if ((rc = yv_attention_launch(w.qkv, w.y, cc, T, c.heads, D / c.heads, s))) return rc;
-      ep = GemmEpilogue{w.x32, m->F(p + "attn.proj.bias"), w.x32, nullptr, 0, false, true, true};
+      ep = GemmEpilogue{w.d, m->F(p + "attn.proj.bias"), nullptr, nullptr, 0, false, false, false};
       if ((rc = yv_gemm_launch(w.y, m->B(p + "attn.proj.weight"), M, D, D, ep, s))) return rc;
-      if ((rc = yv_ln_launch(w.x32, true, D, m->F(p + "norm2.weight"), m->F(p + "norm2.bias"), w.y, M, D, c.eps, s))) return rc;
+      if ((rc = yv_ln_launch(w.x32, true, D, w.d, D, true, m->F(p + "norm2.weight"), m->F(p + "norm2.bias"), w.y, M, D, c.eps, s))) return rc;
       ep = GemmEpilogue{w.h, m->F(p + "mlp.fc1.bias"), nullptr, nullptr, 0, true, false, false};
       if ((rc = yv_gemm_launch(w.y, m->B(p + "mlp.fc1.weight"), M, c.mlp, D, ep, s))) return rc;
-      ep = GemmEpilogue{w.x32, m->F(p + "mlp.fc2.bias"), w.x32, nullptr, 0, false, true, true};
+      ep = GemmEpilogue{w.d, m->F(p + "mlp.fc2.bias"), nullptr, nullptr, 0, false, false, false};
       if ((rc = yv_gemm_launch(w.h, m->B(p + "mlp.fc2.weight"), M, D, c.mlp, ep, s))) return rc;
+      pending = w.d;
     }
-    // final norm on the class-token rows only, 1000-way head, wrapper MLP + argmax
-    if ((rc = yv_ln_launch(w.x32, true, (size_t)T * D, m->F("model.norm.weight"), m->F("model.norm.bias"), w.cls_ln, cc, D, c.eps, s))) return rc;
+    // final norm on the class-token rows only (+ the last fc2 delta), 1000-way head, wrapper MLP + argmax
+    if ((rc = yv_ln_launch(w.x32, true, (size_t)T * D, pending, (size_t)T * D, false, m->F("model.norm.weight"), m->F("model.norm.bias"), w.cls_ln, cc, D, c.eps, s))) return rc;
     ep = GemmEpilogue{w.hidden, m->F("model.head.bias"), nullptr, nullptr, 0, false, true, false};
     if ((rc = yv_gemm_launch(w.cls_ln, m->B("model.head.weight"), cc, c.head_out, D, ep, s))) return rc;
     if ((rc = yv_wrapper_head_launch(w.hidden, c.head_out, m->F("fc.1.weight"), m->F("fc.1.bias"), m->F("fc.3.weight"),

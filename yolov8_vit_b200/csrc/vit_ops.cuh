@@ -4,10 +4,13 @@
 #include <cuda_bf16.h>
 #include <stdint.h>
 
-// y[r, :] = LayerNorm(x[r * in_stride : +dim]) * gamma + beta; fp32 statistics, bf16 output.
-// x is f32 (x_f32 = true, the residual stream) or bf16.  dim % 256 == 0, dim <= 1024.
-int yv_ln_launch(const void *x, bool x_f32, size_t in_stride, const float *gamma, const float *beta,
-                 __nv_bfloat16 *y, int rows, int dim, float eps, cudaStream_t s);
+// y[r, :] = LayerNorm(x[r * in_stride : +dim] (+ delta[r * delta_stride : +dim])) * gamma + beta; fp32
+// statistics, bf16 output.  x is f32 (x_f32 = true, the residual stream) or bf16.  With `delta` the
+// residual add of the preceding GEMM is fused here (x += delta, written back when `writeback`), so the
+// GEMM epilogue is a plain bf16 store.  dim % 256 == 0, dim <= 1024.
+int yv_ln_launch(const void *x, bool x_f32, size_t in_stride, const __nv_bfloat16 *delta, size_t delta_stride,
+                 bool writeback, const float *gamma, const float *beta, __nv_bfloat16 *y, int rows, int dim, float eps,
+                 cudaStream_t s);
 
 // softmax(Q K^T / sqrt(dh)) V; qkv [n*T, 3*heads*dh] bf16 (timm packing: q | k | v, head-major),
 // out [n*T, heads*dh] bf16.  dh == 64, T <= 256.
