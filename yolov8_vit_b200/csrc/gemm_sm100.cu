@@ -39,30 +39,53 @@ constexpr int NUM_EPI_WARPS = 8;
 constexpr int GEMM_THREADS = (4 + NUM_EPI_WARPS) * 32;
 constexpr int TMEM_COLS = 512;         // 2 accumulator stages x BN
 constexpr int BAR_BYTES = 256;          // mbarriers + TMEM slot
-constexpr int EPI_LD = 20;              // epilogue staging row: 16 fp32 + 4 pad (80 B: conflict-free 16-byte rows)
-constexpr int EPI_BYTES = NUM_EPI_WARPS * 32 * EPI_LD * 4;
+constexpr int EPI_BYTES = NUM_EPI_WARPS * 32 * 16 * 4;   // per warp: 32 rows x 16 fp32, XOR-swizzled 16-byte segments
 constexpr size_t SMEM_BYTES = (size_t)STAGES * STAGE_BYTES + 1024 /*align slack*/ + BAR_BYTES + EPI_BYTES;
 
 // erf-GELU, x * Phi(x), with erf(z) ~ z * P(z^2) on |z| <= 3 (degree-8 minimax fit, clamped beyond):
 // |gelu error| < 6e-5 absolute for every x (well under the bf16 rounding of the stored result),
-// 15 FMA-pipe instructions and no MUFU -- erff() costs ~30 issue slots per element, which made the
+// ~9 issue slots per element with packed fp32x2 FMAs and no MUFU -- erff() costs ~30 issue slots per element, which made the
 // K=768 fc1 GEMM epilogue-bound (one 128x256 tile has only 6144 MMA cycles).
-__device__ __forceinline__ float gelu_fast(float x) {
-  float z = x * 0.70710678118654752440f;
-  z = fminf(fmaxf(z, -3.0f), 3.0f);
-  const float z2 = z * z;
-  float p = 4.074204153e-08f;
-  p = fmaf(p, z2, -1.944820304e-06f);
-  p = fmaf(p, z2, 4.106048667e-05f);
-  p = fmaf(p, z2, -5.110365571e-04f);
-  p = fmaf(p, z2, 4.235425968e-03f);
-  p = fmaf(p, z2, -2.510285741e-02f);
-  p = fmaf(p, z2, 1.110793300e-01f);
-  p = fmaf(p, z2, -3.753148727e-01f);
-  p = fmaf(p, z2, 1.128268428e+00f);
-  return x * fmaf(0.5f * z, p, 0.5f);
+// Packed fp32x2 arithmetic (sm_100: one FFMA2 / FMUL2 does two lanes) halves the GELU issue cost.
+__device__ __forceinline__ uint64_t pk2(float a, float b) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ void unpk2(uint64_t v, float &a, float &b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+  return r;
+}
+__device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) {
+  uint64_t r;
+  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+  return r;
+}
+__device__ __forceinline__ void gelu2(float &a, float &b) {
+  const float k = 0.70710678118654752440f;
+  const float za = fminf(fmaxf(a * k, -3.0f), 3.0f), zb = fminf(fmaxf(b * k, -3.0f), 3.0f);
+  const uint64_t z = pk2(za, zb), z2 = mul2(z, z);
+  uint64_t p = fma2(pk2(4.074204153e-08f, 4.074204153e-08f), z2, pk2(-1.944820304e-06f, -1.944820304e-06f));
+  p = fma2(p, z2, pk2(4.106048667e-05f, 4.106048667e-05f));
+  p = fma2(p, z2, pk2(-5.110365571e-04f, -5.110365571e-04f));
+  p = fma2(p, z2, pk2(4.235425968e-03f, 4.235425968e-03f));
+  p = fma2(p, z2, pk2(-2.510285741e-02f, -2.510285741e-02f));
+  p = fma2(p, z2, pk2(1.110793300e-01f, 1.110793300e-01f));
+  p = fma2(p, z2, pk2(-3.753148727e-01f, -3.753148727e-01f));
+  p = fma2(p, z2, pk2(1.128268428e+00f, 1.128268428e+00f));
+  const uint64_t t = fma2(mul2(z, pk2(0.5f, 0.5f)), p, pk2(0.5f, 0.5f));
+  unpk2(mul2(pk2(a, b), t), a, b);
+}
+__device__ __forceinline__ void gelu4(float4 &v) {
+  gelu2(v.x, v.y);
+  gelu2(v.z, v.w);
 }
 
+// GELU / OUT_F32 select the epilogue arithmetic at compile time; EXTRA compiles in the rarely used
+// position-table (patch embedding) and residual operands.
+template <bool GELU, bool OUT_F32, bool EXTRA>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const GemmEpilogue ep, int M, int N, int K) {
@@ -150,75 +173,89 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // ===================== epilogue: TMEM -> registers -> smem transpose -> global =====================
     // tcgen05.ld hands every thread one accumulator ROW (32 lanes x 16 columns per load).  Storing
     // that directly would make each warp instruction touch 32 rows; instead the 32 x 16 fp32 block
-    // goes through a per-warp padded smem buffer and comes back with 4 lanes per row, so every
-    // global access (bias, residual, position table, output) is a run of 64 contiguous bytes per
-    // row and all per-column operands (bias) live in registers.
+    // goes through a per-warp XOR-swizzled smem buffer (conflict-free both ways) and comes back with
+    // 4 lanes per row, so every global access is a run of 64 contiguous bytes per row and the
+    // per-column operand (bias) lives in registers, fetched BEFORE the wait on the accumulator.
+    // The TMEM load of chunk c+1 is issued as soon as chunk c is in smem, hiding its latency.
     const int ew = warp - 4;
     const int q = warp & 3;                        // TMEM lane quarter this warp may access
     const int half = ew >> 2;                      // column half of the tile
-    float *stg = reinterpret_cast<float *>(smem + (size_t)STAGES * STAGE_BYTES + BAR_BYTES) + ew * (32 * EPI_LD);
+    float *stg = reinterpret_cast<float *>(smem + (size_t)STAGES * STAGE_BYTES + BAR_BYTES) + ew * (32 * 16);
     const int trow = lane >> 2, tseg = lane & 3;   // transposed role: row-in-group, 16-byte segment
+    constexpr int NCH = BN / 2 / 16;               // 16-column chunks per warp
     uint32_t it = 0;
     for (int tile = pair; tile < num_tiles; tile += npairs, ++it) {
       const uint32_t as = it & 1u, aph = (it >> 1) & 1u;
       const int m0 = (tile / n_tiles) * PM + (int)rank * BM, n0 = (tile % n_tiles) * BN;
-      mbar_wait(&tfull[as], aph);
-      tc_fence_after();
-      // the 4 rows this thread stores (per 16-column chunk)
-      long long drow[4];
+      const int colw = n0 + half * (BN / 2) + tseg * 4;       // this thread's first column (chunk 0)
+      float4 bias4[NCH];
+#pragma unroll
+      for (int ch = 0; ch < NCH; ++ch) {
+        bias4[ch] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (ep.bias && colw + ch * 16 < N) bias4[ch] = __ldg(reinterpret_cast<const float4 *>(ep.bias + colw + ch * 16));
+      }
+      // the 4 rows this thread stores (per chunk)
+      size_t obase[4];
       const float *pos_row[4];
       bool rok[4];
 #pragma unroll
       for (int i = 0; i < 4; ++i) {
         const int row = m0 + q * 32 + i * 8 + trow;
         rok[i] = row < M;
-        drow[i] = row;
+        long long drow = row;
         pos_row[i] = nullptr;
-        if (ep.group_rows > 0) {                   // patch-embed: token row = r + r/196 + 1, + pos[1 + r%196]
+        if (EXTRA && ep.group_rows > 0) {          // patch-embed: token row = r + r/196 + 1, + pos[1 + r%196]
           const int g = row / ep.group_rows;
-          drow[i] = (long long)row + g + 1;
+          drow = (long long)row + g + 1;
           pos_row[i] = ep.pos + (size_t)(row - g * ep.group_rows + 1) * N;
         }
+        obase[i] = (size_t)drow * N + colw;
       }
-#pragma unroll 1
-      for (int ch = 0; ch < BN / 2 / 16; ++ch) {
-        const int cbase = half * (BN / 2) + ch * 16;
-        uint32_t r[16];
-        tmem_ld_32x16(tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + cbase, r);
-        tmem_ld_wait();
-        float4 *srow = reinterpret_cast<float4 *>(stg + lane * EPI_LD);
+      mbar_wait(&tfull[as], aph);
+      tc_fence_after();
+      const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + half * (BN / 2);
+      uint32_t r[16];
+      tmem_ld_32x16(tbase, r);
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-          srow[j] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
-                                __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+      for (int ch = 0; ch < NCH; ++ch) {
+        tmem_ld_wait();
+        {
+          float4 *srow = reinterpret_cast<float4 *>(stg + lane * 16);
+          const int sw = (lane >> 1) & 3;
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            srow[j ^ sw] = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
+                                       __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+        }
+        if (ch + 1 < NCH) tmem_ld_32x16(tbase + (ch + 1) * 16, r);
         __syncwarp();
-        const int col = n0 + cbase + tseg * 4;
-        if (col < N) {
-          float4 bias4 = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (ep.bias) bias4 = __ldg(reinterpret_cast<const float4 *>(ep.bias + col));
+        if (colw + ch * 16 < N) {
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
+            const int rr = i * 8 + trow;
+            float4 v = *reinterpret_cast<const float4 *>(stg + rr * 16 + ((tseg ^ ((rr >> 1) & 3)) << 2));
             if (!rok[i]) continue;
-            float4 v = *reinterpret_cast<const float4 *>(stg + (i * 8 + trow) * EPI_LD + tseg * 4);
-            v.x += bias4.x; v.y += bias4.y; v.z += bias4.z; v.w += bias4.w;
-            if (ep.gelu) { v.x = gelu_fast(v.x); v.y = gelu_fast(v.y); v.z = gelu_fast(v.z); v.w = gelu_fast(v.w); }
-            if (pos_row[i]) {
-              const float4 p = __ldg(reinterpret_cast<const float4 *>(pos_row[i] + col));
-              v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w;
-            }
-            const size_t o = (size_t)drow[i] * N + col;
-            if (ep.residual) {
-              if (ep.res_f32) {
-                const float4 f = *reinterpret_cast<const float4 *>((const float *)ep.residual + o);
-                v.x += f.x; v.y += f.y; v.z += f.z; v.w += f.w;
-              } else {
-                const uint2 u = *reinterpret_cast<const uint2 *>((const __nv_bfloat16 *)ep.residual + o);
-                const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&u.x));
-                const float2 f1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&u.y));
-                v.x += f0.x; v.y += f0.y; v.z += f1.x; v.w += f1.y;
+            v.x += bias4[ch].x; v.y += bias4[ch].y; v.z += bias4[ch].z; v.w += bias4[ch].w;
+            if (GELU) gelu4(v);
+            const size_t o = obase[i] + ch * 16;
+            if (EXTRA) {
+              if (pos_row[i]) {
+                const float4 p = __ldg(reinterpret_cast<const float4 *>(pos_row[i] + colw + ch * 16));
+                v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w;
+              }
+              if (ep.residual) {
+                if (ep.res_f32) {
+                  const float4 f = *reinterpret_cast<const float4 *>((const float *)ep.residual + o);
+                  v.x += f.x; v.y += f.y; v.z += f.z; v.w += f.w;
+                } else {
+                  const uint2 u = *reinterpret_cast<const uint2 *>((const __nv_bfloat16 *)ep.residual + o);
+                  const float2 f0 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&u.x));
+                  const float2 f1 = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162 *>(&u.y));
+                  v.x += f0.x; v.y += f0.y; v.z += f1.x; v.w += f1.y;
+                }
               }
             }
-            if (ep.out_f32) {
+            if (OUT_F32) {
               *reinterpret_cast<float4 *>((float *)ep.out + o) = v;
             } else {
               __nv_bfloat162 h0 = __floats2bfloat162_rn(v.x, v.y), h1 = __floats2bfloat162_rn(v.z, v.w);
@@ -265,7 +302,13 @@ void init_once() {
     return;
   }
   g_encode = (PFN_encodeTiled)fn;
-  e = cudaFuncSetAttribute(gemm_bf16_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
+#define YV_SET(G, F, X)                                                                                       \
+  if (e == cudaSuccess)                                                                                     \
+    e = cudaFuncSetAttribute(gemm_bf16_kernel<G, F, X>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
+  e = cudaSuccess;
+  YV_SET(false, false, false) YV_SET(false, false, true) YV_SET(false, true, false) YV_SET(false, true, true)
+  YV_SET(true, false, false) YV_SET(true, false, true) YV_SET(true, true, false) YV_SET(true, true, true)
+#undef YV_SET
   if (e != cudaSuccess) {
     g_init_status = yv_cuda_fail(e, "cudaFuncSetAttribute(gemm smem)", __FILE__, __LINE__);
   }
@@ -310,7 +353,16 @@ int yv_gemm_launch(const void *A, const void *W, int M, int N, int K, const Gemm
   const int pairs = yv_num_sms() / 2;
   const int grid = 2 * (tiles < pairs ? tiles : pairs);
   YvProf prof(YV_K_GEMM, s, 2.0 * M * (double)N * K);
-  gemm_bf16_kernel<<<grid, GEMM_THREADS, SMEM_BYTES, s>>>(tmA, tmB, ep, M, N, K);
+  const bool extra = ep.group_rows > 0 || ep.residual != nullptr;
+#define YV_GO(G, F, X) gemm_bf16_kernel<G, F, X><<<grid, GEMM_THREADS, SMEM_BYTES, s>>>(tmA, tmB, ep, M, N, K)
+  if (ep.gelu) {
+    if (ep.out_f32) { if (extra) YV_GO(true, true, true); else YV_GO(true, true, false); }
+    else { if (extra) YV_GO(true, false, true); else YV_GO(true, false, false); }
+  } else {
+    if (ep.out_f32) { if (extra) YV_GO(false, true, true); else YV_GO(false, true, false); }
+    else { if (extra) YV_GO(false, false, true); else YV_GO(false, false, false); }
+  }
+#undef YV_GO
   YV_LAUNCH_CHECK();
   return YV_OK;
 }
