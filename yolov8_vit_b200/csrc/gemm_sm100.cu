@@ -333,6 +333,12 @@ int make_tmap(CUtensorMap *m, const void *ptr, uint64_t rows, uint64_t cols, uin
 
 }  // namespace
 
+int yv_tmap_bf16_2d(CUtensorMap *m, const void *ptr, uint64_t rows, uint64_t cols, uint32_t box_rows) {
+  std::call_once(g_once, init_once);
+  if (g_init_status != YV_OK) return g_init_status;
+  return make_tmap(m, ptr, rows, cols, box_rows);
+}
+
 int yv_gemm_launch(const void *A, const void *W, int M, int N, int K, const GemmEpilogue &ep, cudaStream_t s) {
   YV_REQUIRE(M >= 1 && N >= 8 && K >= BK, "yv_gemm: bad shape M=%d N=%d K=%d", M, N, K);
   YV_REQUIRE(K % BK == 0, "yv_gemm: K=%d must be a multiple of %d", K, BK);

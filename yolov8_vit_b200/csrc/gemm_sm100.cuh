@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <cuda_bf16.h>
+#include <cuda.h>
 
 struct GemmEpilogue {
   void *out;                        // [rows, N] bf16 or f32 (row remapped when group_rows > 0)
@@ -17,3 +18,7 @@ struct GemmEpilogue {
 
 // D = A[M,K] * W[N,K]^T with the epilogue above.  K % 64 == 0, N % 8 == 0.
 int yv_gemm_launch(const void *A, const void *W, int M, int N, int K, const GemmEpilogue &ep, cudaStream_t s);
+
+// TMA descriptor of a row-major bf16 [rows, cols] matrix: box = box_rows x 64 columns (128 B), 128-byte
+// swizzle, zero fill out of bounds -- the K-major (or, read the other way, MN-major) UMMA operand layout.
+int yv_tmap_bf16_2d(CUtensorMap *m, const void *ptr, uint64_t rows, uint64_t cols, uint32_t box_rows);
