@@ -10,7 +10,7 @@
 //   MMA      S_g = Q_g K^T  (128 x NK x 64, g = query rows 0-127 / 128-255) into TMEM,
 //            then O_g = P_g V (128 x 64 x NK) into the TMEM columns S_g just vacated; V is consumed
 //            as an MN-major B operand, so no transpose is ever materialised;
-//   softmax  8 warps (4 per query tile, one thread per row): two passes over the S row in TMEM
+//   softmax  16 warps (8 per query tile; a row is split between 2 threads): two passes over S in TMEM
 //            (max, then exp2 / sum), P written as bf16 into shared memory in the K-major
 //            128B-swizzled A-operand layout; finally O * (1/sum) -> bf16 -> global.
 // The fp32 scores never leave the SM; HBM traffic is qkv in, out out.
@@ -25,11 +25,11 @@ namespace {
 
 constexpr int AT_DH = 64;
 constexpr int AT_QROWS = 256;                       // Q box rows (two 128-row query tiles)
-constexpr int AT_THREADS = 12 * 32;                 // TMA, MMA, TMEM-alloc, spare + 8 softmax warps
+constexpr int AT_THREADS = 20 * 32;                 // TMA, MMA, TMEM-alloc, spare + 16 softmax warps
 constexpr int AT_Q_BYTES = AT_QROWS * AT_DH * 2;    // 32 KB
 constexpr int AT_KV_BYTES = 256 * AT_DH * 2;        // 32 KB reserved each (box is NK rows)
 constexpr int AT_P_BYTES = 4 * 128 * 128;           // per query tile: 4 chunks of 64 keys x 128 rows x 128 B
-constexpr int AT_SMEM = AT_Q_BYTES + 2 * AT_KV_BYTES + 2 * AT_P_BYTES + 1024 + 256;
+constexpr int AT_SMEM = AT_Q_BYTES + 2 * AT_KV_BYTES + 2 * AT_P_BYTES + 2304;   // + barriers / exchange
 constexpr int AT_TMEM_COLS = 512;                   // S_0 at column 0, S_1 at column 256
 
 // MN-major B operand (V: keys x 64, 128-byte swizzled rows of dh): 8-key groups are 1024 B apart
@@ -53,13 +53,15 @@ struct AttnBars {
   uint64_t qk_full, v_full;
   uint64_t s_full[2], p_full[2], o_full[2], t_free[2];
   uint32_t tmem_slot;
+  float xch[2][2][128];       // [tile][slot][row]: max / sum exchange between the two column halves
 };
 
 __global__ void __launch_bounds__(AT_THREADS, 1)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
                     __nv_bfloat16 *__restrict__ out, int n_items, int T, int heads, float scale_log2e) {
-  extern __shared__ uint8_t at_raw[];
-  uint8_t *smem = (uint8_t *)(((uintptr_t)at_raw + 1023) & ~(uintptr_t)1023);
+  extern __shared__ __align__(1024) uint8_t at_raw[];
+  uint8_t *smem = at_raw;                           // 128B-swizzled tiles need 1024-byte alignment
+  if ((smem_u32(smem) & 1023u) != 0u) __trap();
   uint8_t *sQ = smem, *sK = sQ + AT_Q_BYTES, *sV = sK + AT_KV_BYTES, *sP = sV + AT_KV_BYTES;
   AttnBars *bar = reinterpret_cast<AttnBars *>(sP + 2 * AT_P_BYTES);
 
@@ -78,9 +80,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     mbar_init(&bar->v_full, 1);
     for (int g = 0; g < 2; ++g) {
       mbar_init(&bar->s_full[g], 1);
-      mbar_init(&bar->p_full[g], 4);                // the 4 softmax warps of the tile
+      mbar_init(&bar->p_full[g], 8);                // the 8 softmax warps of the tile
       mbar_init(&bar->o_full[g], 1);
-      mbar_init(&bar->t_free[g], 4);
+      mbar_init(&bar->t_free[g], 8);
     }
     fence_barrier_init();
   }
@@ -145,54 +147,72 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       }
     }
   } else if (warp >= 4) {
-    // ===================== softmax + output: one thread per query row =====================
-    const int g = (warp - 4) >> 2;                  // query tile
-    const int q = warp & 3;                         // TMEM lane quarter
+    // ===================== softmax + output =====================
+    // 16 warps: query tile g, TMEM lane quarter q (one thread per query row), column half hf.  The two
+    // warps that share a row exchange their partial max / sum through shared memory (named barrier per
+    // tile).  4 softmax warps per scheduler hide the MUFU / tcgen05.ld latencies that 2 could not.
+    const int sw_id = warp - 4;
+    const int q = warp & 3, g = (sw_id >> 2) & 1, hf = sw_id >> 3;
     if (g < NG) {
       const int trow = q * 32 + lane;               // row inside the tile
       const int tok = g * 128 + trow;               // token index inside the crop
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + g * 256;
       uint8_t *prow = sP + g * AT_P_BYTES + trow * 128;
-      const int sw = trow & 7;
+      const int swz = trow & 7;
+      const int H0 = ((NK / 16 + 1) / 2) * 16;      // first half: ceil(chunks / 2) 16-key chunks
+      const int c_lo = hf ? H0 : 0, c_hi = hf ? NK : H0;
+      // slot[hf] carries my max to the partner; once I have read the partner's max from slot[hf ^ 1]
+      // that slot is mine to carry my sum back (each slot has one writer and one reader per phase)
+      float *xmine = bar->xch[g][hf] + trow, *xother = bar->xch[g][hf ^ 1] + trow;
       uint32_t it = 0;
       for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
         const uint32_t ph = it & 1u;
         const int crop = item / heads, head = item - crop * heads;
         mbar_wait(&bar->s_full[g], ph);
         tc_fence_after();
-        // pass 1: row maximum over the valid keys
+        // pass 1: maximum of this warp's half of the row (keys >= T are masked)
         float mx = -INFINITY;
-        for (int c = 0; c < NK; c += 32) {
+        for (int c = c_lo; c < c_hi; c += 32) {
           uint32_t a[16], b[16];
-          const bool two = c + 16 < NK;
+          const bool two = c + 16 < c_hi;
           tmem_ld_32x16(taddr + c, a);
           if (two) tmem_ld_32x16(taddr + c + 16, b);
           tmem_ld_wait();
+          if (c + 32 <= T) {
 #pragma unroll
-          for (int j = 0; j < 16; ++j)
-            if (c + j < T) mx = fmaxf(mx, __uint_as_float(a[j]));
-          if (two) {
+            for (int j = 0; j < 16; ++j) mx = fmaxf(mx, fmaxf(__uint_as_float(a[j]), __uint_as_float(b[j])));
+          } else {
 #pragma unroll
             for (int j = 0; j < 16; ++j)
-              if (c + 16 + j < T) mx = fmaxf(mx, __uint_as_float(b[j]));
+              if (c + j < T) mx = fmaxf(mx, __uint_as_float(a[j]));
+            if (two) {
+#pragma unroll
+              for (int j = 0; j < 16; ++j)
+                if (c + 16 + j < T) mx = fmaxf(mx, __uint_as_float(b[j]));
+            }
           }
         }
+        *xmine = mx;
+        asm volatile("bar.sync %0, 256;" ::"r"(1 + g) : "memory");
+        mx = fmaxf(mx, *xother);
         const float mneg = -mx * scale_log2e;
         // pass 2: p = exp2(s * scale - max * scale); row sum; P -> smem (bf16, K-major, 128B swizzle)
         float sum = 0.f;
         uint32_t r[16];
-        tmem_ld_32x16(taddr, r);
-        for (int c = 0; c < NK; c += 16) {
+        tmem_ld_32x16(taddr + c_lo, r);
+        for (int c = c_lo; c < c_hi; c += 16) {
           tmem_ld_wait();
           float p[16];
 #pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            const float e = ex2_approx(fmaf(__uint_as_float(r[j]), scale_log2e, mneg));
-            p[j] = (c + j < T) ? e : 0.f;
-          }
-          if (c + 16 < NK) tmem_ld_32x16(taddr + c + 16, r);
+          for (int j = 0; j < 16; ++j) p[j] = ex2_approx(fmaf(__uint_as_float(r[j]), scale_log2e, mneg));
+          if (c + 16 < c_hi) tmem_ld_32x16(taddr + c + 16, r);
+          if (c + 16 > T) {
 #pragma unroll
-          for (int j = 0; j < 16; ++j) sum += p[j];
+            for (int j = 0; j < 16; ++j)
+              if (c + j >= T) p[j] = 0.f;
+          }
+#pragma unroll
+          for (int j = 0; j < 16; j += 4) sum += (p[j] + p[j + 1]) + (p[j + 2] + p[j + 3]);
           uint8_t *chunk = prow + (c >> 6) * (128 * 128);
           const int u0 = (c & 63) >> 3;             // 16-byte unit (8 keys) inside the 128-byte row
 #pragma unroll
@@ -206,29 +226,29 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
             w.y = *reinterpret_cast<uint32_t *>(&h1);
             w.z = *reinterpret_cast<uint32_t *>(&h2);
             w.w = *reinterpret_cast<uint32_t *>(&h3);
-            *reinterpret_cast<uint4 *>(chunk + (((u0 + u) ^ sw) << 4)) = w;
+            *reinterpret_cast<uint4 *>(chunk + (((u0 + u) ^ swz) << 4)) = w;
           }
         }
         fence_proxy_async_smem();                   // P (generic-proxy stores) -> visible to the UMMA reads
         tc_fence_before();                          // our tcgen05.ld of S_g precede the MMA that overwrites it
         __syncwarp();
         if (lane == 0) mbar_arrive(&bar->p_full[g]);
+        *xother = sum;
+        asm volatile("bar.sync %0, 256;" ::"r"(1 + g) : "memory");
+        const float inv = 1.0f / (sum + *xmine);
 
-        // O_g = P_g V is in TMEM columns [0, 64) of the tile: normalise, convert, store
-        const float inv = 1.0f / sum;
+        // O_g = P_g V is in TMEM columns [0, 64) of the tile: this warp normalises and stores 32 of them
         mbar_wait(&bar->o_full[g], ph);
         tc_fence_after();
-        uint32_t o0[16], o1[16], o2[16], o3[16];
-        tmem_ld_32x16(taddr, o0);
-        tmem_ld_32x16(taddr + 16, o1);
-        tmem_ld_32x16(taddr + 32, o2);
-        tmem_ld_32x16(taddr + 48, o3);
+        uint32_t o0[16], o1[16];
+        tmem_ld_32x16(taddr + hf * 32, o0);
+        tmem_ld_32x16(taddr + hf * 32 + 16, o1);
         tmem_ld_wait();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&bar->t_free[g]);   // the accumulator columns may be reused
         if (tok < T) {
-          uint4 *dst = reinterpret_cast<uint4 *>(out + ((size_t)crop * T + tok) * D + (size_t)head * AT_DH);
+          uint4 *dst = reinterpret_cast<uint4 *>(out + ((size_t)crop * T + tok) * D + (size_t)head * AT_DH + hf * 32);
           auto pack8 = [&](const uint32_t *v) {
             uint4 w;
             __nv_bfloat162 h0 = __floats2bfloat162_rn(__uint_as_float(v[0]) * inv, __uint_as_float(v[1]) * inv);
@@ -243,8 +263,6 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           };
           dst[0] = pack8(o0); dst[1] = pack8(o0 + 8);
           dst[2] = pack8(o1); dst[3] = pack8(o1 + 8);
-          dst[4] = pack8(o2); dst[5] = pack8(o2 + 8);
-          dst[6] = pack8(o3); dst[7] = pack8(o3 + 8);
         }
       }
     }
