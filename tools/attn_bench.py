@@ -4,7 +4,7 @@ sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
 from yolov8_vit_b200 import ops
 dev = "cuda:0"
-n, T, H = 268, 197, 12
+n, T, H = int(os.environ.get('N', 268)), 197, 12
 qkv = (torch.randn(n, T, 3 * H * 64, device=dev) * 0.7).to(torch.bfloat16)
 NCU = bool(os.environ.get("NCU"))
 for _ in range(1 if NCU else 3):
@@ -18,3 +18,4 @@ ts.sort()
 ms = ts[len(ts) // 2]
 fl = 4.0 * n * H * T * T * 64
 print(f"attention n={n} T={T}: {ms*1e3:.1f} us, {fl/ms/1e9:.1f} TFLOP/s, {ms*1e3/(n*H/148):.2f} us per item per SM")
+

@@ -47,22 +47,6 @@ constexpr size_t SMEM_BYTES = (size_t)STAGES * STAGE_BYTES + 1024 /*align slack*
 // ~9 issue slots per element with packed fp32x2 FMAs and no MUFU -- erff() costs ~30 issue slots per element, which made the
 // K=768 fc1 GEMM epilogue-bound (one 128x256 tile has only 6144 MMA cycles).
 // Packed fp32x2 arithmetic (sm_100: one FFMA2 / FMUL2 does two lanes) halves the GELU issue cost.
-__device__ __forceinline__ uint64_t pk2(float a, float b) {
-  uint64_t r;
-  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
-  return r;
-}
-__device__ __forceinline__ void unpk2(uint64_t v, float &a, float &b) { asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(v)); }
-__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
-  uint64_t r;
-  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
-  return r;
-}
-__device__ __forceinline__ uint64_t mul2(uint64_t a, uint64_t b) {
-  uint64_t r;
-  asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
-  return r;
-}
 __device__ __forceinline__ void gelu2(float &a, float &b) {
   const float k = 0.70710678118654752440f;
   const float za = fminf(fmaxf(a * k, -3.0f), 3.0f), zb = fminf(fmaxf(b * k, -3.0f), 3.0f);
