@@ -37,6 +37,9 @@ ANCHORS = 8400
 IMG = 640
 SEED = 20240410 + 1
 FLOP_PER_CROP = 35.128e9           # SURVEY.md §8d (ViT-B/16 + heads)
+# ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch, mean of the four block GEMMs
+# at M = 50 432 (profiles/r01_vit_ncu_v2.md): (378.7 + 261.9 + 115.9 + 339.9) / 4 MB
+GEMM_DRAM_BYTES_PER_LAUNCH = 274.1e6
 
 
 def parse():
@@ -200,13 +203,12 @@ def run_ours(args):
         return r
 
     def step_e2e():
-        h = head_h.to(dev, non_blocking=True)
-        im = imgs_h.to(dev, non_blocking=True)
-        r = hp(h, im)
+        # public host-buffer entry point: pinned head + images in, pinned records out; the upload of
+        # later image slices overlaps the ViT of earlier ones (HotPath.run_host)
+        r = hp.run_host(head_h, imgs_h, rec_h, device=dev)
         if world > 1:
             gather_records(r.records, world * B)
-        rec_h.copy_(r.records, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
+            torch.cuda.current_stream().synchronize()
         return r
 
     def barrier():
@@ -236,8 +238,11 @@ def run_ours(args):
         r = step_resident()
     clocks = ClockSampler(local)
     clocks.start()
-    ms, r = timed(step_resident, args.steps, prof=True)
+    ms, r = timed(step_resident, args.steps)
     clk = clocks.stop()
+    # second pass of the same K steps with every launch event-bracketed on its stream: per-kernel
+    # device time for the roofline (kept out of the headline timing: 2 events per launch)
+    ms_prof, _ = timed(step_resident, args.steps, prof=True)
     prof = _lib.prof_read()
     _lib.prof_enable(False)
     n_crops = r.n_crops
@@ -263,14 +268,17 @@ def run_ours(args):
                        "l2": "inputs larger than L2 (head 722 MB + images 315 MB per step)",
                        "parallelism": f"batch-sharded x{world}, final NCCL all-gather of records"},
             "roofline": {"bound": "tensor", "kernel": "gemm_bf16_kernel (tcgen05)", "achieved": achieved,
-                         "peak": tf_sus, "unit": "TFLOP/s", "frac": achieved / tf_sus, "traffic": None,
+                         "peak": tf_sus, "unit": "TFLOP/s", "frac": achieved / tf_sus, "traffic": GEMM_DRAM_BYTES_PER_LAUNCH,
+                         "traffic_note": "mean dram read+write bytes of the qkv/proj/fc1/fc2 launches of a 256-crop "
+                                         "chunk, ncu --set full (profiles/r01_vit_ncu_v2.md)",
                          "peak_source": f"{which} bf16_tflops_sustained (kernel timed inside a long step)",
                          "launches_per_step": g["launches"] / args.steps,
                          "flops_per_launch": per_launch_flops, "ms_per_launch": per_launch_ms,
-                         "share_of_step": g["ms"] / ms},
+                         "share_of_step": g["ms"] / ms_prof},
             "stages_ms_per_step": stage_ms,
             "decode_hbm": {"achieved_gbs": dec["work"] / max(dec["ms"], 1e-9) / 1e6, "peak_gbs": hbm,
                            "frac": dec["work"] / max(dec["ms"], 1e-9) / 1e6 / hbm},
+            "nms_us_per_img": prof["nms"]["ms"] * 1e3 / (B * args.steps),
             "crops_per_s": world * n_crops * args.steps / (ms * 1e-3),
             "vit_tflops_effective": world * n_crops * FLOP_PER_CROP * args.steps / (ms * 1e-3) / 1e12,
             "e2e": {"value": world * B * args.steps / (ms_e2e * 1e-3), "unit": "images/s",

@@ -120,3 +120,31 @@ def test_pipeline_batch_against_oracle(full_model):
         assert np.array_equal(r.crops.det_box[b, :n].cpu().numpy(), ref["box"])
         assert np.array_equal(r.crops.det_crop_box[b, :n].cpu().numpy(), ref["crop_box"])
         assert rec[b, :n, 4].int().tolist() == ref["cls"].tolist(), b
+
+
+@pytest.mark.parametrize("slices,chunk", [(1, 256), (3, 256), (8, 16), (13, 7)])
+def test_run_host_equals_resident_path(full_model, slices, chunk):
+    """The pipelined host-buffer entry point (sliced upload on a second stream, crops gathered into
+    fixed ViT chunks) returns exactly the records / logits of the resident call on the same inputs."""
+    m, _ = full_model
+    head = synth.make_head(13, 80, 8400, n_obj=3, n_jit=12, seed=31)
+    imgs = synth.make_images(13, 640, 640, seed=32)
+    hp = HotPath(m, HotPathConfig())
+    ref = hp(head.to(DEV), imgs.to(DEV))
+    rec_h = torch.empty(13, 100, 8).pin_memory()
+    for _ in range(2):                      # second call reuses the staging buffers
+        r = hp.run_host(head.pin_memory(), imgs.pin_memory(), rec_h, device=DEV, slices=slices, vit_chunk=chunk)
+    assert r.n_crops == ref.n_crops
+    assert torch.equal(r.det_count.cpu(), ref.det_count.cpu())
+    assert torch.equal(rec_h, ref.records.cpu())
+    assert torch.equal(r.top1.cpu(), ref.top1.cpu())
+    # chunk boundaries differ from the resident call (different GEMM M), the arithmetic per row does not
+    assert torch.equal(r.logits.cpu(), ref.logits.cpu())
+
+
+def test_run_host_no_detections(full_model):
+    m, _ = full_model
+    head = torch.zeros(4, 84, 8400)
+    imgs = synth.make_images(4, 640, 640, seed=33)
+    r = HotPath(m, HotPathConfig()).run_host(head, imgs, device=DEV, slices=2)
+    assert r.n_crops == 0 and float(r.records[..., 7].sum()) == 0.0

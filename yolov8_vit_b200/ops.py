@@ -184,9 +184,11 @@ def attention_bf16(qkv: torch.Tensor, heads: int):
     return out
 
 
-def pack_results(cl: CropList, top1: torch.Tensor | None):
+def pack_results(cl: CropList, top1: torch.Tensor | None, out: torch.Tensor | None = None):
+    """top1 is indexed by det_crop (crop index inside `cl`); `out` [B,max_det,8] f32 is written in place."""
     B, max_det = cl.det_score.shape
-    rec = torch.empty(B, max_det, 8, dtype=torch.float32, device=cl.det_score.device)
+    rec = torch.empty(B, max_det, 8, dtype=torch.float32, device=cl.det_score.device) if out is None else out
+    assert rec.is_contiguous() and rec.shape == (B, max_det, 8)
     check(load().yv_pack_results(ptr(cl.det_box), ptr(cl.det_score), ptr(cl.det_anchor), ptr(cl.det_count),
                                  ptr(cl.det_crop), ptr(top1), B, max_det, ptr(rec), stream_ptr(rec.device)),
           "yv_pack_results")

@@ -93,6 +93,115 @@ class HotPath:
         return r
 
 
+    # ------------------------------------------------------------------ host-buffer entry point
+    def _host_state(self, head_h: torch.Tensor, imgs_h: torch.Tensor, dev, slices: int):
+        key = (tuple(head_h.shape), tuple(imgs_h.shape), str(dev), slices)
+        st = getattr(self, "_hs", None)
+        if st is None or st["key"] != key:
+            st = {"key": key,
+                  "head": torch.empty(head_h.shape, dtype=torch.float32, device=dev),
+                  "imgs": torch.empty(imgs_h.shape, dtype=torch.uint8, device=dev),
+                  "pin": torch.empty(slices, dtype=torch.int32).pin_memory(),
+                  "front": torch.cuda.Stream(device=dev, priority=-1),
+                  "events": [torch.cuda.Event() for _ in range(slices)],
+                  "patches": None, "top1": None, "logits": None, "cap": 0}
+            self._hs = st
+        return st
+
+    def _grow(self, st, need: int, used: int, dev):
+        """Crop-indexed buffers (patches, logits, top1) with geometric growth; `used` crops are preserved."""
+        if need <= st["cap"]:
+            return
+        cap = max(need, 2 * st["cap"], 1024)
+        m = self.model.cfg
+        g = (self.cfg.out_size // m.patch) ** 2
+        new = (torch.empty(cap * g, 3 * m.patch * m.patch, dtype=torch.bfloat16, device=dev),
+               torch.empty(cap, m.num_classes, dtype=torch.float32, device=dev),
+               torch.empty(cap, dtype=torch.int32, device=dev))
+        if used and st["patches"] is not None:
+            new[0][:used * g].copy_(st["patches"][:used * g])
+            new[1][:used].copy_(st["logits"][:used])
+            new[2][:used].copy_(st["top1"][:used])
+        st["patches"], st["logits"], st["top1"], st["cap"] = new[0], new[1], new[2], cap
+
+    def run_host(self, head_h: torch.Tensor, imgs_h: torch.Tensor, out_records_h: torch.Tensor | None = None,
+                 device="cuda:0", slices: int = 8, vit_chunk: int = 256) -> HotPathResult:
+        """The same path from HOST buffers (pinned memory recommended): head [B,4+nc,A] f32 and images
+        [B,H,W,3] u8 on the CPU -> records on the CPU (`out_records_h`, pinned, optional).
+
+        The batch is cut into `slices` image slices.  A high-priority "front" stream uploads slice
+        after slice and runs decode -> custom_nms -> crop list on each as soon as it has landed; the
+        caller's stream gathers the crops of every finished slice into one patch buffer and runs
+        the ViT over fixed `vit_chunk`-crop chunks as soon as enough crops exist, so the upload of
+        slice i+1.. overlaps the ViT of slice ..i.  Host syncs: one 4-byte crop count per slice
+        (it sizes the ViT launches) and the final record download.  Not re-entrant per instance
+        (it owns staging buffers); use one HotPath per thread.
+        """
+        if self.model is None:
+            raise ValueError("run_host needs a classifier")
+        if head_h.is_cuda or imgs_h.is_cuda:
+            raise ValueError("run_host takes host tensors; call the instance for device-resident inputs")
+        c = self.cfg
+        dev = torch.device(device)
+        B, H, W, _ = imgs_h.shape
+        slices = max(1, min(slices, B))
+        st = self._host_state(head_h, imgs_h, dev, slices)
+        main = torch.cuda.current_stream(dev)
+        front = st["front"]
+        bounds = [(B * i) // slices for i in range(slices + 1)]
+        front.wait_stream(main)            # staging buffers of the previous call are no longer read
+        cls, dets = [], []
+        with torch.cuda.stream(front):
+            for i in range(slices):
+                a, b = bounds[i], bounds[i + 1]
+                hd, im = st["head"][a:b], st["imgs"][a:b]
+                hd.copy_(head_h[a:b], non_blocking=True)
+                im.copy_(imgs_h[a:b], non_blocking=True)
+                cand, keep, keep_counts = self.detect(hd)
+                boxes, scores, labels, anchors, _ = cand
+                cl = ops.build_crops(boxes, scores, labels, anchors, keep, keep_counts, c.max_det, W, H, c.alpha,
+                                     c.dilate_mode)
+                st["pin"][i:i + 1].copy_(cl.n_crops, non_blocking=True)
+                st["events"][i].record(front)
+                cls.append(cl)
+                dets.append((cand, keep, keep_counts))
+        total = done = 0
+        offs = []
+        g = (c.out_size // self.model.cfg.patch) ** 2
+
+        def vit(upto):
+            nonlocal done
+            while done < upto:
+                n = min(vit_chunk, upto - done)
+                self.model.forward_patches(st["patches"][done * g:(done + n) * g], n,
+                                           out_logits=st["logits"][done:done + n], out_top1=st["top1"][done:done + n])
+                done += n
+
+        for i in range(slices):
+            a, b = bounds[i], bounds[i + 1]
+            st["events"][i].synchronize()
+            n_i = min(int(st["pin"][i].item()), cls[i].crop_box.shape[0])
+            main.wait_event(st["events"][i])
+            self._grow(st, total + n_i, total, dev)
+            if n_i:
+                ops.crop_resize(st["imgs"][a:b], cls[i].crop_box, cls[i].crop_img, n_i, c.interp, c.out_size,
+                                self.model.cfg.patch, "patch", out=st["patches"][total * g:(total + n_i) * g])
+            offs.append(total)
+            total += n_i
+            vit(done + ((total - done) // vit_chunk) * vit_chunk)      # only full chunks while slices remain
+        vit(total)
+        rec = torch.empty(B, c.max_det, 8, dtype=torch.float32, device=dev)
+        for i in range(slices):
+            a, b = bounds[i], bounds[i + 1]
+            ops.pack_results(cls[i], st["top1"][offs[i]:] if total else None, out=rec[a:b])
+        if out_records_h is not None:
+            out_records_h.copy_(rec, non_blocking=True)
+        main.synchronize()
+        return HotPathResult(records=rec, det_count=torch.cat([cl.det_count for cl in cls]), n_crops=total,
+                             logits=st["logits"][:total] if total else None,
+                             top1=st["top1"][:total] if total else None)
+
+
 def records_to_tuples(records: torch.Tensor, names=None):
     """[(image_name, class_id, conf, xmin, ymin, xmax, ymax)] sorted by image name -- the return
     value of the wrapper's main() (YOLOTensorRT_yolodet_py_解读.md:103-116).  Host side."""

@@ -90,11 +90,14 @@ class ViTModel:
             self._ws_crops = min(n, 256)
         return self._ws
 
-    def forward_patches(self, patches: torch.Tensor, n: int, return_hidden: bool = False):
-        """patches: layout-0 output of ops.crop_resize for n crops -> (logits [n,C] f32, top1 [n] i32)."""
+    def forward_patches(self, patches: torch.Tensor, n: int, return_hidden: bool = False,
+                        out_logits: torch.Tensor | None = None, out_top1: torch.Tensor | None = None):
+        """patches: layout-0 output of ops.crop_resize for n crops -> (logits [n,C] f32, top1 [n] i32).
+        ``out_logits`` / ``out_top1`` (contiguous, >= n rows) receive the results in place."""
         cfg = self.cfg
-        logits = torch.empty(n, cfg.num_classes, dtype=torch.float32, device=self.device)
-        top1 = torch.empty(n, dtype=torch.int32, device=self.device)
+        logits = torch.empty(n, cfg.num_classes, dtype=torch.float32, device=self.device) \
+            if out_logits is None else out_logits
+        top1 = torch.empty(n, dtype=torch.int32, device=self.device) if out_top1 is None else out_top1
         hidden = torch.empty(n, cfg.head_out, dtype=torch.float32, device=self.device) if return_hidden else None
         if n == 0:
             return (logits, top1, hidden) if return_hidden else (logits, top1)
