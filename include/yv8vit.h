@@ -199,6 +199,10 @@ int yv_prof_enable(int on);                 /* resets the counters              
 int yv_prof_kinds(void);
 const char *yv_prof_kind_name(int kind);
 int yv_prof_read(double *ms, long long *launches, double *work); /* syncs      */
+/* Debug: per-tile clock64() stamps of CTA 0 of the pipelined attention kernel
+ * (8 slots per tile, first 64 tiles).  enable=1 arms the next launches;
+ * host_out (HOST pointer, n <= 512 entries) receives the stamps; enable=0 frees. */
+int yv_debug_attn_trace(int enable, unsigned long long *host_out, int n);
 
 #ifdef __cplusplus
 }

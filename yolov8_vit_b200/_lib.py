@@ -24,7 +24,7 @@ SYMBOLS = [
     "yv_vit_create", "yv_vit_destroy", "yv_vit_set_param", "yv_vit_missing_params",
     "yv_vit_workspace_bytes", "yv_vit_forward",
     "yv_gemm_bf16", "yv_layernorm_bf16", "yv_attention_bf16", "yv_pack_results",
-    "yv_prof_enable", "yv_prof_kinds", "yv_prof_kind_name", "yv_prof_read",
+    "yv_prof_enable", "yv_prof_kinds", "yv_prof_kind_name", "yv_prof_read", "yv_debug_attn_trace",
 ]
 
 

@@ -3,7 +3,10 @@
 // timm Attention.forward (vit_base_patch{16,8}_224; reached by the reference through
 // utils/utils.py:71-72): qkv [n, T, 3, heads, 64] -> per head softmax(q k^T * 64^-0.5) v.
 //
-// Work item = (crop, head, 128-row query tile).  Two persistent CTAs per SM (84 KB of shared memory and
+// Two kernels: attention_pipe_kernel (further down; software-pipelined, used whenever two score buffers
+// fit in tensor memory, i.e. T <= 224: the ViT-B/16 case) and attention_tc_kernel below (T <= 256).
+//
+// attention_tc_kernel: work item = (crop, head, 128-row query tile).  Two persistent CTAs per SM (84 KB of shared memory and
 // 256 TMEM columns each) walk the items, so one CTA's softmax overlaps the other's MMA / TMA round
 // trips.  Per item (T <= 256 tokens, NK = T rounded up to 16 keys):
 //   TMA      Q (128 x 64), K (NK x 64), V (NK x 64) boxes straight out of the packed qkv activation
@@ -268,7 +271,345 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   if (warp == 2) tmem_dealloc(tmem_base, AT_TMEM_COLS);
 }
 
+
+// =================================================================================================
+// v3: software-pipelined variant for NK <= 224 keys (ViT-B/16: T = 197 -> NK = 208).
+//
+// One persistent CTA per SM, 24 warps.  A work unit is a (crop, head): K and V are loaded ONCE and
+// shared by its NG query tiles; the 256-row Q box covers both tiles.  Tensor memory holds TWO score
+// buffers (S0 at [0, NK), S1 at [NK, 2NK)) and a separate O accumulator at [2NK, 2NK + 64):
+//   MMA warp      S(t+1) is issued BEFORE it waits for P(t), so by the time the softmax warps finish
+//                 tile t the scores of tile t+1 are already complete -- they never wait on an MMA;
+//   softmax       16 warps = 4 lane quarters x 4 column quarters (<= 64 columns per thread); the four
+//                 threads of a row exchange their maxima through shared memory (one 128-thread named
+//                 barrier per lane quarter); partial row sums go to shared memory for the output warps;
+//                 P overwrites the head of each thread's own part of S as packed bf16 (A-from-TMEM);
+//   output        4 warps drain O after the P V MMA, normalise with the summed partial sums and store,
+//                 off the softmax warps' critical path.
+// Warps whose 32 query rows are all past T (the tail of the last tile) skip the arithmetic.
+// Measured (tools/attn_trace.py, clock64 stamps of CTA 0): the softmax warps run back to back at ~3.7k
+// cycles per tile and never wait for S; a variant with dedicated row-max warps moved the max into the
+// MMA -> max -> softmax dependency chain and was no faster, and moving half of the exp2 to an FMA-pipe
+// polynomial was slower (the warps are issue/latency-bound, the MUFU pipe is only 38 % busy).
+constexpr int AP_THREADS = 24 * 32;              // TMA, MMA, alloc, spare, 16 softmax, 4 output
+constexpr int AP_Q_BYTES = 256 * AT_DH * 2;         // 32 KB: both query tiles of a unit
+constexpr int AP_STAGE = AP_Q_BYTES + 2 * AT_KV_BYTES;   // 96 KB
+constexpr int AP_STAGES = 2;
+
+struct ApBars {
+  uint64_t qk_full[AP_STAGES], v_full[AP_STAGES], qk_empty[AP_STAGES], v_empty[AP_STAGES];
+  uint64_t s_full[2], p_full[2], o_full, o_free;
+  uint32_t tmem_slot, pad;
+  float xmax[2][4][128];      // [processed-tile parity][column quarter][row]
+  float xsum[4][4][128];      // [tile & 3][column quarter][row]: partial row sums for the output warps
+};
+constexpr int AP_SMEM = AP_STAGES * AP_STAGE + (int)sizeof(ApBars) + 1024;
+
+// first 16-key chunk of column quarter c when nch chunks are split as evenly as possible
+__device__ __forceinline__ int ap_cstart(int c, int nch) {
+  const int base = nch >> 2, rem = nch & 3;
+  return c * base + (c < rem ? c : rem);
+}
+// TMEM column (inside a score buffer) of P chunk k: quarter c keeps its packed P at the head of its S part
+__device__ __forceinline__ int ap_pcol(int k, int nch) {
+  int c = 3;
+#pragma unroll
+  for (int i = 3; i >= 1; --i)
+    if (k < ap_cstart(i, nch)) c = i - 1;
+  const int s0 = ap_cstart(c, nch);
+  return 16 * s0 + 8 * (k - s0);
+}
+
+__global__ void __launch_bounds__(AP_THREADS, 1)
+attention_pipe_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
+                      __nv_bfloat16 *__restrict__ out, int n_units, int T, int heads, float scale_log2e,
+                      unsigned long long *__restrict__ trace) {
+  // trace (debug, normally null): CTA 0 stamps clock64() per tile and role, 8 slots per tile
+#define AP_STAMP(t, e) do { if (trace && blockIdx.x == 0 && (t) < 64) trace[(t) * 8 + (e)] = clock64(); } while (0)
+  extern __shared__ __align__(1024) uint8_t ap_raw[];
+  uint8_t *smem = ap_raw;
+  if ((smem_u32(smem) & 1023u) != 0u) __trap();
+  ApBars *bar = reinterpret_cast<ApBars *>(smem + AP_STAGES * AP_STAGE);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int NK = (T + 15) & ~15;                    // <= 224
+  const int NCH = NK >> 4;
+  const int NG = (T + 127) >> 7;                    // 1 or 2 query tiles per unit
+  const int ng_sh = NG - 1;                         // NG is 1 or 2
+  const int D = heads * AT_DH;
+  const uint32_t kv_bytes = (uint32_t)NK * AT_DH * 2;
+  const uint32_t q_bytes = (uint32_t)NG * 128 * AT_DH * 2;
+  const int my_units = (n_units - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+  const int NT = my_units * NG;                     // tiles this CTA walks
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmQ);
+    prefetch_tmap(&tmKV);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < AP_STAGES; ++i) {
+      mbar_init(&bar->qk_full[i], 1);
+      mbar_init(&bar->v_full[i], 1);
+      mbar_init(&bar->qk_empty[i], 1);
+      mbar_init(&bar->v_empty[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&bar->s_full[i], 1);
+      mbar_init(&bar->p_full[i], 16);               // the 16 softmax warps
+    }
+    mbar_init(&bar->o_full, 1);
+    mbar_init(&bar->o_free, 4);                     // the 4 output warps
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(&bar->tmem_slot, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = bar->tmem_slot;
+  const uint32_t o_col = 2u * (uint32_t)NK;         // O accumulator [o_col, o_col + 64)
+
+
+  if (warp == 0) {
+    // ===================== TMA producer: one unit (Q tiles + K + V) per stage =====================
+    if (elect_one()) {
+      for (int u = 0; u < my_units; ++u) {
+        const int unit = (int)blockIdx.x + u * (int)gridDim.x;
+        const int crop = unit / heads, head = unit - crop * heads;
+        const int row0 = crop * T;
+        const int st = u & 1;
+        const uint32_t ph = (uint32_t)(u >> 1) & 1u;
+        uint8_t *sQ = smem + st * AP_STAGE, *sK = sQ + AP_Q_BYTES, *sV = sK + AT_KV_BYTES;
+        mbar_wait(&bar->qk_empty[st], ph ^ 1u);         // S MMAs of unit u-2 retired
+        mbar_arrive_expect_tx(&bar->qk_full[st], q_bytes + kv_bytes);
+        tma_load_2d(sQ, &tmQ, &bar->qk_full[st], head * AT_DH, row0);
+        tma_load_2d(sK, &tmKV, &bar->qk_full[st], D + head * AT_DH, row0);
+        mbar_wait(&bar->v_empty[st], ph ^ 1u);          // P V MMAs of unit u-2 retired
+        mbar_arrive_expect_tx(&bar->v_full[st], kv_bytes);
+        tma_load_2d(sV, &tmKV, &bar->v_full[st], 2 * D + head * AT_DH, row0);
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer: S runs one tile ahead of P V =====================
+    if (elect_one()) {
+      const uint32_t idesc_s = umma_idesc_bf16(128, NK);
+      const uint32_t idesc_o = umma_idesc_bf16_bmn(128, AT_DH);
+      auto issue_s = [&](int t) {
+        const int u = t >> ng_sh, g = t & (NG - 1), st = u & 1;
+        if (g == 0) {
+          mbar_wait(&bar->qk_full[st], (uint32_t)(u >> 1) & 1u);
+          tc_fence_after();
+        }
+        const uint32_t aQ = smem_u32(smem + st * AP_STAGE) + (uint32_t)g * AT_Q_BYTES;
+        const uint32_t aK = smem_u32(smem + st * AP_STAGE + AP_Q_BYTES);
+        const uint64_t dq = umma_desc_k_sw128(aQ), dk = umma_desc_k_sw128(aK);
+        const uint32_t d = tmem_base + (uint32_t)(t & 1) * (uint32_t)NK;
+#pragma unroll
+        for (int k = 0; k < AT_DH / 16; ++k)
+          umma_bf16(d, dq + (uint64_t)(k * 2), dk + (uint64_t)(k * 2), idesc_s, (uint32_t)(k != 0));
+        umma_commit(&bar->s_full[t & 1]);
+        if (g == NG - 1) umma_commit(&bar->qk_empty[st]);
+      };
+      if (NT > 0) issue_s(0);
+      for (int t = 0; t < NT; ++t) {
+        // buffer (t+1)&1 was last read by P V(t-1), issued earlier by this thread: in order
+        if (t + 1 < NT) issue_s(t + 1);
+        const int u = t >> ng_sh, g = t & (NG - 1), st = u & 1;
+        if (g == 0) mbar_wait(&bar->v_full[st], (uint32_t)(u >> 1) & 1u);
+        mbar_wait(&bar->p_full[t & 1], (uint32_t)(t >> 1) & 1u);
+        AP_STAMP(t, 0);
+        if (t > 0) mbar_wait(&bar->o_free, (uint32_t)(t - 1) & 1u);   // O(t-1) drained
+        tc_fence_after();
+        const uint32_t aV = smem_u32(smem + st * AP_STAGE + AP_Q_BYTES + AT_KV_BYTES);
+        const uint32_t pbase = tmem_base + (uint32_t)(t & 1) * (uint32_t)NK;
+        {
+          uint64_t dv = umma_desc_mn_sw128(aV);     // +16 keys = +2048 B = +128 in the (addr >> 4) field
+          uint32_t acc = 0;
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            const int s0 = ap_cstart(c, NCH), s1 = ap_cstart(c + 1, NCH);
+            uint32_t pc = pbase + 16u * (uint32_t)s0;
+            for (int k = s0; k < s1; ++k, pc += 8, dv += 128) {
+              umma_bf16_ts(tmem_base + o_col, pc, dv, idesc_o, acc);
+              acc = 1;
+            }
+          }
+        }
+        umma_commit(&bar->o_full);
+        if (g == NG - 1) umma_commit(&bar->v_empty[st]);
+        AP_STAMP(t, 1);
+      }
+    }
+  }
+
+  else if (warp >= 4 && warp < 20) {
+    // ===================== softmax: 4 lane quarters x 4 column quarters =====================
+    const int q = warp & 3, cq = (warp - 4) >> 2;
+    const int trow = q * 32 + lane;
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
+    const int k_lo = ap_cstart(cq, NCH), k_hi = ap_cstart(cq + 1, NCH);
+    const uint64_t sc2 = pk2(scale_log2e, scale_log2e);
+    float *xsum = &bar->xsum[0][cq][trow];
+    int np = 0;                                     // tiles this warp has processed (not skipped)
+    for (int t = 0; t < NT; ++t) {
+      const int g = t & (NG - 1);
+      const int b = t & 1;
+      const uint32_t sbuf = lane_addr + (uint32_t)b * (uint32_t)NK;
+      mbar_wait(&bar->s_full[b], (uint32_t)(t >> 1) & 1u);    // (also keeps skipping warps in step)
+      if (warp == 4 && lane == 0) AP_STAMP(t, 4);
+      if (g * 128 + q * 32 >= T) {                  // every row of this warp is padding: nothing to compute
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bar->p_full[b]);
+        continue;
+      }
+      tc_fence_after();
+      float *xm = &bar->xmax[np & 1][0][trow];      // the 4 warps of a lane quarter skip the same tiles
+      ++np;
+      // pass 1: maximum over this thread's columns (keys >= T masked)
+      float mx = -INFINITY;
+      for (int k = k_lo; k < k_hi; k += 2) {
+        uint32_t a[16], c[16];
+        const bool two = k + 1 < k_hi;
+        tmem_ld_32x16(sbuf + 16 * k, a);
+        if (two) tmem_ld_32x16(sbuf + 16 * k + 16, c);
+        tmem_ld_wait();
+        if (two && 16 * k + 32 <= T) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) mx = fmaxf(mx, fmaxf(__uint_as_float(a[j]), __uint_as_float(c[j])));
+        } else {
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            if (16 * k + j < T) mx = fmaxf(mx, __uint_as_float(a[j]));
+          if (two) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+              if (16 * k + 16 + j < T) mx = fmaxf(mx, __uint_as_float(c[j]));
+          }
+        }
+      }
+      xm[cq * 128] = mx;
+      asm volatile("bar.sync %0, 128;" ::"r"(1 + q) : "memory");
+      mx = fmaxf(fmaxf(xm[0], xm[128]), fmaxf(xm[256], xm[384]));
+      const float mneg = -mx * scale_log2e;
+      const uint64_t mn2 = pk2(mneg, mneg);
+      // pass 2: p = exp2(s * scale - max * scale); partial row sum; P -> TMEM as packed bf16 pairs behind
+      // this thread's own read pointer
+      uint64_t sum2 = pk2(0.f, 0.f);
+      uint32_t r[16];
+      if (k_lo < k_hi) tmem_ld_32x16(sbuf + 16 * k_lo, r);
+      for (int k = k_lo; k < k_hi; ++k) {
+        tmem_ld_wait();
+        float p[16];
+#pragma unroll
+        for (int j = 0; j < 16; j += 2) {
+          float x0, x1;
+          unpk2(fma2(pk2(__uint_as_float(r[j]), __uint_as_float(r[j + 1])), sc2, mn2), x0, x1);
+          p[j] = ex2_approx(x0);
+          p[j + 1] = ex2_approx(x1);
+        }
+        if (k + 1 < k_hi) tmem_ld_32x16(sbuf + 16 * (k + 1), r);
+        if (16 * k + 16 > T) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j)
+            if (16 * k + j >= T) p[j] = 0.f;
+        }
+#pragma unroll
+        for (int j = 0; j < 16; j += 4) sum2 = add2(sum2, add2(pk2(p[j], p[j + 1]), pk2(p[j + 2], p[j + 3])));
+        uint32_t w[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) w[j] = pack_bf16x2(p[2 * j], p[2 * j + 1]);
+        tmem_st_32x8(sbuf + 16 * k_lo + 8 * (k - k_lo), w);
+      }
+      float sum, sum_hi;
+      unpk2(sum2, sum, sum_hi);
+      xsum[(t & 3) * 512] = sum + sum_hi;           // partial row sum for the output warps
+      tmem_st_wait();
+      tc_fence_before();                            // P stores and S loads precede the MMA that reads P
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bar->p_full[b]);
+      if (warp == 4 && lane == 0) AP_STAMP(t, 5);
+    }
+  } else if (warp >= 20) {
+    // ===================== output: drain O, normalise, store =====================
+    const int q = warp & 3;
+    const int trow = q * 32 + lane;
+    const uint32_t o_addr = tmem_base + ((uint32_t)(q * 32) << 16) + o_col;
+    for (int t = 0; t < NT; ++t) {
+      const int u = t >> ng_sh, g = t & (NG - 1);
+      const int unit = (int)blockIdx.x + u * (int)gridDim.x;
+      const int crop = unit / heads, head = unit - crop * heads;
+      const int tok = g * 128 + trow;
+      mbar_wait_sleep(&bar->o_full, (uint32_t)t & 1u);
+      tc_fence_after();
+      if (warp == 20 && lane == 0) AP_STAMP(t, 6);
+      const bool live = g * 128 + q * 32 < T;       // warp-uniform
+      float inv = 0.f;
+      if (live) {
+        const float *xs = &bar->xsum[t & 3][0][trow];
+        inv = 1.0f / ((xs[0] + xs[128]) + (xs[256] + xs[384]));
+      }
+      auto pack8 = [&](const uint32_t *v) {
+        uint4 w;
+        w.x = pack_bf16x2(__uint_as_float(v[0]) * inv, __uint_as_float(v[1]) * inv);
+        w.y = pack_bf16x2(__uint_as_float(v[2]) * inv, __uint_as_float(v[3]) * inv);
+        w.z = pack_bf16x2(__uint_as_float(v[4]) * inv, __uint_as_float(v[5]) * inv);
+        w.w = pack_bf16x2(__uint_as_float(v[6]) * inv, __uint_as_float(v[7]) * inv);
+        return w;
+      };
+      uint4 h0[4], h1[4];
+      if (live) {
+        uint32_t o[32];
+        tmem_ld_32x32(o_addr, o);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 4; ++j) h0[j] = pack8(o + 8 * j);
+        tmem_ld_32x32(o_addr + 32, o);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 4; ++j) h1[j] = pack8(o + 8 * j);
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bar->o_free);     // the accumulator may be overwritten by P V(t+1)
+      if (warp == 20 && lane == 0) AP_STAMP(t, 7);
+      if (live && tok < T) {
+        uint4 *dst = reinterpret_cast<uint4 *>(out + ((size_t)crop * T + tok) * D + (size_t)head * AT_DH);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) dst[j] = h0[j];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) dst[4 + j] = h1[j];
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, 512);
+}
+
+
 }  // namespace
+
+// debug: per-tile clock stamps of CTA 0 (tools/attn_trace.py); off unless yv_debug_attn_trace(1, ...) was called
+static unsigned long long *g_trace = nullptr;
+
+YV_EXPORT int yv_debug_attn_trace(int enable, unsigned long long *host_out, int n) {
+  if (enable && !g_trace) {
+    YV_CUDA(cudaMalloc(&g_trace, 64 * 8 * sizeof(unsigned long long)));
+    YV_CUDA(cudaMemset(g_trace, 0, 64 * 8 * sizeof(unsigned long long)));
+  }
+  if (host_out && g_trace) {
+    YV_CUDA(cudaDeviceSynchronize());
+    YV_CUDA(cudaMemcpy(host_out, g_trace, (size_t)(n < 512 ? n : 512) * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+  }
+  if (!enable && g_trace) {
+    cudaFree(g_trace);
+    g_trace = nullptr;
+  }
+  return YV_OK;
+}
 
 int yv_attention_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, int T, int heads, int dh,
                         cudaStream_t s) {
@@ -278,22 +619,30 @@ int yv_attention_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, int
   YV_REQUIRE(((uintptr_t)qkv % 16) == 0 && ((uintptr_t)out % 16) == 0, "attention: operands must be 16-byte aligned");
   const int NK = (T + 15) & ~15, NG = (T + 127) >> 7;
   const int D = heads * AT_DH;
+  const float scale_log2e = (1.0f / sqrtf((float)dh)) * 1.4426950408889634f;
+  const bool pipelined = 2 * NK + AT_DH <= 512;     // two score buffers + O fit in tensor memory
   CUtensorMap tmQ, tmKV;
-  int rc = yv_tmap_bf16_2d(&tmQ, qkv, (uint64_t)n * T, (uint64_t)3 * D, 128);
+  int rc = yv_tmap_bf16_2d(&tmQ, qkv, (uint64_t)n * T, (uint64_t)3 * D, pipelined ? (uint32_t)(128 * NG) : 128u);
   if (rc) return rc;
   rc = yv_tmap_bf16_2d(&tmKV, qkv, (uint64_t)n * T, (uint64_t)3 * D, (uint32_t)NK);
   if (rc) return rc;
   static bool attr_set = false;
   if (!attr_set) {
     YV_CUDA(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
+    YV_CUDA(cudaFuncSetAttribute(attention_pipe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AP_SMEM));
     attr_set = true;
   }
-  const int items = n * heads * NG;
-  const int slots = 2 * yv_num_sms();               // two co-resident CTAs per SM
-  const int grid = items < slots ? items : slots;
-  const float scale_log2e = (1.0f / sqrtf((float)dh)) * 1.4426950408889634f;
   YvProf prof(YV_K_ATTN, s, 4.0 * n * heads * (double)T * T * dh);
-  attention_tc_kernel<<<grid, AT_THREADS, AT_SMEM, s>>>(tmQ, tmKV, out, items, T, heads, scale_log2e);
+  if (pipelined) {
+    const int units = n * heads;
+    const int grid = units < yv_num_sms() ? units : yv_num_sms();
+    attention_pipe_kernel<<<grid, AP_THREADS, AP_SMEM, s>>>(tmQ, tmKV, out, units, T, heads, scale_log2e, g_trace);
+  } else {
+    const int items = n * heads * NG;
+    const int slots = 2 * yv_num_sms();             // two co-resident CTAs per SM
+    const int grid = items < slots ? items : slots;
+    attention_tc_kernel<<<grid, AT_THREADS, AT_SMEM, s>>>(tmQ, tmKV, out, items, T, heads, scale_log2e);
+  }
   YV_LAUNCH_CHECK();
   return YV_OK;
 }
