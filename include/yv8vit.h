@@ -61,6 +61,28 @@ int yv_decode_filter(const float *head, int B, int nc, int A, float conf,
                      int32_t *anchors, int32_t *counts, void *ws,
                      size_t ws_bytes, yv_stream_t stream);
 
+/* --- f1: the same, starting from the Detect head's RAW output ------------------
+ * Fuses the head decode upstream of a1 (docs/YOLO_TensorRT_Technical.md:13-30
+ * make_anchors, :71-77 DFL: softmax over 16 bins x arange, anchors -/+ distances,
+ * x strides; YOLOTensorRT_yolodet_py_解读.md:64-92) into the filter kernel.
+ *   raw [B, 64+nc, A] f32: 4 x 16 DFL bin logits, then nc class LOGITS, anchors of
+ *   the 3 pyramid levels back to back (A = sum h_l*w_l), as the head's
+ *   torch.cat([x_l.view(B, no, -1)], 2) lays them out.
+ *   level_hw_host [3][2] (h, w) and level_stride_host [3] are HOST arrays.
+ *   score = sigmoid(max logit), label = first arg-max, keep iff !(score < conf);
+ *   box xyxy = ((gx+.5 - l) s, (gy+.5 - t) s, (gx+.5 + r) s, (gy+.5 + b) s).
+ * The DFL rows are read for kept anchors only.  Outputs / workspace as a1
+ * (yv_decode_filter_workspace_bytes(B, nc, A)).  Scores and boxes match the
+ * torch fp32 reference to 1e-5 relative (expf), integer outputs exactly unless a
+ * score lies within that distance of `conf`.                                    */
+int yv_decode_filter_raw(const float *raw, int B, int nc,
+                         const int32_t *level_hw_host,
+                         const float *level_stride_host, float conf,
+                         int unletterbox, float ratio, float dw, float dh,
+                         int cap, float *boxes, float *scores, int32_t *labels,
+                         int32_t *anchors, int32_t *counts, void *ws,
+                         size_t ws_bytes, yv_stream_t stream);
+
 /* --- a2: custom_nms ---------------------------------------------------------
  * Replaces custom_nms(boxes, scores, iou_threshold) (README.md:62-83 =
  * tech.md:72-93) with torchvision.ops.box_iou's fp32 arithmetic, batched:

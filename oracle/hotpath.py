@@ -71,6 +71,46 @@ def decode_head(head: torch.Tensor, conf: float = 0.35, ratio: float = 1.0,
     return boxes, scores[idx], labels[idx].to(torch.int32), idx.to(torch.int32)
 
 
+# --------------------------------------------------------------------------- f1
+def make_anchors(levels, grid_cell_offset: float = 0.5):
+    """docs/YOLO_TensorRT_Technical.md:14-29 (make_anchors) for levels [(h, w, stride)]:
+    anchor points (x + .5, y + .5) row-major per level and the stride of every anchor."""
+    pts, strides = [], []
+    for h, w, stride in levels:
+        sx = torch.arange(w, dtype=torch.float32) + grid_cell_offset
+        sy = torch.arange(h, dtype=torch.float32) + grid_cell_offset
+        sy, sx = torch.meshgrid(sy, sx, indexing="ij")
+        pts.append(torch.stack((sx, sy), -1).view(-1, 2))
+        strides.append(torch.full((h * w, 1), float(stride), dtype=torch.float32))
+    return torch.cat(pts), torch.cat(strides)
+
+
+def decode_raw_head(raw: torch.Tensor, levels, reg_max: int = 16) -> torch.Tensor:
+    """Detect-head decode of ONE image's raw output ``[4*reg_max+nc, A]`` -> ``[4+nc, A]`` with rows
+    x0,y0,x1,y1 (pixels) then sigmoid class probabilities.  Follows the reference's PyTorch form
+    (docs/YOLO_TensorRT_Technical.md:71-77): ``boxes.view(4, reg_max, A).softmax(bins) @ arange``,
+    ``anchors.repeat(2) + cat(-lt, rb)``, ``* strides``; class scores ``sigmoid``
+    (YOLOTensorRT_yolodet_py_解读.md:64-92).  fp32."""
+    raw = raw.to(torch.float32)
+    A = raw.shape[1]
+    anchors, strides = make_anchors(levels)
+    boxes = raw[:4 * reg_max].view(4, reg_max, A).permute(0, 2, 1)             # [4, A, reg_max]
+    boxes = boxes.softmax(-1) @ torch.arange(reg_max, dtype=torch.float32)     # [4, A]
+    boxes0, boxes1 = -boxes[:2], boxes[2:]
+    boxes = anchors.t().repeat(2, 1) + torch.cat([boxes0, boxes1], 0)          # x0,y0,x1,y1 in cells
+    boxes = boxes * strides.t()
+    return torch.cat([boxes, raw[4 * reg_max:].sigmoid()], 0)
+
+
+def decode_raw_filter(raw: torch.Tensor, levels, conf: float = 0.35):
+    """f1 + the a1 filter on xyxy boxes: returns boxes[K,4], scores[K], labels[K] i32, anchor_idx[K] i32."""
+    dec = decode_raw_head(raw, levels)
+    scores, labels = dec[4:].max(dim=0)
+    keep = ~(scores < torch.tensor(conf, dtype=torch.float32))
+    idx = torch.nonzero(keep).squeeze(1)
+    return dec[:4, idx].t().contiguous(), scores[idx], labels[idx].to(torch.int32), idx.to(torch.int32)
+
+
 def round_boxes(boxes: torch.Tensor) -> torch.Tensor:
     """D6: float xyxy -> round half-to-even -> int32 (解读.md:97 ``bbox.round().int()``)."""
     return torch.round(boxes).to(torch.int32)

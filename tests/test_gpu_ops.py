@@ -157,3 +157,29 @@ def test_crop_image_reference_surface():
     t = U.crop_image(img, 50, 40, 150, 120)
     x0, y0, x1, y1, ok = O.dilate_box(50, 40, 150, 120, 300, 200, 1, 10, "infer_half")
     assert np.array_equal(t.cpu().numpy(), O.crop_resize_norm(img, (x0, y0, x1, y1), 224, "nearest"))
+
+
+def test_decode_raw_head_against_oracle():
+    """Row f1: DFL + anchor decode fused into the filter kernel vs the torch fp32 restatement.
+    Integer outputs (labels, anchors, counts) exact; scores / boxes to 1e-5 relative (expf)."""
+    levels = synth.LEVELS_640
+    raw = synth.make_raw_head(5, 80, levels, n_obj=9, seed=77)
+    boxes, scores, labels, anchors, counts = [t.cpu() for t in ops.decode_filter_raw(raw.to(DEV), levels, 0.35)]
+    for b in range(5):
+        rb, rs, rl, ra = O.decode_raw_filter(raw[b], levels, 0.35)
+        n = int(counts[b])
+        assert n == len(ra) and n >= 5
+        assert anchors[b, :n].tolist() == ra.tolist() and labels[b, :n].tolist() == rl.tolist()
+        assert torch.allclose(scores[b, :n], rs, rtol=1e-5, atol=1e-6)
+        assert torch.allclose(boxes[b, :n], rb, rtol=1e-5, atol=2e-3)
+
+
+def test_decode_raw_feeds_the_same_pipeline():
+    """raw head -> f1 decode -> custom_nms gives the keep lists of the oracle chain on the same input."""
+    levels = [(8, 8, 8.0), (4, 4, 16.0), (2, 2, 32.0)]
+    raw = synth.make_raw_head(3, 5, levels, n_obj=20, seed=78)
+    cand = ops.decode_filter_raw(raw.to(DEV), levels, 0.35)
+    keep, kc = ops.nms_batched(cand[0], cand[1], cand[4], 0.45)
+    for b in range(3):
+        rb, rs, _, _ = O.decode_raw_filter(raw[b], levels, 0.35)
+        assert keep[b, :int(kc[b])].cpu().tolist() == O.custom_nms(rb, rs, 0.45)

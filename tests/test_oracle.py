@@ -149,3 +149,23 @@ def test_pipeline_cfg1_golden(golden):
     for k in ("keep", "anchor", "label", "box", "crop_box", "valid"):
         assert np.array_equal(r[k], g[k]), k
     assert len(r["keep"]) >= 6
+
+
+def test_raw_head_decode_oracle_properties():
+    """f1 oracle: uniform DFL logits -> every distance is the mean bin (7.5 cells); a one-hot bin gives that
+    bin; boxes scale with the level stride; anchors follow make_anchors (row-major, +0.5)."""
+    levels = [(4, 6, 8.0), (2, 3, 16.0), (1, 2, 32.0)]
+    A = 24 + 6 + 2
+    raw = torch.zeros(64 + 3, A)
+    raw[64:] = -5.0
+    dec = O.decode_raw_head(raw, levels)
+    pts, st = O.make_anchors(levels)
+    assert pts.shape == (A, 2) and pts[0].tolist() == [0.5, 0.5] and pts[7].tolist() == [1.5, 1.5]
+    assert torch.allclose(dec[0], (pts[:, 0] - 7.5) * st[:, 0]) and torch.allclose(dec[3], (pts[:, 1] + 7.5) * st[:, 0])
+    raw[:64] = -30.0
+    for k, bin_ in enumerate((2, 0, 5, 15)):
+        raw[k * 16 + bin_] = 30.0
+    dec = O.decode_raw_head(raw, levels)
+    a = 24 + 4                                    # level 1, cell (1, 1)
+    assert torch.allclose(dec[:4, a], torch.tensor([(1.5 - 2) * 16, (1.5 - 0) * 16, (1.5 + 5) * 16, (1.5 + 15) * 16]))
+    assert torch.allclose(dec[4:], torch.sigmoid(torch.tensor(-5.0)).expand(3, A))

@@ -40,19 +40,30 @@ struct DecodeStage {          // tile-local staging, SoA, capacity = tiles*TILE 
   unsigned *ticket;           // [B], zero before launch, reset by the last tile
 };
 
-template <int VEC>
+// Raw-head mode (row f1): the tensor is the Detect head's concatenated raw output [B, 4*16+nc, A] --
+// 4 x 16 DFL bin logits then nc class logits per anchor, anchors of the 3 levels back to back
+// (docs/YOLO_TensorRT_Technical.md:13-30 make_anchors, :71-77 DFL decode; 解读.md:64-92).
+struct RawLevels {
+  int start[3];      // first anchor of each level
+  int width[3];      // feature-map width of each level
+  float stride[3];
+};
+constexpr int DFL_BINS = 16;
+
+template <int VEC, bool RAW>
 __global__ void __launch_bounds__(DEC_NT)
 decode_filter_kernel(const float *__restrict__ head, int nc, int A, float conf, int unletterbox,
                      float ratio, float dw, float dh, int cap, DecodeStage st,
                      float4 *__restrict__ out_box, float *__restrict__ out_score,
                      int32_t *__restrict__ out_label, int32_t *__restrict__ out_anchor,
-                     int32_t *__restrict__ out_count) {
+                     int32_t *__restrict__ out_count, RawLevels lv) {
   constexpr int TILE = DEC_NT * VEC;
+  constexpr int BOXROWS = RAW ? 4 * DFL_BINS : 4;
   const int tiles = gridDim.x;
   const int tile = blockIdx.x, b = blockIdx.y;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int a0 = tile * TILE + tid * VEC;
-  const float *hp = head + (size_t)b * (size_t)(4 + nc) * (size_t)A;
+  const float *hp = head + (size_t)b * (size_t)(BOXROWS + nc) * (size_t)A;
   // VEC == 4 requires A % 4 == 0, so a thread's 4 anchors are all in range or all out.
   const bool in_range = a0 < A;
 
@@ -63,7 +74,7 @@ decode_filter_kernel(const float *__restrict__ head, int nc, int A, float conf, 
   for (int j = 0; j < VEC; ++j) { best[j] = 0.f; lab[j] = 0; }
 
   if (in_range) {
-    const float *cp = hp + (size_t)4 * A + a0;
+    const float *cp = hp + (size_t)BOXROWS * A + a0;
     {  // class 0 initialises the running max (first max wins on ties: strict > below)
       RowVec<VEC> r;
       r.load(cp);
@@ -88,8 +99,15 @@ decode_filter_kernel(const float *__restrict__ head, int nc, int A, float conf, 
       for (int j = 0; j < VEC; ++j)
         if (r.v[j] > best[j]) { best[j] = r.v[j]; lab[j] = c; }
     }
+    if (!RAW) {
 #pragma unroll
-    for (int k = 0; k < 4; ++k) bx[k].load(hp + (size_t)k * A + a0);
+      for (int k = 0; k < 4; ++k) bx[k].load(hp + (size_t)k * A + a0);
+    } else {
+      // class probabilities are sigmoid(logit): monotonic, so the arg-max is taken on the logits and only
+      // the winner is squashed (torch.sigmoid in fp32)
+#pragma unroll
+      for (int j = 0; j < VEC; ++j) best[j] = __fdiv_rn(1.0f, __fadd_rn(1.0f, expf(-best[j])));
+    }
   }
 
   // D4: keep iff not (score < conf)
@@ -126,10 +144,42 @@ decode_filter_kernel(const float *__restrict__ head, int nc, int A, float conf, 
 #pragma unroll
     for (int j = 0; j < VEC; ++j) {
       if (flags & (1u << j)) {
-        float cx = bx[0].v[j], cy = bx[1].v[j], w = bx[2].v[j], h = bx[3].v[j];
-        float hw = __fmul_rn(0.5f, w), hh = __fmul_rn(0.5f, h);
-        float x0 = __fsub_rn(cx, hw), y0 = __fsub_rn(cy, hh);
-        float x1 = __fadd_rn(cx, hw), y1 = __fadd_rn(cy, hh);
+        float x0, y0, x1, y1;
+        if (!RAW) {
+          float cx = bx[0].v[j], cy = bx[1].v[j], w = bx[2].v[j], h = bx[3].v[j];
+          float hw = __fmul_rn(0.5f, w), hh = __fmul_rn(0.5f, h);
+          x0 = __fsub_rn(cx, hw); y0 = __fsub_rn(cy, hh);
+          x1 = __fadd_rn(cx, hw); y1 = __fadd_rn(cy, hh);
+        } else {
+          // DFL only for KEPT anchors (sparse): distance = sum_i i * softmax(bins)_i per side, then
+          // (anchor -/+ distance) * stride, anchor = cell index + 0.5
+          const int a = a0 + j;
+          const int l = a >= lv.start[2] ? 2 : (a >= lv.start[1] ? 1 : 0);
+          const int cell = a - lv.start[l];
+          const int gy = cell / lv.width[l], gx = cell - gy * lv.width[l];
+          const float ax = (float)gx + 0.5f, ay = (float)gy + 0.5f, sd = lv.stride[l];
+          float d[4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            float e[DFL_BINS], m = -INFINITY;
+#pragma unroll
+            for (int i = 0; i < DFL_BINS; ++i) {
+              e[i] = __ldg(hp + (size_t)(k * DFL_BINS + i) * A + a);
+              m = fmaxf(m, e[i]);
+            }
+            float den = 0.f, num = 0.f;
+#pragma unroll
+            for (int i = 0; i < DFL_BINS; ++i) {
+              e[i] = expf(e[i] - m);
+              den += e[i];
+            }
+#pragma unroll
+            for (int i = 0; i < DFL_BINS; ++i) num = fmaf(__fdiv_rn(e[i], den), (float)i, num);
+            d[k] = num;
+          }
+          x0 = __fmul_rn(__fsub_rn(ax, d[0]), sd); y0 = __fmul_rn(__fsub_rn(ay, d[1]), sd);
+          x1 = __fmul_rn(__fadd_rn(ax, d[2]), sd); y1 = __fmul_rn(__fadd_rn(ay, d[3]), sd);
+        }
         if (unletterbox) {
           x0 = __fdiv_rn(__fsub_rn(x0, dw), ratio);
           x1 = __fdiv_rn(__fsub_rn(x1, dw), ratio);
@@ -238,12 +288,62 @@ YV_EXPORT int yv_decode_filter(const float *head, int B, int nc, int A, float co
   YV_CUDA(cudaMemsetAsync(st.ticket, 0, (size_t)B * sizeof(unsigned), s));
   dim3 grid(L.tiles, B);
   YvProf prof(YV_K_DECODE, s, (double)B * (4 + nc) * A * 4.0);
+  const RawLevels none{};
   if (L.vec == 4)
-    decode_filter_kernel<4><<<grid, DEC_NT, 0, s>>>(head, nc, A, conf, unletterbox, ratio, dw, dh, cap, st,
-                                                    (float4 *)boxes, scores, labels, anchors, counts);
+    decode_filter_kernel<4, false><<<grid, DEC_NT, 0, s>>>(head, nc, A, conf, unletterbox, ratio, dw, dh, cap, st,
+                                                           (float4 *)boxes, scores, labels, anchors, counts, none);
   else
-    decode_filter_kernel<1><<<grid, DEC_NT, 0, s>>>(head, nc, A, conf, unletterbox, ratio, dw, dh, cap, st,
-                                                    (float4 *)boxes, scores, labels, anchors, counts);
+    decode_filter_kernel<1, false><<<grid, DEC_NT, 0, s>>>(head, nc, A, conf, unletterbox, ratio, dw, dh, cap, st,
+                                                           (float4 *)boxes, scores, labels, anchors, counts, none);
+  YV_LAUNCH_CHECK();
+  return YV_OK;
+}
+
+YV_EXPORT int yv_decode_filter_raw(const float *raw, int B, int nc, const int32_t *level_hw_host,
+                                   const float *level_stride_host, float conf, int unletterbox, float ratio,
+                                   float dw, float dh, int cap, float *boxes, float *scores, int32_t *labels,
+                                   int32_t *anchors, int32_t *counts, void *ws, size_t ws_bytes,
+                                   yv_stream_t stream) {
+  YV_REQUIRE(level_hw_host && level_stride_host, "yv_decode_filter_raw: null level description");
+  RawLevels lv;
+  int A = 0;
+  for (int l = 0; l < 3; ++l) {
+    const int h = level_hw_host[2 * l], w = level_hw_host[2 * l + 1];
+    YV_REQUIRE(h >= 1 && w >= 1 && level_stride_host[l] > 0.f, "yv_decode_filter_raw: bad level %d (%d x %d)", l, h, w);
+    lv.start[l] = A;
+    lv.width[l] = w;
+    lv.stride[l] = level_stride_host[l];
+    A += h * w;
+  }
+  YV_REQUIRE(B >= 0 && nc >= 1 && cap >= 1, "yv_decode_filter_raw: bad shape B=%d nc=%d cap=%d", B, nc, cap);
+  if (B == 0) return YV_OK;
+  YV_REQUIRE(B <= 65535, "yv_decode_filter_raw: B=%d exceeds 65535 (gridDim.y)", B);
+  YV_REQUIRE(raw && boxes && scores && labels && anchors && counts && ws, "yv_decode_filter_raw: null pointer");
+  YV_REQUIRE(((uintptr_t)raw % 16) == 0 && ((uintptr_t)boxes % 16) == 0, "yv_decode_filter_raw: raw/boxes must be 16-byte aligned");
+  const DecodeLayout L = decode_layout(B, A);
+  if (ws_bytes < L.total) {
+    yv_set_error("yv_decode_filter_raw: workspace %zu < required %zu", ws_bytes, L.total);
+    return YV_ENOMEM;
+  }
+  cudaStream_t s = (cudaStream_t)stream;
+  char *w = (char *)ws;
+  DecodeStage st;
+  st.box = (float4 *)(w + L.o_box);
+  st.score = (float *)(w + L.o_score);
+  st.label = (int32_t *)(w + L.o_label);
+  st.anchor = (int32_t *)(w + L.o_anchor);
+  st.tile_count = (int32_t *)(w + L.o_tcount);
+  st.ticket = (unsigned *)(w + L.o_ticket);
+  YV_CUDA(cudaMemsetAsync(st.ticket, 0, (size_t)B * sizeof(unsigned), s));
+  dim3 grid(L.tiles, B);
+  // algorithmic bytes: the class rows of every anchor (the 64 DFL rows are read for kept anchors only)
+  YvProf prof(YV_K_DECODE, s, (double)B * nc * A * 4.0);
+  if (L.vec == 4)
+    decode_filter_kernel<4, true><<<grid, DEC_NT, 0, s>>>(raw, nc, A, conf, unletterbox, ratio, dw, dh, cap, st,
+                                                          (float4 *)boxes, scores, labels, anchors, counts, lv);
+  else
+    decode_filter_kernel<1, true><<<grid, DEC_NT, 0, s>>>(raw, nc, A, conf, unletterbox, ratio, dw, dh, cap, st,
+                                                          (float4 *)boxes, scores, labels, anchors, counts, lv);
   YV_LAUNCH_CHECK();
   return YV_OK;
 }

@@ -48,6 +48,36 @@ def decode_filter(head: torch.Tensor, conf: float = 0.35, ratio: float = 1.0, dw
     return boxes, scores, labels, anchors, counts
 
 
+def decode_filter_raw(raw: torch.Tensor, levels, conf: float = 0.35, ratio: float = 1.0, dwdh=(0.0, 0.0),
+                      cap: int | None = None):
+    """Row f1: raw Detect-head output [B, 64+nc, A] f32 (DFL bin logits + class logits) ->
+    the same outputs as :func:`decode_filter`.  ``levels`` = [(h, w, stride)] x 3."""
+    import ctypes
+    require_device(raw)
+    assert raw.dtype == torch.float32 and raw.dim() == 3 and len(levels) == 3
+    raw = raw.contiguous()
+    B, C, A = raw.shape
+    nc = C - 64
+    assert nc >= 1 and A == sum(int(h) * int(w) for h, w, _ in levels), "levels do not match the anchor count"
+    cap = A if cap is None else int(cap)
+    dev = raw.device
+    boxes = torch.empty(B, cap, 4, dtype=torch.float32, device=dev)
+    scores = torch.empty(B, cap, dtype=torch.float32, device=dev)
+    labels = torch.empty(B, cap, dtype=torch.int32, device=dev)
+    anchors = torch.empty(B, cap, dtype=torch.int32, device=dev)
+    counts = torch.empty(B, dtype=torch.int32, device=dev)
+    lib = load()
+    ws = _ws(lib.yv_decode_filter_workspace_bytes(B, nc, A), dev)
+    hw = (ctypes.c_int32 * 6)(*[int(v) for h, w, _ in levels for v in (h, w)])
+    st = (ctypes.c_float * 3)(*[float(s) for _, _, s in levels])
+    unl = int(ratio != 1.0 or dwdh[0] != 0.0 or dwdh[1] != 0.0)
+    check(lib.yv_decode_filter_raw(ptr(raw), B, nc, hw, st, float(np.float32(conf)), unl, float(np.float32(ratio)),
+                                   float(np.float32(dwdh[0])), float(np.float32(dwdh[1])), cap, ptr(boxes),
+                                   ptr(scores), ptr(labels), ptr(anchors), ptr(counts), ptr(ws), ws.numel(),
+                                   stream_ptr(dev)), "yv_decode_filter_raw")
+    return boxes, scores, labels, anchors, counts
+
+
 # ------------------------------------------------------------------------- a2
 def nms_batched(boxes: torch.Tensor, scores: torch.Tensor, counts: torch.Tensor | None = None,
                 iou_threshold: float = 0.45, max_keep: int = 0):

@@ -56,6 +56,7 @@ class HotPath:
     def __init__(self, model: ViTModel | None = None, cfg: HotPathConfig = HotPathConfig()):
         self.model = model
         self.cfg = cfg
+        self.extra_models = ()         # further classifiers of the reference's model_list (logits are summed)
         self._pin = None
 
     def detect(self, head: torch.Tensor):
@@ -66,11 +67,33 @@ class HotPath:
         keep, keep_counts = ops.nms_batched(boxes, scores, counts, c.iou, max_keep=c.max_det)
         return cand, keep, keep_counts
 
-    def __call__(self, head: torch.Tensor, images: torch.Tensor, keep_intermediates: bool = False) -> HotPathResult:
-        """head [B,4+nc,A] f32, images [B,H,W,3] u8 (both on the GPU)."""
+    def __call__(self, head: torch.Tensor, images: torch.Tensor, keep_intermediates: bool = False,
+                 levels=None) -> HotPathResult:
+        """head [B,4+nc,A] f32 (or, with ``levels`` = [(h,w,stride)]x3, the Detect head's RAW output
+        [B,64+nc,A]: row f1), images [B,H,W,3] u8 (both on the GPU)."""
+        c = self.cfg
+        if levels is None:
+            cand, keep, keep_counts = self.detect(head)
+        else:
+            cand = ops.decode_filter_raw(head, levels, c.conf, c.ratio, c.dwdh, cap=c.cand_cap)
+            keep, keep_counts = ops.nms_batched(cand[0], cand[1], cand[4], c.iou, max_keep=c.max_det)
+        return self.classify(cand, keep, keep_counts, images, keep_intermediates)
+
+    def from_candidates(self, boxes: torch.Tensor, scores: torch.Tensor, labels: torch.Tensor,
+                        counts: torch.Tensor, images: torch.Tensor, keep_intermediates: bool = False):
+        """Entry for detectors that already emit per-image candidate lists (the reference's engine with its
+        EfficientNMS plugin, test.ipynb:20-24): boxes [B,S,4] f32 xyxy in image pixels, scores [B,S] f32,
+        labels [B,S] i32, counts [B] i32 -> custom_nms -> dilation -> crop -> ViT as usual."""
+        anchors = torch.arange(scores.shape[1], dtype=torch.int32, device=scores.device).repeat(scores.shape[0], 1)
+        keep, keep_counts = ops.nms_batched(boxes, scores, counts, self.cfg.iou, max_keep=self.cfg.max_det)
+        cand = (boxes.contiguous(), scores.contiguous(), labels.contiguous(), anchors, counts)
+        return self.classify(cand, keep, keep_counts, images, keep_intermediates)
+
+    def classify(self, cand, keep, keep_counts, images: torch.Tensor, keep_intermediates: bool = False):
+        """a3..K9: crop list -> crop + resize -> ViT (ensemble: logits of ``extra_models`` are added, the
+        reference's ``for net in model_list`` loop, app.py:30-37) -> records."""
         c = self.cfg
         B, H, W, _ = images.shape
-        cand, keep, keep_counts = self.detect(head)
         boxes, scores, labels, anchors, _ = cand
         cl = ops.build_crops(boxes, scores, labels, anchors, keep, keep_counts, c.max_det, W, H, c.alpha,
                              c.dilate_mode)
@@ -81,17 +104,20 @@ class HotPath:
             if self._pin is None:
                 self._pin = torch.empty(1, dtype=torch.int32).pin_memory()
             self._pin.copy_(cl.n_crops, non_blocking=True)
-            torch.cuda.current_stream(head.device).synchronize()
+            torch.cuda.current_stream(images.device).synchronize()
             n = min(int(self._pin.item()), cl.crop_box.shape[0])
             patches = ops.crop_resize(images, cl.crop_box, cl.crop_img, n, c.interp, c.out_size,
                                       self.model.cfg.patch, "patch")
             logits, top1 = self.model.forward_patches(patches, n)
+            for m in getattr(self, "extra_models", ()):
+                logits = logits + m.forward_patches(patches, n)[0]
+            if getattr(self, "extra_models", ()) and n:
+                top1 = logits.argmax(dim=1).to(torch.int32)
         rec = ops.pack_results(cl, top1)
         r = HotPathResult(records=rec, det_count=cl.det_count, n_crops=n, logits=logits, top1=top1)
         if keep_intermediates:
             r.crops, r.keep, r.keep_counts, r.cand = cl, keep, keep_counts, cand
         return r
-
 
     # ------------------------------------------------------------------ host-buffer entry point
     def _host_state(self, head_h: torch.Tensor, imgs_h: torch.Tensor, dev, slices: int):

@@ -77,3 +77,23 @@ def make_boxes_int(C: int, H: int = 640, W: int = 640, seed: int = SEED0 + 3,
     x0 = (torch.rand(C, generator=g) * (W - w + 20) - 10).round().to(torch.int64).clamp_(0, W - 1)
     y0 = (torch.rand(C, generator=g) * (H - h + 20) - 10).round().to(torch.int64).clamp_(0, H - 1)
     return torch.stack([x0, y0, x0 + w, y0 + h], dim=1).to(torch.int32)
+
+
+LEVELS_640 = [(80, 80, 8.0), (40, 40, 16.0), (20, 20, 32.0)]       # YOLOv8 @ 640: A = 8400
+
+
+def make_raw_head(B: int, nc: int = 80, levels=LEVELS_640, n_obj: int = 8, seed: int = SEED0 + 6):
+    """Row f1 input: raw Detect-head output [B, 64+nc, A] f32 -- DFL bin logits ~ N(0, 2) and class logits
+    ~ N(-6, 1) (sigmoid << conf), with `n_obj` random anchors per image given one confident class logit
+    (pairwise-distinct values in [0, 4], away from logit(0.35))."""
+    g = torch.Generator().manual_seed(seed)
+    A = sum(h * w for h, w, _ in levels)
+    raw = torch.empty(B, 64 + nc, A, dtype=torch.float32)
+    raw[:, :64] = torch.randn(B, 64, A, generator=g) * 2.0
+    raw[:, 64:] = torch.randn(B, nc, A, generator=g) - 6.0
+    for b in range(B):
+        idx = torch.randperm(A, generator=g)[:n_obj]
+        cls = torch.randint(0, nc, (n_obj,), generator=g)
+        val = (torch.randperm(n_obj, generator=g).to(torch.float32) + 0.5) * (4.0 / n_obj)
+        raw[b, 64 + cls, idx] = val
+    return raw

@@ -130,3 +130,38 @@ def classify_crops(model_list, x):
         l = net(x)
         logits = l if logits is None else logits + l
     return logits.argmax(dim=1), logits
+
+
+def generate_annotation(folder_name, image_filename, image_path, objects_data, save_dir="train/new/"):
+    """VOC-style XML writer with the reference's tag set (utils/utils.py:133-228): <annotation> with
+    folder / filename / path / source.database / size (0, 0, 3 as upstream) / segmented, and one <object>
+    per detection carrying <sort> (label string mapped to its id), pose, truncated, difficult, bndbox.
+    Host-side result formatting (row f3).  Returns the path written (raises on I/O errors)."""
+    import os
+    import xml.etree.ElementTree as ET
+    root = ET.Element("annotation")
+    ET.SubElement(root, "folder").text = folder_name
+    ET.SubElement(root, "filename").text = image_filename
+    ET.SubElement(root, "path").text = image_path
+    ET.SubElement(ET.SubElement(root, "source"), "database").text = "Unknown"
+    size = ET.SubElement(root, "size")
+    for tag, val in (("width", "0"), ("height", "0"), ("depth", "3")):
+        ET.SubElement(size, tag).text = val
+    ET.SubElement(root, "segmented").text = "0"
+    mapping = {"good": "0", "broke": "1", "lose": "2", "loss": "2", "uncovered": "3", "circle": "4"}
+    for obj in objects_data:
+        node = ET.SubElement(root, "object")
+        v = obj["sort"]
+        ET.SubElement(node, "sort").text = str(v) if isinstance(v, int) else (
+            mapping.get(v, str(v)) if isinstance(v, str) else "unknown")
+        ET.SubElement(node, "pose").text = "Unspecified"
+        ET.SubElement(node, "truncated").text = "0"
+        ET.SubElement(node, "difficult").text = "0"
+        bb = ET.SubElement(node, "bndbox")
+        for tag in ("xmin", "ymin", "xmax", "ymax"):
+            ET.SubElement(bb, tag).text = str(obj[tag])
+    ET.indent(root, space="  ")
+    os.makedirs(save_dir, exist_ok=True)
+    path = os.path.join(save_dir, f"{os.path.splitext(image_filename)[0]}.xml")
+    ET.ElementTree(root).write(path, encoding="utf-8", xml_declaration=False)
+    return path
