@@ -83,6 +83,20 @@ int yv_decode_filter_raw(const float *raw, int B, int nc,
                          int32_t *anchors, int32_t *counts, void *ws,
                          size_t ws_bytes, yv_stream_t stream);
 
+/* --- f2: letterbox + blob of the detector input ---------------------------------
+ * The wrapper's per-image host preprocessing (YOLOTensorRT_yolodet_py_解读.md:
+ * 67-78): letterbox(bgr, (W, H)) -> cvtColor(BGR2RGB) -> blob (/255, CHW), for a
+ * batch of equally sized images.  images [B,H,W,3] u8 (swap_rb = 1 for BGR input),
+ * blob [B,3,out_h,out_w] f32.  The resize is OpenCV's 8-bit INTER_LINEAR fixed-point
+ * arithmetic, bit-exact; padding value 114.  yv_letterbox_geometry (host, no
+ * device work) returns the ratio / (dw, dh) the wrapper feeds to the un-letterbox
+ * step, the resized size and its top-left offset.                                 */
+int yv_letterbox_geometry(int H, int W, int out_h, int out_w, double *ratio,
+                          double *dw, double *dh, int32_t *unpad_wh,
+                          int32_t *left_top);
+int yv_letterbox_blob(const uint8_t *images, int B, int H, int W, int swap_rb,
+                      int out_h, int out_w, float *blob, yv_stream_t stream);
+
 /* --- a2: custom_nms ---------------------------------------------------------
  * Replaces custom_nms(boxes, scores, iou_threshold) (README.md:62-83 =
  * tech.md:72-93) with torchvision.ops.box_iou's fp32 arithmetic, batched:

@@ -111,6 +111,28 @@ def decode_raw_filter(raw: torch.Tensor, levels, conf: float = 0.35):
     return dec[:4, idx].t().contiguous(), scores[idx], labels[idx].to(torch.int32), idx.to(torch.int32)
 
 
+# --------------------------------------------------------------------------- f2
+def letterbox_blob(bgr: np.ndarray, new_shape=(640, 640), color=(114, 114, 114)):
+    """The wrapper's detector-input preprocessing of one BGR image (YOLOTensorRT_yolodet_py_解读.md:67-78;
+    letterbox as in the upstream YOLOv8-TensorRT ``models/utils.py``): resize keeping the aspect ratio with
+    cv2.INTER_LINEAR, pad to ``new_shape`` (w, h) with 114, BGR->RGB, /255, CHW.  Returns
+    (blob [1,3,H,W] f32, ratio, (dw, dh)).  cv2 itself is the arithmetic (third-party, installed 4.13)."""
+    import cv2
+    shape = bgr.shape[:2]
+    r = min(new_shape[1] / shape[0], new_shape[0] / shape[1])
+    unpad = int(round(shape[1] * r)), int(round(shape[0] * r))
+    dw, dh = (new_shape[0] - unpad[0]) / 2, (new_shape[1] - unpad[1]) / 2
+    im = bgr
+    if shape[::-1] != unpad:
+        im = cv2.resize(im, unpad, interpolation=cv2.INTER_LINEAR)
+    top, bottom = int(round(dh - 0.1)), int(round(dh + 0.1))
+    left, right = int(round(dw - 0.1)), int(round(dw + 0.1))
+    im = cv2.copyMakeBorder(im, top, bottom, left, right, cv2.BORDER_CONSTANT, value=color)
+    rgb = cv2.cvtColor(im, cv2.COLOR_BGR2RGB)
+    blob = np.ascontiguousarray(rgb.transpose(2, 0, 1)[None].astype(np.float32) / 255.0)
+    return blob, r, (dw, dh)
+
+
 def round_boxes(boxes: torch.Tensor) -> torch.Tensor:
     """D6: float xyxy -> round half-to-even -> int32 (解读.md:97 ``bbox.round().int()``)."""
     return torch.round(boxes).to(torch.int32)

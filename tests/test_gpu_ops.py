@@ -183,3 +183,19 @@ def test_decode_raw_feeds_the_same_pipeline():
     for b in range(3):
         rb, rs, _, _ = O.decode_raw_filter(raw[b], levels, 0.35)
         assert keep[b, :int(kc[b])].cpu().tolist() == O.custom_nms(rb, rs, 0.45)
+
+
+@pytest.mark.parametrize("H,W", [(640, 640), (480, 640), (1280, 960), (333, 517), (100, 100), (1080, 1920), (97, 211)])
+def test_letterbox_blob_bit_exact_vs_cv2(H, W):
+    """Row f2: GPU letterbox + BGR->RGB + /255 + CHW equals the cv2-based oracle bit for bit (8-bit INTER_LINEAR
+    fixed-point resize, 114 padding), and returns the same ratio / (dw, dh)."""
+    g = torch.Generator().manual_seed(H * 7 + W)
+    imgs = torch.randint(0, 256, (3, H, W, 3), generator=g, dtype=torch.uint8)
+    blob, ratio, dwdh = ops.letterbox_blob(imgs.to(DEV), (640, 640), bgr=True)
+    blob = blob.cpu().numpy()
+    for b in range(3):
+        ref, r, (dw, dh) = O.letterbox_blob(imgs[b].numpy(), (640, 640))
+        assert r == ratio and (dw, dh) == dwdh
+        assert np.array_equal(blob[b], ref[0]), (H, W, b, int((blob[b] != ref[0]).sum()))
+    rgb_blob, _, _ = ops.letterbox_blob(imgs.to(DEV), (640, 640), bgr=False)
+    assert np.array_equal(rgb_blob.cpu().numpy()[:, [2, 1, 0]], blob)

@@ -7,8 +7,9 @@ YOLOTensorRT_yolodet_py_解读.md:35-116), batched:
 Per image the reference does letterbox -> blob -> Engine -> det_postprocess -> un-letterbox ->
 ``score < 0.35`` filter -> custom_nms -> dilation -> crop -> transform -> model_list -> argmax, one Python
 iteration per detection.  Here the images of a call are grouped by size and every group goes through the
-CUDA hot path (:class:`yolov8_vit_b200.HotPath`) as ONE batch.  Host-side work kept as upstream: image
-decoding and the letterbox resize of the detector INPUT (row f2 of SURVEY.md §8 is a "next" row).
+CUDA hot path (:class:`yolov8_vit_b200.HotPath`) as ONE batch, including the detector-input letterbox/blob
+(row f2).  Host-side work kept as upstream: image decoding.  ``letterbox`` / ``blob`` below are the host
+helpers of the upstream wrapper, kept for callers that use them directly.
 """
 from __future__ import annotations
 
@@ -102,13 +103,11 @@ def main(Engine, imgs, device, model_list=None, transform=None, aliyunoss=None, 
     for idx, (_, bgr) in enumerate(items):
         groups.setdefault(bgr.shape[:2], []).append(idx)
     for (h0, w0), idxs in groups.items():
-        # detector input: letterbox (same ratio / padding for the whole group) -> RGB -> blob
-        blobs, ratio, dwdh = [], 1.0, (0.0, 0.0)
-        for i in idxs:
-            lb, ratio, dwdh = letterbox(items[i][1], (W_in, H_in))
-            blobs.append(blob(cv2.cvtColor(lb, cv2.COLOR_BGR2RGB)))
-        x = torch.from_numpy(np.concatenate(blobs, 0)).to(dev)
-        rgb = torch.from_numpy(np.stack([cv2.cvtColor(items[i][1], cv2.COLOR_BGR2RGB) for i in idxs])).to(dev)
+        # one upload of the group's BGR frames; detector input (letterbox -> RGB -> /255 -> CHW) on the GPU
+        # (row f2, bit-exact against the cv2 path the wrapper runs on the host)
+        bgr_d = torch.from_numpy(np.stack([items[i][1] for i in idxs])).to(dev)
+        x, ratio, dwdh = ops.letterbox_blob(bgr_d, (H_in, W_in), bgr=True)
+        rgb = bgr_d.flip(-1).contiguous()                # crop source: the reference crops the RGB PIL image
         hp = HotPath(models[0] if models else None,
                      HotPathConfig(conf=conf, iou=iou, interp=interp, ratio=float(ratio),
                                    dwdh=(float(dwdh[0]), float(dwdh[1]))))

@@ -18,7 +18,7 @@ LIB_PATH = os.path.join(_HERE, "libyv8vit.so")
 # every symbol include/yv8vit.h declares (tests check the .so exports all of them)
 SYMBOLS = [
     "yv_version", "yv_last_error", "yv_check_device",
-    "yv_decode_filter_workspace_bytes", "yv_decode_filter", "yv_decode_filter_raw",
+    "yv_decode_filter_workspace_bytes", "yv_decode_filter", "yv_decode_filter_raw", "yv_letterbox_geometry", "yv_letterbox_blob",
     "yv_nms_workspace_bytes", "yv_nms_batched",
     "yv_dilate_boxes", "yv_build_crops", "yv_crop_resize",
     "yv_vit_create", "yv_vit_destroy", "yv_vit_set_param", "yv_vit_missing_params",
@@ -61,6 +61,8 @@ def load() -> ctypes.CDLL:
     lib.yv_decode_filter_raw.argtypes = [c_void_p, c_int, c_int, c_void_p, c_void_p, c_float, c_int, c_float, c_float,
                                          c_float, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
                                          c_size_t, c_void_p]
+    lib.yv_letterbox_geometry.argtypes = [c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p]
+    lib.yv_letterbox_blob.argtypes = [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p]
     lib.yv_nms_workspace_bytes.restype = c_size_t
     lib.yv_nms_workspace_bytes.argtypes = [c_int, c_int]
     lib.yv_nms_batched.argtypes = [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_int, c_void_p,

@@ -78,6 +78,30 @@ def decode_filter_raw(raw: torch.Tensor, levels, conf: float = 0.35, ratio: floa
     return boxes, scores, labels, anchors, counts
 
 
+def letterbox_geometry(H: int, W: int, out_hw=(640, 640)):
+    """(ratio, (dw, dh), (unpad_w, unpad_h), (left, top)) of the wrapper's letterbox (host arithmetic)."""
+    import ctypes
+    r, dw, dh = ctypes.c_double(), ctypes.c_double(), ctypes.c_double()
+    un, lt = (ctypes.c_int32 * 2)(), (ctypes.c_int32 * 2)()
+    check(load().yv_letterbox_geometry(int(H), int(W), int(out_hw[0]), int(out_hw[1]), ctypes.byref(r),
+                                       ctypes.byref(dw), ctypes.byref(dh), un, lt), "yv_letterbox_geometry")
+    return r.value, (dw.value, dh.value), (un[0], un[1]), (lt[0], lt[1])
+
+
+def letterbox_blob(images: torch.Tensor, out_hw=(640, 640), bgr: bool = True):
+    """Row f2: images [B,H,W,3] u8 -> detector input blob [B,3,out_h,out_w] f32 (RGB, /255), letterboxed
+    exactly like cv2.resize(INTER_LINEAR) + copyMakeBorder(114).  Returns (blob, ratio, (dw, dh))."""
+    require_device(images)
+    assert images.dtype == torch.uint8 and images.dim() == 4 and images.shape[3] == 3
+    images = images.contiguous()
+    B, H, W, _ = images.shape
+    blob = torch.empty(B, 3, int(out_hw[0]), int(out_hw[1]), dtype=torch.float32, device=images.device)
+    check(load().yv_letterbox_blob(ptr(images), B, H, W, 1 if bgr else 0, int(out_hw[0]), int(out_hw[1]), ptr(blob),
+                                   stream_ptr(images.device)), "yv_letterbox_blob")
+    ratio, dwdh, _, _ = letterbox_geometry(H, W, out_hw)
+    return blob, ratio, dwdh
+
+
 # ------------------------------------------------------------------------- a2
 def nms_batched(boxes: torch.Tensor, scores: torch.Tensor, counts: torch.Tensor | None = None,
                 iou_threshold: float = 0.45, max_keep: int = 0):
