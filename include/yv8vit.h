@@ -115,6 +115,19 @@ int yv_nms_batched(const float *boxes, const float *scores,
                    int32_t *keep_counts, void *ws, size_t ws_bytes,
                    yv_stream_t stream);
 
+/* Same kernel with the survivor rule selectable (row f4): YV_NMS_RULE_CUSTOM is
+ * custom_nms (suppress unless iou < thr); YV_NMS_RULE_STANDARD is
+ * torchvision.ops.nms / the engine's EfficientNMS plugin (suppress iff iou > thr;
+ * docs/YOLO_TensorRT_Technical.md:108-150: iou .65, conf .25, top-100).  The
+ * class-aware form offsets the boxes per label first (torchvision batched_nms).  */
+#define YV_NMS_RULE_CUSTOM 0
+#define YV_NMS_RULE_STANDARD 1
+int yv_nms_batched_rule(const float *boxes, const float *scores,
+                        const int32_t *counts, int B, int stride, int n_all,
+                        float iou_thr, int max_keep, int rule, int32_t *keep,
+                        int32_t *keep_counts, void *ws, size_t ws_bytes,
+                        yv_stream_t stream);
+
 /* --- a3: box rounding + dilation + clamp -----------------------------------
  * README.md:86-124 in the integer form of utils/trainClass.py:76-91.
  * d = ((max-min)*num)/den (floor), mode 1 ("infer_half") halves it again;

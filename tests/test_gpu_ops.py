@@ -199,3 +199,26 @@ def test_letterbox_blob_bit_exact_vs_cv2(H, W):
         assert np.array_equal(blob[b], ref[0]), (H, W, b, int((blob[b] != ref[0]).sum()))
     rgb_blob, _, _ = ops.letterbox_blob(imgs.to(DEV), (640, 640), bgr=False)
     assert np.array_equal(rgb_blob.cpu().numpy()[:, [2, 1, 0]], blob)
+
+
+@pytest.mark.parametrize("thr", [0.65, 0.5])
+def test_efficient_nms_equals_torchvision_batched_nms(thr):
+    """Row f4: class-aware standard NMS (iou > thr suppresses, top-100) vs torchvision.ops.batched_nms."""
+    import torchvision
+    g = torch.Generator().manual_seed(11)
+    B, N = 6, 900
+    c = torch.rand(B, N, 2, generator=g) * 300
+    wh = torch.rand(B, N, 2, generator=g) * 80 + 10
+    boxes = torch.cat([c - wh / 2, c + wh / 2], 2)
+    scores = torch.stack([synth.distinct_scores(N, N, g, 0.0, 1.0) for _ in range(B)])
+    labels = torch.randint(0, 5, (B, N), generator=g, dtype=torch.int32)
+    keep, kc = ops.efficient_nms(boxes.to(DEV), scores.to(DEV), labels.to(DEV), None, thr, 100)
+    for b in range(B):
+        ref = torchvision.ops.batched_nms(boxes[b], scores[b], labels[b].long(), thr)[:100]
+        assert keep[b, :int(kc[b])].cpu().tolist() == ref.tolist(), b
+    # class-agnostic standard rule = torchvision.ops.nms, including an IoU == thr pair (kept under this rule)
+    bx = torch.tensor([[0., 0, 2, 2], [0, 0, 2, 1], [5, 5, 6, 6]]); sc = torch.tensor([.9, .8, .7])
+    k, n = ops.nms_batched(bx[None].to(DEV), sc[None].to(DEV), None, 0.5, 0, rule="standard")
+    assert k[0, :int(n[0])].cpu().tolist() == torchvision.ops.nms(bx, sc, 0.5).tolist() == [0, 1, 2]
+    k, n = ops.nms_batched(bx[None].to(DEV), sc[None].to(DEV), None, 0.5, 0)          # custom_nms suppresses equality
+    assert k[0, :int(n[0])].cpu().tolist() == [0, 2]

@@ -34,8 +34,9 @@ __device__ __forceinline__ float min_t(float a, float b) {
 __device__ __forceinline__ float area_of(const float4 &p) {
   return __fmul_rn(__fsub_rn(p.z, p.x), __fsub_rn(p.w, p.y));
 }
-// true iff box q is SUPPRESSED by kept box p: not (iou(p, q) < thr)
-__device__ __forceinline__ bool suppresses(const float4 &p, float area_p, const float4 &q, float thr) {
+// true iff box q is SUPPRESSED by kept box p.  rule 0 (custom_nms, README.md:77-79): not (iou < thr);
+// rule 1 (torchvision.ops.nms / EfficientNMS, row f4): iou > thr (equality and NaN are kept).
+__device__ __forceinline__ bool suppresses(const float4 &p, float area_p, const float4 &q, float thr, int rule = 0) {
   float area_q = area_of(q);
   float w = __fsub_rn(min_t(p.z, q.z), max_t(p.x, q.x));
   float h = __fsub_rn(min_t(p.w, q.w), max_t(p.y, q.y));
@@ -44,7 +45,7 @@ __device__ __forceinline__ bool suppresses(const float4 &p, float area_p, const 
   float inter = __fmul_rn(w, h);
   float uni = __fsub_rn(__fadd_rn(area_p, area_q), inter);
   float iou = __fdiv_rn(inter, uni);
-  return !(iou < thr);
+  return rule ? (iou > thr) : !(iou < thr);
 }
 
 __device__ __forceinline__ unsigned score_key_desc(float s) {
@@ -64,7 +65,7 @@ struct NmsWs {
 __global__ void __launch_bounds__(NMS_T)
 nms_kernel(const float4 *__restrict__ boxes, const float *__restrict__ scores,
            const int32_t *__restrict__ counts, int stride, int n_all, float thr, int max_keep,
-           int32_t *__restrict__ keep, int32_t *__restrict__ keep_counts, NmsWs ws) {
+           int32_t *__restrict__ keep, int32_t *__restrict__ keep_counts, NmsWs ws, int rule) {
   const int b = blockIdx.x;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   int n = counts ? counts[b] : n_all;
@@ -203,7 +204,7 @@ nms_kernel(const float4 *__restrict__ boxes, const float *__restrict__ scores,
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
           const int c = part * 8 + j;
-          if (c > r && c < hb && suppresses(p, ap, s_hbox[c], thr)) bits |= 1ull << c;
+          if (c > r && c < hb && suppresses(p, ap, s_hbox[c], thr, rule)) bits |= 1ull << c;
         }
       }
       bits |= __shfl_xor_sync(0xffffffffu, bits, 1);
@@ -250,7 +251,7 @@ nms_kernel(const float4 *__restrict__ boxes, const float *__restrict__ scores,
       if (live) {
         const float4 q = lb[i];
         for (int t = 0; t < k; ++t)
-          if (suppresses(s_kbox[t], s_karea[t], q, thr)) { live = false; break; }
+          if (suppresses(s_kbox[t], s_karea[t], q, thr, rule)) { live = false; break; }
       }
       const unsigned bal = __ballot_sync(0xffffffffu, live);
       if (lane == 0) s_ballot[warp][it] = bal;
@@ -305,9 +306,10 @@ YV_EXPORT size_t yv_nms_workspace_bytes(int B, int stride) {
   return nms_layout(B, stride).total;
 }
 
-YV_EXPORT int yv_nms_batched(const float *boxes, const float *scores, const int32_t *counts, int B,
-                             int stride, int n_all, float iou_thr, int max_keep, int32_t *keep,
-                             int32_t *keep_counts, void *ws, size_t ws_bytes, yv_stream_t stream) {
+YV_EXPORT int yv_nms_batched_rule(const float *boxes, const float *scores, const int32_t *counts, int B,
+                                  int stride, int n_all, float iou_thr, int max_keep, int rule, int32_t *keep,
+                                  int32_t *keep_counts, void *ws, size_t ws_bytes, yv_stream_t stream) {
+  YV_REQUIRE(rule == 0 || rule == 1, "yv_nms_batched: unknown rule %d", rule);
   YV_REQUIRE(B >= 0 && stride >= 1, "yv_nms_batched: bad shape B=%d stride=%d", B, stride);
   if (B == 0) return YV_OK;
   YV_REQUIRE(boxes && scores && keep && keep_counts && ws, "yv_nms_batched: null pointer");
@@ -329,7 +331,14 @@ YV_EXPORT int yv_nms_batched(const float *boxes, const float *scores, const int3
   }
   YvProf prof(YV_K_NMS, (cudaStream_t)stream, counts ? 0.0 : (double)B * n_all * 20.0);
   nms_kernel<<<B, NMS_T, 0, (cudaStream_t)stream>>>((const float4 *)boxes, scores, counts, stride, n_all,
-                                                    iou_thr, max_keep, keep, keep_counts, W);
+                                                    iou_thr, max_keep, keep, keep_counts, W, rule);
   YV_LAUNCH_CHECK();
   return YV_OK;
+}
+
+YV_EXPORT int yv_nms_batched(const float *boxes, const float *scores, const int32_t *counts, int B,
+                             int stride, int n_all, float iou_thr, int max_keep, int32_t *keep,
+                             int32_t *keep_counts, void *ws, size_t ws_bytes, yv_stream_t stream) {
+  return yv_nms_batched_rule(boxes, scores, counts, B, stride, n_all, iou_thr, max_keep, YV_NMS_RULE_CUSTOM, keep,
+                             keep_counts, ws, ws_bytes, stream);
 }

@@ -104,7 +104,7 @@ def letterbox_blob(images: torch.Tensor, out_hw=(640, 640), bgr: bool = True):
 
 # ------------------------------------------------------------------------- a2
 def nms_batched(boxes: torch.Tensor, scores: torch.Tensor, counts: torch.Tensor | None = None,
-                iou_threshold: float = 0.45, max_keep: int = 0):
+                iou_threshold: float = 0.45, max_keep: int = 0, rule: str = "custom"):
     """boxes [B,S,4] f32, scores [B,S] f32, counts [B] i32 (or None = all S) ->
     keep [B,S] i32 (original indices, descending score), keep_counts [B] i32."""
     require_device(boxes)
@@ -120,10 +120,24 @@ def nms_batched(boxes: torch.Tensor, scores: torch.Tensor, counts: torch.Tensor 
     ws = _ws(lib.yv_nms_workspace_bytes(B, S), dev)
     if counts is not None:
         assert counts.dtype == torch.int32 and counts.is_cuda
-    check(lib.yv_nms_batched(ptr(boxes), ptr(scores), ptr(counts), B, S, S, float(np.float32(iou_threshold)),
-                             int(max_keep), ptr(keep), ptr(keep_counts), ptr(ws), ws.numel(), stream_ptr(dev)),
-          "yv_nms_batched")
+    check(lib.yv_nms_batched_rule(ptr(boxes), ptr(scores), ptr(counts), B, S, S, float(np.float32(iou_threshold)),
+                                  int(max_keep), {"custom": 0, "standard": 1}[rule], ptr(keep), ptr(keep_counts),
+                                  ptr(ws), ws.numel(), stream_ptr(dev)), "yv_nms_batched")
     return keep, keep_counts
+
+
+def efficient_nms(boxes: torch.Tensor, scores: torch.Tensor, labels: torch.Tensor, counts: torch.Tensor | None = None,
+                  iou_threshold: float = 0.65, max_det: int = 100):
+    """Row f4: the engine's class-aware EfficientNMS stage (iou .65, top-100;
+    docs/YOLO_TensorRT_Technical.md:108-150) = torchvision.ops.batched_nms per image: boxes of different
+    classes never suppress each other (coordinate offset label * (max + 1), as torchvision does), survivor
+    rule ``iou > thr`` suppresses.  boxes [B,S,4], scores [B,S], labels [B,S] -> keep [B,S] i32, counts [B]."""
+    require_device(boxes)
+    mx = boxes.amax(dim=(1, 2), keepdim=True) if counts is None else boxes.masked_fill(
+        (torch.arange(boxes.shape[1], device=boxes.device)[None] >= counts[:, None])[..., None], float("-inf")
+    ).amax(dim=(1, 2), keepdim=True)
+    off = labels.to(boxes.dtype)[..., None] * (mx + 1)
+    return nms_batched(boxes + off, scores, counts, iou_threshold, max_det, rule="standard")
 
 
 # ------------------------------------------------------------------------- a3
