@@ -27,7 +27,7 @@ def test_layernorm():
     assert float((got - ref).abs().max()) <= 2 ** -7 * float(ref.abs().max())
 
 
-@pytest.mark.parametrize("n,T", [(3, 197), (2, 64), (2, 5), (1, 256)])
+@pytest.mark.parametrize("n,T", [(3, 197), (2, 64), (2, 5), (1, 256), (2, 785), (1, 300)])
 def test_attention(n, T):
     heads, dh = 12, 64
     qkv = (torch.randn(n, T, 3 * heads * dh) * 0.7).to(torch.bfloat16)
@@ -148,3 +148,16 @@ def test_run_host_no_detections(full_model):
     imgs = synth.make_images(4, 640, 640, seed=33)
     r = HotPath(m, HotPathConfig()).run_host(head, imgs, device=DEV, slices=2)
     assert r.n_crops == 0 and float(r.records[..., 7].sum()) == 0.0
+
+
+def test_vit_b8_reference_literal_model():
+    """Row f4: the reference-literal vit_base_patch8_224 shape (785 tokens, utils/class_config.py:21) runs end to
+    end (patch-8 crop layout, K = 192 patch-embed GEMM, long-sequence attention); 2 blocks vs the oracle."""
+    cfg = O.ViTConfig(patch=8, depth=2)
+    sd = O.make_vit_weights(cfg, seed=9)
+    m = ViTModel(ViTConfig(patch=8, depth=2), DEV).load_state_dict(sd)
+    x = torch.randn(3, 3, 224, 224, generator=torch.Generator().manual_seed(3)).clamp_(-1, 1)
+    ref = O.vit_forward(sd, x, cfg)
+    got = m(x.to(DEV)).cpu()
+    assert rel_err(got, ref) <= REL_TOL
+    assert got.argmax(1).tolist() == ref.argmax(1).tolist()

@@ -1,13 +1,15 @@
-// attention.cu -- K7: softmax(Q K^T / sqrt(dh)) V for one (crop, head) per CTA.
+// attention.cu -- K7 for LONG sequences (T > 256: ViT-B/8's 785 tokens, row f4): softmax(Q K^T / sqrt(dh)) V.
 //
-// timm Attention.forward (vit_base_patch{16,8}_224; the arithmetic the reference reaches through
-// utils/utils.py:71-72): qkv [n, T, 3, heads, dh] -> per head softmax(q k^T * dh^-0.5) v.
+// timm Attention.forward (vit_base_patch8_224, the reference-literal model of utils/class_config.py:21):
+// qkv [n, T, 3, heads, dh] -> per head softmax(q k^T * dh^-0.5) v.
 //
-// First tensor-core version: mma.sync.m16n8k16 (bf16 x bf16 -> f32) fed by ldmatrix from padded
-// shared memory; one warp owns 16 query rows, walks the keys in blocks of 64 with the online
-// softmax recurrence (running max / sum in registers, exp2 domain), P stays in registers as the
-// A operand of P.V.  Q, K, V of the head are staged once per CTA with 16-byte loads.
-// dh == 64, T <= 256 (ViT-B/16: T = 197 -> 13 warps, 4 key blocks).
+// mma.sync.m16n8k16 (bf16 x bf16 -> f32) flash-style kernel: a CTA owns up to 256 query rows of one
+// (crop, head) -- one warp per 16 rows, Q fragments in registers -- and walks ALL keys in blocks of 64 with
+// the online-softmax recurrence (running max / sum in registers, exp2 domain); every K / V block is staged
+// through padded shared memory (ldmatrix conflict-free), P stays in registers as the A operand of P V.
+// 55 KB of shared memory per CTA -> several CTAs per SM hide the staging.  T <= 256 never comes here: the
+// tcgen05 kernels of attention_sm100.cu handle it.  This is the functional path for the reference-literal
+// B/8 model; a tcgen05 multi-block variant is the "next" item of DESIGN.md.
 #include "common.cuh"
 #include "vit_ops.cuh"
 
@@ -38,39 +40,29 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   return *reinterpret_cast<uint32_t *>(&h);
 }
 
-__global__ void __launch_bounds__(512, 1)
-attention_kernel(const __nv_bfloat16 *__restrict__ qkv, __nv_bfloat16 *__restrict__ out, int T, int heads,
-                 float scale_log2e) {
+__global__ void __launch_bounds__(512)
+attention_long_kernel(const __nv_bfloat16 *__restrict__ qkv, __nv_bfloat16 *__restrict__ out, int T, int heads,
+                      float scale_log2e) {
   extern __shared__ __align__(16) uint8_t att_smem[];
-  const int nw = blockDim.x >> 5;                 // = ceil(T / 16)
+  const int nw = blockDim.x >> 5;                 // warps = 16-row query groups of this CTA
   const int nkb = (T + ATT_KB - 1) / ATT_KB;
-  const int qrows = nw * 16, krows = nkb * ATT_KB;
+  const int qrows = nw * 16;
   __nv_bfloat16 *Qs = reinterpret_cast<__nv_bfloat16 *>(att_smem);
-  __nv_bfloat16 *Ks = Qs + (size_t)qrows * ATT_LD;
-  __nv_bfloat16 *Vs = Ks + (size_t)krows * ATT_LD;
+  __nv_bfloat16 *Ks = Qs + (size_t)qrows * ATT_LD;          // one 64-key block
+  __nv_bfloat16 *Vs = Ks + (size_t)ATT_KB * ATT_LD;
 
-  const int head = blockIdx.x, crop = blockIdx.y;
+  const int head = blockIdx.x, crop = blockIdx.y, q0 = blockIdx.z * 256;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int D = heads * ATT_DH;
   const __nv_bfloat16 *base = qkv + (size_t)crop * T * 3 * D + (size_t)head * ATT_DH;
 
-  // stage Q | K | V: 8 x 16-byte chunks per (row, matrix); padded rows are zero
+  // stage this CTA's Q rows: 8 x 16-byte chunks per row; rows past T are zero
   const uint4 zero = make_uint4(0u, 0u, 0u, 0u);
   for (int i = tid; i < qrows * 8; i += blockDim.x) {
     const int r = i >> 3, c = i & 7;
     uint4 v = zero;
-    if (r < T) v = *reinterpret_cast<const uint4 *>(base + (size_t)r * 3 * D + c * 8);
+    if (q0 + r < T) v = *reinterpret_cast<const uint4 *>(base + (size_t)(q0 + r) * 3 * D + c * 8);
     *reinterpret_cast<uint4 *>(Qs + (size_t)r * ATT_LD + c * 8) = v;
-  }
-  for (int i = tid; i < krows * 8; i += blockDim.x) {
-    const int r = i >> 3, c = i & 7;
-    uint4 k = zero, v = zero;
-    if (r < T) {
-      k = *reinterpret_cast<const uint4 *>(base + (size_t)r * 3 * D + D + c * 8);
-      v = *reinterpret_cast<const uint4 *>(base + (size_t)r * 3 * D + 2 * D + c * 8);
-    }
-    *reinterpret_cast<uint4 *>(Ks + (size_t)r * ATT_LD + c * 8) = k;
-    *reinterpret_cast<uint4 *>(Vs + (size_t)r * ATT_LD + c * 8) = v;
   }
   __syncthreads();
 
@@ -89,10 +81,22 @@ attention_kernel(const __nv_bfloat16 *__restrict__ qkv, __nv_bfloat16 *__restric
   float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
 
   for (int kb = 0; kb < nkb; ++kb) {
+    __syncthreads();                              // the previous block's K / V are no longer read
+    for (int i = tid; i < ATT_KB * 8; i += blockDim.x) {
+      const int r = i >> 3, c = i & 7, key = kb * ATT_KB + r;
+      uint4 k = zero, v = zero;
+      if (key < T) {
+        k = *reinterpret_cast<const uint4 *>(base + (size_t)key * 3 * D + D + c * 8);
+        v = *reinterpret_cast<const uint4 *>(base + (size_t)key * 3 * D + 2 * D + c * 8);
+      }
+      *reinterpret_cast<uint4 *>(Ks + (size_t)r * ATT_LD + c * 8) = k;
+      *reinterpret_cast<uint4 *>(Vs + (size_t)r * ATT_LD + c * 8) = v;
+    }
+    __syncthreads();
     float s[8][4];
 #pragma unroll
     for (int j = 0; j < 8; ++j) { s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f; }
-    const __nv_bfloat16 *Kb = Ks + (size_t)kb * ATT_KB * ATT_LD;
+    const __nv_bfloat16 *Kb = Ks;
 #pragma unroll
     for (int ks = 0; ks < 4; ++ks) {
 #pragma unroll
@@ -145,7 +149,7 @@ attention_kernel(const __nv_bfloat16 *__restrict__ qkv, __nv_bfloat16 *__restric
       o[j][2] *= corr1; o[j][3] *= corr1;
     }
     // O += P V
-    const __nv_bfloat16 *Vb = Vs + (size_t)kb * ATT_KB * ATT_LD;
+    const __nv_bfloat16 *Vb = Vs;
 #pragma unroll
     for (int t = 0; t < 4; ++t) {               // k16 steps over the 64 keys of the block
       uint32_t pf[4];
@@ -171,7 +175,7 @@ attention_kernel(const __nv_bfloat16 *__restrict__ qkv, __nv_bfloat16 *__restric
   l1 += __shfl_xor_sync(0xffffffffu, l1, 1);
   l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
   const float inv0 = 1.f / l0, inv1 = 1.f / l1;
-  const int r0 = warp * 16 + (lane >> 2), r1 = r0 + 8;
+  const int r0 = q0 + warp * 16 + (lane >> 2), r1 = r0 + 8;
   __nv_bfloat16 *ob = out + (size_t)crop * T * D + (size_t)head * ATT_DH + (lane & 3) * 2;
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
@@ -182,27 +186,23 @@ attention_kernel(const __nv_bfloat16 *__restrict__ qkv, __nv_bfloat16 *__restric
 
 }  // namespace
 
-int yv_attention_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, int T, int heads, int dh,
-                        cudaStream_t s) {
+int yv_attention_long_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, int T, int heads, int dh,
+                             cudaStream_t s) {
   YV_REQUIRE(dh == ATT_DH, "attention: head dim %d unsupported (need %d)", dh, ATT_DH);
   YV_REQUIRE(n >= 1 && n <= 65535 && heads >= 1 && T >= 1, "attention: bad shape");
-  const int nw = (T + 15) / 16, nkb = (T + ATT_KB - 1) / ATT_KB;
-  YV_REQUIRE(nw <= 16, "attention: T=%d exceeds 256 tokens (needs the multi-block variant)", T);
-  const size_t smem = (size_t)(nw * 16 + 2 * nkb * ATT_KB) * ATT_LD * sizeof(__nv_bfloat16);
+  const int qblocks = (T + 255) / 256;
+  const int rows = T < 256 ? T : 256;
+  const int nw = (rows + 15) / 16;
+  const size_t smem = (size_t)(nw * 16 + 2 * ATT_KB) * ATT_LD * sizeof(__nv_bfloat16);
   static bool attr_set = false;
   if (!attr_set) {
-    YV_CUDA(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    YV_CUDA(cudaFuncSetAttribute(attention_long_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
     attr_set = true;
   }
-  dim3 grid(heads, n);
+  dim3 grid(heads, n, qblocks);
   const float scale_log2e = (1.0f / sqrtf((float)dh)) * 1.4426950408889634f;
   YvProf prof(YV_K_ATTN, s, 4.0 * n * heads * (double)T * T * dh);
-  attention_kernel<<<grid, nw * 32, smem, s>>>(qkv, out, T, heads, scale_log2e);
+  attention_long_kernel<<<grid, nw * 32, smem, s>>>(qkv, out, T, heads, scale_log2e);
   YV_LAUNCH_CHECK();
   return YV_OK;
-}
-
-YV_EXPORT int yv_attention_bf16(const void *qkv, void *out, int n, int T, int heads, int dh, yv_stream_t stream) {
-  YV_REQUIRE(qkv && out, "yv_attention_bf16: null pointer");
-  return yv_attention_launch((const __nv_bfloat16 *)qkv, (__nv_bfloat16 *)out, n, T, heads, dh, (cudaStream_t)stream);
 }

@@ -620,7 +620,7 @@ int yv_attention_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, int
                         cudaStream_t s) {
   YV_REQUIRE(dh == AT_DH, "attention: head dim %d unsupported (need %d)", dh, AT_DH);
   YV_REQUIRE(n >= 1 && heads >= 1 && T >= 1, "attention: bad shape");
-  YV_REQUIRE(T <= 256, "attention: T=%d exceeds 256 tokens (ViT-B/8's 785 tokens need the multi-block variant)", T);
+  if (T > 256) return yv_attention_long_launch(qkv, out, n, T, heads, dh, s);   // ViT-B/8: mma.sync multi-block path
   YV_REQUIRE(((uintptr_t)qkv % 16) == 0 && ((uintptr_t)out % 16) == 0, "attention: operands must be 16-byte aligned");
   const int NK = (T + 15) & ~15, NG = (T + 127) >> 7;
   const int D = heads * AT_DH;

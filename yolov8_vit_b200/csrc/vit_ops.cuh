@@ -13,9 +13,12 @@ int yv_ln_launch(const void *x, bool x_f32, size_t in_stride, const __nv_bfloat1
                  cudaStream_t s);
 
 // softmax(Q K^T / sqrt(dh)) V; qkv [n*T, 3*heads*dh] bf16 (timm packing: q | k | v, head-major),
-// out [n*T, heads*dh] bf16.  dh == 64, T <= 256.
+// out [n*T, heads*dh] bf16.  dh == 64.  T <= 256: tcgen05 kernels (attention_sm100.cu); longer sequences
+// (ViT-B/8) are forwarded to the mma.sync multi-block kernel of attention.cu.
 int yv_attention_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, int T, int heads, int dh,
                         cudaStream_t s);
+int yv_attention_long_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, int T, int heads, int dh,
+                             cudaStream_t s);
 
 // x32[c*T, :] = cls + pos[0]  (the class-token row of every crop)
 int yv_cls_rows_launch(float *x32, const float *cls_pos0, int n, int T, int dim, cudaStream_t s);
