@@ -161,3 +161,31 @@ def test_vit_b8_reference_literal_model():
     got = m(x.to(DEV)).cpu()
     assert rel_err(got, ref) <= REL_TOL
     assert got.argmax(1).tolist() == ref.argmax(1).tolist()
+
+
+def test_fused_layernorm_pipeline_parity(golden):
+    """The folded-LayerNorm pipeline (YV_VIT_FUSED_LN=1: LN folded into the qkv / fc1 GEMM epilogues, residual add +
+    row statistics in the proj / fc2 epilogues) is EXPERIMENTAL and off by default: feeding the raw bf16 residual
+    stream to the tensor cores (instead of the normalised rows) roughly doubles the logit error, so it is held to
+    2e-2 + identical top-1 here, not to the product bar of 1e-2.  The switch is read once per process, so this
+    runs in a child process."""
+    import os, subprocess, sys
+    code = r"""
+import sys, torch
+sys.path.insert(0, %r)
+from oracle import hotpath as O
+from yolov8_vit_b200 import ViTConfig, ViTModel
+cfg = O.ViTConfig(depth=3)
+sd = O.make_vit_weights(cfg, seed=12)
+m = ViTModel(ViTConfig(depth=3), 'cuda:0').load_state_dict(sd)
+x = torch.randn(37, 3, 224, 224, generator=torch.Generator().manual_seed(4)).clamp_(-1, 1)
+ref = O.vit_forward(sd, x, cfg)
+got = m(x.cuda()).cpu()
+err = float((got - ref).abs().max() / ref.abs().max())
+assert err <= 2e-2, err
+assert got.argmax(1).tolist() == ref.argmax(1).tolist()
+print('fused ok', err)
+""" % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, YV_VIT_FUSED_LN="1")
+    r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=280)
+    assert r.returncode == 0 and "fused ok" in r.stdout, r.stdout + r.stderr

@@ -67,9 +67,11 @@ __device__ __forceinline__ void gelu4(float4 &v) {
   gelu2(v.z, v.w);
 }
 
-// GELU / OUT_F32 select the epilogue arithmetic at compile time; EXTRA compiles in the rarely used
-// position-table (patch embedding) and residual operands.
-template <bool GELU, bool OUT_F32, bool EXTRA>
+// GELU / OUT_F32 select the epilogue arithmetic at compile time; MODE 1 compiles in the rarely used
+// position-table (patch embedding) and residual operands, MODE 2 the folded LayerNorm (row statistics +
+// column sums), MODE 3 the fused residual update (fp32 stream read-modify-write + bf16 copy + row statistics).
+constexpr int EPI_PLAIN = 0, EPI_EXTRA = 1, EPI_LNFOLD = 2, EPI_RESID = 3;
+template <bool GELU, bool OUT_F32, int MODE>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const GemmEpilogue ep, int M, int N, int K) {
@@ -188,12 +190,56 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         rok[i] = row < M;
         long long drow = row;
         pos_row[i] = nullptr;
-        if (EXTRA && ep.group_rows > 0) {          // patch-embed: token row = r + r/196 + 1, + pos[1 + r%196]
+        if (MODE == EPI_EXTRA && ep.group_rows > 0) {          // patch-embed: token row = r + r/196 + 1, + pos[1 + r%196]
           const int g = row / ep.group_rows;
           drow = (long long)row + g + 1;
           pos_row[i] = ep.pos + (size_t)(row - g * ep.group_rows + 1) * N;
         }
         obase[i] = (size_t)drow * N + colw;
+      }
+      // folded LayerNorm: per-row (mu, rstd) from the producer's (sum, sum of squares); per-column sums
+      float ln_mu[4], ln_rstd[4];
+      float4 s4[MODE == EPI_LNFOLD ? NCH : 1];
+      if (MODE == EPI_LNFOLD) {
+        const float invd = 1.0f / (float)ep.ln_dim;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int row = m0 + q * 32 + i * 8 + trow;
+          float2 st = make_float2(0.f, 0.f);
+          if (rok[i]) {                            // fixed-order sum of the producer's per-column-block partials
+            const float2 *sp = reinterpret_cast<const float2 *>(ep.row_stats) + (size_t)row * ep.ln_slots;
+            float2 t[8];                           // all loads in flight at once (ln_slots <= 8)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) t[j] = j < ep.ln_slots ? __ldg(sp + j) : make_float2(0.f, 0.f);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { st.x += t[j].x; st.y += t[j].y; }
+          }
+          ln_mu[i] = st.x * invd;
+          ln_rstd[i] = rsqrtf(fmaxf(st.y * invd - ln_mu[i] * ln_mu[i], 0.f) + ep.ln_eps);
+        }
+#pragma unroll
+        for (int ch = 0; ch < NCH; ++ch) {
+          s4[ch] = make_float4(0.f, 0.f, 0.f, 0.f);
+          if (colw + ch * 16 < N) s4[ch] = __ldg(reinterpret_cast<const float4 *>(ep.col_s + colw + ch * 16));
+        }
+      }
+      float rs_sum[4] = {0.f, 0.f, 0.f, 0.f}, rs_sq[4] = {0.f, 0.f, 0.f, 0.f};   // MODE 3 row statistics
+      float4 xres[4];                              // MODE 3: residual-stream values of the current chunk
+      if (MODE == EPI_RESID) {
+        // pull this tile's part of the fp32 residual stream towards L2 while the MMAs of the tile run (one
+        // 128-byte line = 2 chunks of a row; the lane with tseg == 0 speaks for its row group) ...
+        if (tseg == 0) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            if (rok[i])
+#pragma unroll
+              for (int ch = 0; ch < NCH; ch += 2)
+                if (colw + ch * 16 < N) asm volatile("prefetch.global.L2 [%0];" ::"l"(ep.x32 + obase[i] + ch * 16));
+        }
+        // ... and load chunk 0 before waiting for the accumulator
+#pragma unroll
+        for (int i = 0; i < 4; ++i)
+          xres[i] = (rok[i] && colw < N) ? *reinterpret_cast<const float4 *>(ep.x32 + obase[i]) : make_float4(0.f, 0.f, 0.f, 0.f);
       }
       mbar_wait(&tfull[as], aph);
       tc_fence_after();
@@ -213,16 +259,39 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
         if (ch + 1 < NCH) tmem_ld_32x16(tbase + (ch + 1) * 16, r);
         __syncwarp();
+        float4 xnext[4];                           // MODE 3: next chunk's residual values, loaded one chunk ahead
+        if (MODE == EPI_RESID) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i)
+            xnext[i] = (ch + 1 < NCH && rok[i] && colw + (ch + 1) * 16 < N)
+                           ? *reinterpret_cast<const float4 *>(ep.x32 + obase[i] + (ch + 1) * 16)
+                           : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
         if (colw + ch * 16 < N) {
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
             const int rr = i * 8 + trow;
             float4 v = *reinterpret_cast<const float4 *>(stg + rr * 16 + ((tseg ^ ((rr >> 1) & 3)) << 2));
             if (!rok[i]) continue;
-            v.x += bias4[ch].x; v.y += bias4[ch].y; v.z += bias4[ch].z; v.w += bias4[ch].w;
+            if (MODE == EPI_LNFOLD) {
+              const float nm = -ln_mu[i], rs = ln_rstd[i];
+              v.x = fmaf(rs, fmaf(nm, s4[ch].x, v.x), bias4[ch].x);
+              v.y = fmaf(rs, fmaf(nm, s4[ch].y, v.y), bias4[ch].y);
+              v.z = fmaf(rs, fmaf(nm, s4[ch].z, v.z), bias4[ch].z);
+              v.w = fmaf(rs, fmaf(nm, s4[ch].w, v.w), bias4[ch].w);
+            } else {
+              v.x += bias4[ch].x; v.y += bias4[ch].y; v.z += bias4[ch].z; v.w += bias4[ch].w;
+            }
             if (GELU) gelu4(v);
             const size_t o = obase[i] + ch * 16;
-            if (EXTRA) {
+            if (MODE == EPI_RESID) {
+              const float4 x = xres[i];
+              v.x += x.x; v.y += x.y; v.z += x.z; v.w += x.w;
+              *reinterpret_cast<float4 *>(ep.x32 + o) = v;
+              rs_sum[i] += (v.x + v.y) + (v.z + v.w);
+              rs_sq[i] += (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
+            }
+            if (MODE == EPI_EXTRA) {
               if (pos_row[i]) {
                 const float4 p = __ldg(reinterpret_cast<const float4 *>(pos_row[i] + colw + ch * 16));
                 v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w;
@@ -250,7 +319,24 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             }
           }
         }
+        if (MODE == EPI_RESID) {
+#pragma unroll
+          for (int i = 0; i < 4; ++i) xres[i] = xnext[i];
+        }
         __syncwarp();
+      }
+      if (MODE == EPI_RESID) {
+        // the 4 lanes of a row group (tseg) hold partial sums of the same rows: reduce, one atomic per row
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          float a = rs_sum[i], b = rs_sq[i];
+          a += __shfl_xor_sync(0xffffffffu, a, 1); b += __shfl_xor_sync(0xffffffffu, b, 1);
+          a += __shfl_xor_sync(0xffffffffu, a, 2); b += __shfl_xor_sync(0xffffffffu, b, 2);
+          if (tseg == 0 && rok[i]) {               // one slot per 128-column block: deterministic, no atomics
+            const int slot = (n0 >> 7) + half;
+            reinterpret_cast<float2 *>(ep.stats_out)[(size_t)(m0 + q * 32 + i * 8 + trow) * (N >> 7) + slot] = make_float2(a, b);
+          }
+        }
       }
       tc_fence_before();
       __syncwarp();
@@ -290,8 +376,9 @@ void init_once() {
   if (e == cudaSuccess)                                                                                     \
     e = cudaFuncSetAttribute(gemm_bf16_kernel<G, F, X>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
   e = cudaSuccess;
-  YV_SET(false, false, false) YV_SET(false, false, true) YV_SET(false, true, false) YV_SET(false, true, true)
-  YV_SET(true, false, false) YV_SET(true, false, true) YV_SET(true, true, false) YV_SET(true, true, true)
+  YV_SET(false, false, 0) YV_SET(false, false, 1) YV_SET(false, true, 0) YV_SET(false, true, 1)
+  YV_SET(true, false, 0) YV_SET(true, false, 1) YV_SET(true, true, 0) YV_SET(true, true, 1)
+  YV_SET(false, false, 2) YV_SET(true, false, 2) YV_SET(false, false, 3)
 #undef YV_SET
   if (e != cudaSuccess) {
     g_init_status = yv_cuda_fail(e, "cudaFuncSetAttribute(gemm smem)", __FILE__, __LINE__);
@@ -344,13 +431,23 @@ int yv_gemm_launch(const void *A, const void *W, int M, int N, int K, const Gemm
   const int grid = 2 * (tiles < pairs ? tiles : pairs);
   YvProf prof(YV_K_GEMM, s, 2.0 * M * (double)N * K);
   const bool extra = ep.group_rows > 0 || ep.residual != nullptr;
+  const bool lnfold = ep.row_stats != nullptr, resid = ep.x32 != nullptr;
+  YV_REQUIRE(!(lnfold && (extra || resid || ep.out_f32)) && !(resid && (extra || ep.gelu || ep.out_f32)),
+             "yv_gemm: unsupported epilogue combination");
+  YV_REQUIRE(!lnfold || (ep.col_s && ep.ln_dim > 0), "yv_gemm: folded LayerNorm needs col_s and ln_dim");
+  YV_REQUIRE(!lnfold || ep.ln_slots >= 1, "yv_gemm: folded LayerNorm needs ln_slots >= 1");
+  YV_REQUIRE(!resid || (ep.stats_out && N % 128 == 0), "yv_gemm: fused residual needs stats_out and N %% 128 == 0");
 #define YV_GO(G, F, X) gemm_bf16_kernel<G, F, X><<<grid, GEMM_THREADS, SMEM_BYTES, s>>>(tmA, tmB, ep, M, N, K)
-  if (ep.gelu) {
-    if (ep.out_f32) { if (extra) YV_GO(true, true, true); else YV_GO(true, true, false); }
-    else { if (extra) YV_GO(true, false, true); else YV_GO(true, false, false); }
+  if (lnfold) {
+    if (ep.gelu) YV_GO(true, false, 2); else YV_GO(false, false, 2);
+  } else if (resid) {
+    YV_GO(false, false, 3);
+  } else if (ep.gelu) {
+    if (ep.out_f32) { if (extra) YV_GO(true, true, 1); else YV_GO(true, true, 0); }
+    else { if (extra) YV_GO(true, false, 1); else YV_GO(true, false, 0); }
   } else {
-    if (ep.out_f32) { if (extra) YV_GO(false, true, true); else YV_GO(false, true, false); }
-    else { if (extra) YV_GO(false, false, true); else YV_GO(false, false, false); }
+    if (ep.out_f32) { if (extra) YV_GO(false, true, 1); else YV_GO(false, true, 0); }
+    else { if (extra) YV_GO(false, false, 1); else YV_GO(false, false, 0); }
   }
 #undef YV_GO
   YV_LAUNCH_CHECK();

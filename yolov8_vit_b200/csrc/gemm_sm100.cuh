@@ -14,6 +14,19 @@ struct GemmEpilogue {
   bool gelu;
   bool out_f32;
   bool res_f32;
+  // LayerNorm folded into the GEMM (mode 2): A holds the RAW bf16 residual stream x, W = g (.) W_orig,
+  // D = rstd_m * (acc - mu_m * col_s[n]) + bias[n]  with  bias = b . W_orig^T + bias_orig,  col_s[n] = sum_k W[n,k],
+  // (mu_m, rstd_m) from row_stats[m][0..ln_slots) = partial (sum_k x, sum_k x^2) over ln_dim features.
+  const float *row_stats = nullptr;
+  const float *col_s = nullptr;
+  int ln_dim = 0;
+  int ln_slots = 0;
+  float ln_eps = 0.f;
+  // Residual update fused into the producer GEMM (mode 3): x32[m, n] += acc + bias (fp32, in place),
+  // out = bf16(x32) and stats_out[m][n / 128] = (sum, sum of squares) of the new entries of that 128-column
+  // block (one slot per block: deterministic, nothing to zero).  null = off.
+  float *x32 = nullptr;
+  float *stats_out = nullptr;
 };
 
 // D = A[M,K] * W[N,K]^T with the epilogue above.  K % 64 == 0, N % 8 == 0.

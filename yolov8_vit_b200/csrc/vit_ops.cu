@@ -168,6 +168,85 @@ int yv_ln_launch(const void *x, bool x_f32, size_t in_stride, const __nv_bfloat1
   return YV_OK;
 }
 
+namespace {
+
+// xb = bf16(x32) and the one-pass row statistics (sum, sum of squares) in slot 0 of stats[row][slots]
+// (the other slots are zeroed): the first LayerNorm of a chunk in the folded-LayerNorm pipeline.
+__global__ void __launch_bounds__(LN_WARPS * 32)
+row_stats_kernel(const float *__restrict__ x32, __nv_bfloat16 *__restrict__ xb, float2 *__restrict__ stats, int slots,
+                 int rows, int dim) {
+  const int lane = threadIdx.x & 31;
+  const int row = blockIdx.x * LN_WARPS + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  float sum = 0.f, sq = 0.f;
+  for (int e = lane * 8; e < dim; e += 256) {
+    const float4 *p = reinterpret_cast<const float4 *>(x32 + (size_t)row * dim + e);
+    const float4 a = p[0], b = p[1];
+    sum += ((a.x + a.y) + (a.z + a.w)) + ((b.x + b.y) + (b.z + b.w));
+    sq += ((a.x * a.x + a.y * a.y) + (a.z * a.z + a.w * a.w)) + ((b.x * b.x + b.y * b.y) + (b.z * b.z + b.w * b.w));
+    __nv_bfloat162 h[4] = {__floats2bfloat162_rn(a.x, a.y), __floats2bfloat162_rn(a.z, a.w),
+                           __floats2bfloat162_rn(b.x, b.y), __floats2bfloat162_rn(b.z, b.w)};
+    *reinterpret_cast<uint4 *>(xb + (size_t)row * dim + e) = *reinterpret_cast<const uint4 *>(h);
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    sum += __shfl_xor_sync(0xffffffffu, sum, d);
+    sq += __shfl_xor_sync(0xffffffffu, sq, d);
+  }
+  if (lane < slots) stats[(size_t)row * slots + lane] = lane == 0 ? make_float2(sum, sq) : make_float2(0.f, 0.f);
+}
+
+// Folds a LayerNorm's affine part into the following Linear (one block per output feature n):
+//   wf[n, k] = bf16(g[k] * w[n, k]),  colsum[n] = sum_k wf[n, k],  cf[n] = bias[n] + sum_k beta[k] * w[n, k]
+// so that Linear(LN(x)) = rstd * (x . wf^T - mu * colsum) + cf.
+__global__ void __launch_bounds__(256)
+fold_ln_kernel(const __nv_bfloat16 *__restrict__ w, const float *__restrict__ bias, const float *__restrict__ g,
+               const float *__restrict__ beta, int K, __nv_bfloat16 *__restrict__ wf, float *__restrict__ colsum,
+               float *__restrict__ cf) {
+  const int n = blockIdx.x;
+  float s = 0.f, c = 0.f;
+  for (int k = threadIdx.x; k < K; k += 256) {
+    const float wv = __bfloat162float(w[(size_t)n * K + k]);
+    const __nv_bfloat16 f = __float2bfloat16_rn(g[k] * wv);
+    wf[(size_t)n * K + k] = f;
+    s += __bfloat162float(f);
+    c += beta[k] * wv;
+  }
+  __shared__ float sh[2][8];
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, d);
+    c += __shfl_xor_sync(0xffffffffu, c, d);
+  }
+  if ((threadIdx.x & 31) == 0) { sh[0][threadIdx.x >> 5] = s; sh[1][threadIdx.x >> 5] = c; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float ts = 0.f, tc = 0.f;
+    for (int i = 0; i < 8; ++i) { ts += sh[0][i]; tc += sh[1][i]; }
+    colsum[n] = ts;
+    cf[n] = bias[n] + tc;
+  }
+}
+
+}  // namespace
+
+int yv_row_stats_launch(const float *x32, __nv_bfloat16 *xb, float *stats, int slots, int rows, int dim, cudaStream_t s) {
+  YV_REQUIRE(dim % 8 == 0 && slots >= 1 && slots <= 32, "row_stats: dim=%d slots=%d unsupported", dim, slots);
+  const int grid = (rows + LN_WARPS - 1) / LN_WARPS;
+  YvProf prof(YV_K_LN, s, (double)rows * dim * 6.0);
+  row_stats_kernel<<<grid, LN_WARPS * 32, 0, s>>>(x32, xb, reinterpret_cast<float2 *>(stats), slots, rows, dim);
+  YV_LAUNCH_CHECK();
+  return YV_OK;
+}
+
+int yv_fold_ln_launch(const __nv_bfloat16 *w, const float *bias, const float *g, const float *beta, int N, int K,
+                      __nv_bfloat16 *wf, float *colsum, float *cf, cudaStream_t s) {
+  YvProf prof(YV_K_MISC, s, 0.0);
+  fold_ln_kernel<<<N, 256, 0, s>>>(w, bias, g, beta, K, wf, colsum, cf);
+  YV_LAUNCH_CHECK();
+  return YV_OK;
+}
+
 int yv_cls_rows_launch(float *x32, const float *cls_pos0, int n, int T, int dim, cudaStream_t s) {
   const int total = n * dim;
   YvProf prof(YV_K_MISC, s, 0.0);

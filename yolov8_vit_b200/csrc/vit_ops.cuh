@@ -20,6 +20,12 @@ int yv_attention_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, int
 int yv_attention_long_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, int T, int heads, int dh,
                              cudaStream_t s);
 
+// Folded-LayerNorm pipeline: xb = bf16(x32) + one-pass row statistics in slot 0 of
+// stats[rows][slots][2]; and the one-off weight fold wf = g (.) w, colsum, cf = bias + beta . w^T.
+int yv_row_stats_launch(const float *x32, __nv_bfloat16 *xb, float *stats, int slots, int rows, int dim, cudaStream_t s);
+int yv_fold_ln_launch(const __nv_bfloat16 *w, const float *bias, const float *g, const float *beta, int N, int K,
+                      __nv_bfloat16 *wf, float *colsum, float *cf, cudaStream_t s);
+
 // x32[c*T, :] = cls + pos[0]  (the class-token row of every crop)
 int yv_cls_rows_launch(float *x32, const float *cls_pos0, int n, int T, int dim, cudaStream_t s);
 
