@@ -19,6 +19,7 @@
 #include "gemm_sm100.cuh"
 #include "sm100_ptx.cuh"
 
+#include <cstdlib>
 #include <mutex>
 
 using namespace sm100;
@@ -42,25 +43,26 @@ constexpr int BAR_BYTES = 256;          // mbarriers + TMEM slot
 constexpr int EPI_BYTES = NUM_EPI_WARPS * 32 * 16 * 4;   // per warp: 32 rows x 16 fp32, XOR-swizzled 16-byte segments
 constexpr size_t SMEM_BYTES = (size_t)STAGES * STAGE_BYTES + 1024 /*align slack*/ + BAR_BYTES + EPI_BYTES;
 
-// erf-GELU, x * Phi(x), with erf(z) ~ z * P(z^2) on |z| <= 3 (degree-8 minimax fit, clamped beyond):
-// |gelu error| < 6e-5 absolute for every x (well under the bf16 rounding of the stored result),
-// ~9 issue slots per element with packed fp32x2 FMAs and no MUFU -- erff() costs ~30 issue slots per element, which made the
-// K=768 fc1 GEMM epilogue-bound (one 128x256 tile has only 6144 MMA cycles).
-// Packed fp32x2 arithmetic (sm_100: one FFMA2 / FMUL2 does two lanes) halves the GELU issue cost.
+// GELU in the epilogue.  The reference's nn.GELU is the erf form x * Phi(x); the first version evaluated it with
+// a degree-8 minimax polynomial for erf (|error| < 6e-5, ~10 issue slots per element), which cost 45 us of the
+// 197 us fc1 GEMM (K = 768: the epilogue is the critical path; measured with YV_GEMM_DBG).  This version uses
+// the tanh form 0.5 x (1 + tanh(sqrt(2/pi) (x + 0.044715 x^3))) on the MUFU pipe: 5 packed fp32x2 operations
+// + 2 MUFU.TANH per PAIR.  |tanh form - erf form| <= 4.8e-4 absolute (rms 1.8e-4 for N(0, 1.5) inputs) and
+// tanh.approx adds <= 2^-11 relative -- both several times below the bf16 rounding of the stored value (rms
+// 1.7e-3 on the same inputs); the ViT goldens (1e-2 relative on the logits, identical top-1) cover it.
+__device__ __forceinline__ float tanh_approx(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ void gelu2(float &a, float &b) {
-  const float k = 0.70710678118654752440f;
-  const float za = fminf(fmaxf(a * k, -3.0f), 3.0f), zb = fminf(fmaxf(b * k, -3.0f), 3.0f);
-  const uint64_t z = pk2(za, zb), z2 = mul2(z, z);
-  uint64_t p = fma2(pk2(4.074204153e-08f, 4.074204153e-08f), z2, pk2(-1.944820304e-06f, -1.944820304e-06f));
-  p = fma2(p, z2, pk2(4.106048667e-05f, 4.106048667e-05f));
-  p = fma2(p, z2, pk2(-5.110365571e-04f, -5.110365571e-04f));
-  p = fma2(p, z2, pk2(4.235425968e-03f, 4.235425968e-03f));
-  p = fma2(p, z2, pk2(-2.510285741e-02f, -2.510285741e-02f));
-  p = fma2(p, z2, pk2(1.110793300e-01f, 1.110793300e-01f));
-  p = fma2(p, z2, pk2(-3.753148727e-01f, -3.753148727e-01f));
-  p = fma2(p, z2, pk2(1.128268428e+00f, 1.128268428e+00f));
-  const uint64_t t = fma2(mul2(z, pk2(0.5f, 0.5f)), p, pk2(0.5f, 0.5f));
-  unpk2(mul2(pk2(a, b), t), a, b);
+  const uint64_t x = pk2(a, b);
+  const uint64_t p = fma2(mul2(x, x), pk2(0.0356774081f, 0.0356774081f), pk2(0.7978845608f, 0.7978845608f));
+  float u0, u1;
+  unpk2(mul2(p, x), u0, u1);
+  const uint64_t t = pk2(tanh_approx(u0), tanh_approx(u1));
+  const uint64_t hx = mul2(x, pk2(0.5f, 0.5f));
+  unpk2(fma2(hx, t, hx), a, b);
 }
 __device__ __forceinline__ void gelu4(float4 &v) {
   gelu2(v.x, v.y);
@@ -245,9 +247,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       tc_fence_after();
       const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + half * (BN / 2);
       uint32_t r[16];
-      tmem_ld_32x16(tbase, r);
+      if (ep.dbg != 2) tmem_ld_32x16(tbase, r);
 #pragma unroll
       for (int ch = 0; ch < NCH; ++ch) {
+        if (ep.dbg == 2) break;
         tmem_ld_wait();
         {
           float4 *srow = reinterpret_cast<float4 *>(stg + lane * 16);
@@ -308,6 +311,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                 }
               }
             }
+            if (ep.dbg == 1 && v.x != 12345.678f) continue;      // keeps the arithmetic alive, drops the stores
             if (OUT_F32) {
               *reinterpret_cast<float4 *>((float *)ep.out + o) = v;
             } else {
@@ -430,6 +434,8 @@ int yv_gemm_launch(const void *A, const void *W, int M, int N, int K, const Gemm
   const int pairs = yv_num_sms() / 2;
   const int grid = 2 * (tiles < pairs ? tiles : pairs);
   YvProf prof(YV_K_GEMM, s, 2.0 * M * (double)N * K);
+  static const int dbg = []() { const char *e = getenv("YV_GEMM_DBG"); return e ? atoi(e) : 0; }();
+  const_cast<GemmEpilogue &>(ep).dbg = dbg;
   const bool extra = ep.group_rows > 0 || ep.residual != nullptr;
   const bool lnfold = ep.row_stats != nullptr, resid = ep.x32 != nullptr;
   YV_REQUIRE(!(lnfold && (extra || resid || ep.out_f32)) && !(resid && (extra || ep.gelu || ep.out_f32)),

@@ -27,6 +27,7 @@ struct GemmEpilogue {
   // block (one slot per block: deterministic, nothing to zero).  null = off.
   float *x32 = nullptr;
   float *stats_out = nullptr;
+  int dbg = 0;                      // measurement only (YV_GEMM_DBG): 1 = no global stores, 2 = no epilogue work
 };
 
 // D = A[M,K] * W[N,K]^T with the epilogue above.  K % 64 == 0, N % 8 == 0.
