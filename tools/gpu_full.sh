@@ -1,7 +1,7 @@
 #!/bin/bash
 # full pass: GPU parity tests, smoke, both bench arms, ncu launch list, full captures of the GEMM and attention kernels
 mkdir -p gpurun_out
-for f in test_gpu_ops test_gpu_gemm test_gpu_vit; do
+for f in test_gpu_ops test_gpu_gemm test_gpu_vit test_wrapper; do
   timeout 600 python -m pytest tests/$f.py -q -m gpu --timeout=300 -p no:cacheprovider > gpurun_out/$f.log 2>&1
   echo "$f exit $?"; tail -n 4 gpurun_out/$f.log
 done
