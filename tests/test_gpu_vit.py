@@ -189,3 +189,20 @@ print('fused ok', err)
     env = dict(os.environ, YV_VIT_FUSED_LN="1")
     r = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True, timeout=280)
     assert r.returncode == 0 and "fused ok" in r.stdout, r.stdout + r.stderr
+
+
+def test_submit_host_pipelined_batches(full_model):
+    """Two batches in flight (submit k+1 before result k, alternating staging slots) give each batch exactly the
+    records of its own resident run; a third submit reuses slot 0 safely."""
+    m, _ = full_model
+    hp = HotPath(m, HotPathConfig())
+    batches = [(synth.make_head(6, 80, 8400, n_obj=3, n_jit=12, seed=40 + i).pin_memory(),
+                synth.make_images(6, 640, 640, seed=50 + i).pin_memory()) for i in range(3)]
+    refs = [hp(h.to(DEV), im.to(DEV)).records.cpu() for h, im in batches]
+    outs = [torch.empty(6, 100, 8).pin_memory() for _ in range(3)]
+    pend = hp.submit_host(*batches[0], outs[0], device=DEV, slices=3)
+    for k in range(3):
+        nxt = hp.submit_host(*batches[k + 1], outs[k + 1], device=DEV, slices=3) if k < 2 else None
+        r = pend.result()
+        assert torch.equal(outs[k], refs[k]) and torch.equal(r.records.cpu(), refs[k]), k
+        pend = nxt

@@ -119,20 +119,23 @@ class HotPath:
             r.crops, r.keep, r.keep_counts, r.cand = cl, keep, keep_counts, cand
         return r
 
-    # ------------------------------------------------------------------ host-buffer entry point
-    def _host_state(self, head_h: torch.Tensor, imgs_h: torch.Tensor, dev, slices: int):
+    # ------------------------------------------------------------------ host-buffer entry points
+    def _host_state(self, head_h: torch.Tensor, imgs_h: torch.Tensor, dev, slices: int, slot: int):
         key = (tuple(head_h.shape), tuple(imgs_h.shape), str(dev), slices)
-        st = getattr(self, "_hs", None)
-        if st is None or st["key"] != key:
-            st = {"key": key,
-                  "head": torch.empty(head_h.shape, dtype=torch.float32, device=dev),
+        sets = getattr(self, "_hs", None)
+        if sets is None or sets["key"] != key:
+            sets = {"key": key, "front": torch.cuda.Stream(device=dev, priority=-1), "slots": {}, "next": 0}
+            self._hs = sets
+        st = sets["slots"].get(slot)
+        if st is None:
+            st = {"head": torch.empty(head_h.shape, dtype=torch.float32, device=dev),
                   "imgs": torch.empty(imgs_h.shape, dtype=torch.uint8, device=dev),
                   "pin": torch.empty(slices, dtype=torch.int32).pin_memory(),
-                  "front": torch.cuda.Stream(device=dev, priority=-1),
                   "events": [torch.cuda.Event() for _ in range(slices)],
+                  "free": None,                # recorded on the caller's stream when the slot's buffers are no longer read
                   "patches": None, "top1": None, "logits": None, "cap": 0}
-            self._hs = st
-        return st
+            sets["slots"][slot] = st
+        return sets, st
 
     def _grow(self, st, need: int, used: int, dev):
         """Crop-indexed buffers (patches, logits, top1) with geometric growth; `used` crops are preserved."""
@@ -150,33 +153,32 @@ class HotPath:
             new[2][:used].copy_(st["top1"][:used])
         st["patches"], st["logits"], st["top1"], st["cap"] = new[0], new[1], new[2], cap
 
-    def run_host(self, head_h: torch.Tensor, imgs_h: torch.Tensor, out_records_h: torch.Tensor | None = None,
-                 device="cuda:0", slices: int = 8, vit_chunk: int = 256) -> HotPathResult:
-        """The same path from HOST buffers (pinned memory recommended): head [B,4+nc,A] f32 and images
-        [B,H,W,3] u8 on the CPU -> records on the CPU (`out_records_h`, pinned, optional).
-
-        The batch is cut into `slices` image slices.  A high-priority "front" stream uploads slice
-        after slice and runs decode -> custom_nms -> crop list on each as soon as it has landed; the
-        caller's stream gathers the crops of every finished slice into one patch buffer and runs
-        the ViT over fixed `vit_chunk`-crop chunks as soon as enough crops exist, so the upload of
-        slice i+1.. overlaps the ViT of slice ..i.  Host syncs: one 4-byte crop count per slice
-        (it sizes the ViT launches) and the final record download.  Not re-entrant per instance
-        (it owns staging buffers); use one HotPath per thread.
-        """
+    def submit_host(self, head_h: torch.Tensor, imgs_h: torch.Tensor, out_records_h: torch.Tensor | None = None,
+                    device="cuda:0", slices: int = 8, vit_chunk: int = 256, ramp=()) -> "PendingHost":
+        """Asynchronous half of :meth:`run_host`: enqueues the sliced upload and the per-slice decode ->
+        custom_nms -> crop list on the high-priority front stream and returns at once.  ``.result()`` of the
+        returned handle runs the ViT part and delivers the records.  Two staging slots alternate, so a server
+        loop ``nxt = submit_host(batch i+1); cur.result(); cur = nxt`` uploads batch i+1 while batch i is in the
+        ViT -- the end-to-end rate then equals the resident rate (bench.py's `e2e`)."""
         if self.model is None:
-            raise ValueError("run_host needs a classifier")
+            raise ValueError("the host-buffer path needs a classifier")
         if head_h.is_cuda or imgs_h.is_cuda:
-            raise ValueError("run_host takes host tensors; call the instance for device-resident inputs")
+            raise ValueError("submit_host / run_host take host tensors; call the instance for device-resident inputs")
         c = self.cfg
         dev = torch.device(device)
         B, H, W, _ = imgs_h.shape
         slices = max(1, min(slices, B))
-        st = self._host_state(head_h, imgs_h, dev, slices)
-        main = torch.cuda.current_stream(dev)
-        front = st["front"]
+        sets = getattr(self, "_hs", None)
+        slot = 0 if sets is None else sets.get("next", 0)
+        sets, st = self._host_state(head_h, imgs_h, dev, slices, slot)
+        sets["next"] = slot ^ 1
+        front = sets["front"]
         bounds = [(B * i) // slices for i in range(slices + 1)]
-        front.wait_stream(main)            # staging buffers of the previous call are no longer read
-        cls, dets = [], []
+        if st["free"] is not None:
+            front.wait_event(st["free"])       # the previous user of this slot no longer reads its buffers
+        else:
+            front.wait_stream(torch.cuda.current_stream(dev))
+        cls = []
         with torch.cuda.stream(front):
             for i in range(slices):
                 a, b = bounds[i], bounds[i + 1]
@@ -190,17 +192,56 @@ class HotPath:
                 st["pin"][i:i + 1].copy_(cl.n_crops, non_blocking=True)
                 st["events"][i].record(front)
                 cls.append(cl)
-                dets.append((cand, keep, keep_counts))
+        return PendingHost(self, st, cls, bounds, dev, out_records_h, vit_chunk, ramp, front)
+
+    def run_host(self, head_h: torch.Tensor, imgs_h: torch.Tensor, out_records_h: torch.Tensor | None = None,
+                 device="cuda:0", slices: int = 8, vit_chunk: int = 256, ramp=()) -> HotPathResult:
+        """The same path from HOST buffers (pinned memory recommended): head [B,4+nc,A] f32 and images
+        [B,H,W,3] u8 on the CPU -> records on the CPU (`out_records_h`, pinned, optional).
+
+        The batch is cut into `slices` image slices.  A high-priority "front" stream uploads slice
+        after slice and runs decode -> custom_nms -> crop list on each as soon as it has landed; the
+        caller's stream gathers the crops of every finished slice into one patch buffer and runs
+        the ViT over fixed `vit_chunk`-crop chunks as soon as enough crops exist, so the upload of
+        slice i+1.. overlaps the ViT of slice ..i (`ramp` = smaller first chunks, e.g. (64, 128); measured
+        not to pay off: small chunks run the GEMMs at half efficiency).  Host syncs: one 4-byte crop count per
+        slice (it sizes the ViT launches) and the final record download.  = submit_host(...).result().
+        Not re-entrant per instance (it owns staging buffers); use one HotPath per thread.
+        """
+        return self.submit_host(head_h, imgs_h, out_records_h, device, slices, vit_chunk, ramp).result()
+
+
+class PendingHost:
+    """Handle of :meth:`HotPath.submit_host`: the upload + detection of the batch are in flight."""
+
+    def __init__(self, hp, st, cls, bounds, dev, out_records_h, vit_chunk, ramp, front):
+        self.hp, self.st, self.cls, self.bounds, self.dev = hp, st, cls, bounds, dev
+        self.out_records_h, self.vit_chunk, self.ramp, self.front = out_records_h, vit_chunk, ramp, front
+        self._res = None
+
+    def result(self) -> HotPathResult:
+        if self._res is not None:
+            return self._res
+        hp, st, cls, bounds, dev = self.hp, self.st, self.cls, self.bounds, self.dev
+        c, model, vit_chunk = hp.cfg, hp.model, self.vit_chunk
+        slices, B = len(cls), bounds[-1]
+        main = torch.cuda.current_stream(dev)
         total = done = 0
         offs = []
-        g = (c.out_size // self.model.cfg.patch) ** 2
+        g = (c.out_size // model.cfg.patch) ** 2
+        sizes = [int(r) for r in self.ramp if 0 < int(r) < vit_chunk]
+        launched = 0
+
+        def next_chunk():
+            return sizes[launched] if launched < len(sizes) else vit_chunk
 
         def vit(upto):
-            nonlocal done
+            nonlocal done, launched
             while done < upto:
-                n = min(vit_chunk, upto - done)
-                self.model.forward_patches(st["patches"][done * g:(done + n) * g], n,
-                                           out_logits=st["logits"][done:done + n], out_top1=st["top1"][done:done + n])
+                n = min(next_chunk(), upto - done)
+                launched += 1
+                model.forward_patches(st["patches"][done * g:(done + n) * g], n,
+                                      out_logits=st["logits"][done:done + n], out_top1=st["top1"][done:done + n])
                 done += n
 
         for i in range(slices):
@@ -208,24 +249,31 @@ class HotPath:
             st["events"][i].synchronize()
             n_i = min(int(st["pin"][i].item()), cls[i].crop_box.shape[0])
             main.wait_event(st["events"][i])
-            self._grow(st, total + n_i, total, dev)
+            hp._grow(st, total + n_i, total, dev)
             if n_i:
                 ops.crop_resize(st["imgs"][a:b], cls[i].crop_box, cls[i].crop_img, n_i, c.interp, c.out_size,
-                                self.model.cfg.patch, "patch", out=st["patches"][total * g:(total + n_i) * g])
+                                model.cfg.patch, "patch", out=st["patches"][total * g:(total + n_i) * g])
             offs.append(total)
             total += n_i
-            vit(done + ((total - done) // vit_chunk) * vit_chunk)      # only full chunks while slices remain
+            while total - done >= next_chunk():                        # only full chunks while slices remain
+                vit(done + next_chunk())
         vit(total)
         rec = torch.empty(B, c.max_det, 8, dtype=torch.float32, device=dev)
         for i in range(slices):
             a, b = bounds[i], bounds[i + 1]
             ops.pack_results(cls[i], st["top1"][offs[i]:] if total else None, out=rec[a:b])
-        if out_records_h is not None:
-            out_records_h.copy_(rec, non_blocking=True)
+        if self.out_records_h is not None:
+            self.out_records_h.copy_(rec, non_blocking=True)
+        if st["free"] is None:
+            st["free"] = torch.cuda.Event()
+        st["free"].record(main)                # the slot's staging buffers may be overwritten after this point
         main.synchronize()
-        return HotPathResult(records=rec, det_count=torch.cat([cl.det_count for cl in cls]), n_crops=total,
-                             logits=st["logits"][:total] if total else None,
-                             top1=st["top1"][:total] if total else None)
+        # results are copied out of the slot's crop-indexed buffers: the next-but-one submit reuses them
+        self._res = HotPathResult(records=rec, det_count=torch.cat([cl.det_count for cl in cls]), n_crops=total,
+                                  logits=st["logits"][:total].clone() if total else None,
+                                  top1=st["top1"][:total].clone() if total else None)
+        self.cls = None
+        return self._res
 
 
 def records_to_tuples(records: torch.Tensor, names=None):
