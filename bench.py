@@ -88,17 +88,20 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append([c.strip() for c in line.split(",")])
+            self.rows.append((time.monotonic(), [c.strip() for c in line.split(",")]))
 
-    def stop(self):
+    def stop(self, windows=()):
+        """`windows`: [(t0, t1)] (time.monotonic) of the timed regions; only samples taken inside them count
+        (the sampler is started early because nvidia-smi needs ~1 s to come up on an 8-GPU box)."""
         if not self.proc:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
         self.t.join(timeout=2)
-        sm = sorted(int(r[0]) for r in self.rows if r and r[0].isdigit())
-        mx = [int(r[1]) for r in self.rows if len(r) > 1 and r[1].isdigit()]
+        rows = [r for t, r in self.rows if not windows or any(a <= t <= b + 0.11 for a, b in windows)]
+        sm = sorted(int(r[0]) for r in rows if r and r[0].isdigit())
+        mx = [int(r[1]) for r in rows if len(r) > 1 and r[1].isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i] == "Active" for r in self.rows)]
+        reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i] == "Active" for r in rows)]
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
                 "reasons": reasons, "samples": len(sm)}
 
@@ -189,6 +192,8 @@ def run_ours(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     B = args.batch
+    clocks = ClockSampler(local)                   # started early: nvidia-smi needs ~1 s to come up
+    clocks.start()
     sd = vit_weights()
     model = ViTModel(ViTConfig(), dev).load_state_dict(sd)
     hp = HotPath(model, HotPathConfig())
@@ -244,10 +249,9 @@ def run_ours(args):
 
     for _ in range(max(args.warmup, 3)):
         r = step_resident()
-    clocks = ClockSampler(local)
-    clocks.start()
+    w0 = time.monotonic()
     ms, r = timed(step_resident, args.steps)
-    clk = clocks.stop()
+    windows = [(w0, time.monotonic())]
     # second pass of the same K steps with every launch event-bracketed on its stream: per-kernel
     # device time for the roofline (kept out of the headline timing: 2 events per launch)
     ms_prof, _ = timed(step_resident, args.steps, prof=True)
@@ -255,7 +259,10 @@ def run_ours(args):
     _lib.prof_enable(False)
     n_crops = r.n_crops
     run_e2e(2)
+    w0 = time.monotonic()
     ms_e2e, _ = timed(lambda: run_e2e(args.steps), 1)
+    windows.append((w0, time.monotonic()))
+    clk = clocks.stop(windows)                     # samples taken during the two timed regions
 
     if rank == 0:
         hbm, tf_burst, tf_sus, which = peaks()
