@@ -87,7 +87,7 @@ void add_param(yv_vit *m, const std::string &name, size_t numel, bool bf16, bool
 
 struct VitWs {
   float *x32;
-  __nv_bfloat16 *y, *d, *qkv, *h, *cls_ln;
+  __nv_bfloat16 *y, *d, *d2, *qkv, *h, *cls_ln;
   float *hidden;
   float *stats[2];      // folded-LayerNorm pipeline: per-row partial (sum, sum of squares), dim / 128 slots
   size_t total;
@@ -102,6 +102,7 @@ VitWs vit_ws(const yv_vit *m, void *base, int chunk) {
   w.x32 = (float *)(b + o);            o = yv_align_up(o + M * c.dim * 4, 1024);
   w.y = (__nv_bfloat16 *)(b + o);      o = yv_align_up(o + M * c.dim * 2, 1024);
   w.d = (__nv_bfloat16 *)(b + o);      o = yv_align_up(o + M * c.dim * 2, 1024);
+  w.d2 = (__nv_bfloat16 *)(b + o);     o = yv_align_up(o + M * c.dim * 2, 1024);
   w.qkv = (__nv_bfloat16 *)(b + o);    o = yv_align_up(o + M * 3 * c.dim * 2, 1024);
   w.h = (__nv_bfloat16 *)(b + o);      o = yv_align_up(o + M * c.mlp * 2, 1024);
   w.cls_ln = (__nv_bfloat16 *)(b + o); o = yv_align_up(o + (size_t)chunk * c.dim * 2, 1024);
@@ -311,26 +312,28 @@ YV_EXPORT int yv_vit_forward(yv_vit_t *m, const void *patches_bf16, int n, float
       // final norm on the class-token rows only (x32 is up to date), then the heads
       if ((rc = yv_ln_launch(w.x32, true, (size_t)T * D, nullptr, 0, false, m->F("model.norm.weight"), m->F("model.norm.bias"), w.cls_ln, cc, D, c.eps, s))) return rc;
     } else {
-      // Residual adds are fused into the NEXT LayerNorm (x32 += d, fp32), so proj / fc2 store a plain
-      // bf16 delta d: same HBM traffic, but no global loads on the GEMM epilogue's critical path.
-      const __nv_bfloat16 *pending = nullptr;            // delta not yet added to x32
+      // Residual adds are fused into the LayerNorms, so proj / fc2 store plain bf16 deltas (no global loads on
+      // the GEMM epilogue's critical path).  The fp32 stream is rewritten ONCE per block: norm2 normalises
+      // x32 + d_attn on the fly without writing it back, and the next norm1 folds (x32 + d_attn) + d_mlp in and
+      // writes x32 -- the same fp32 sums in the same order as two separate updates, 1.5 KB less traffic per token.
+      bool have = false;                                 // deltas of the previous block pending?
       for (int i = 0; i < c.depth; ++i) {
         const std::string p = "model.blocks." + std::to_string(i) + ".";
-        if ((rc = yv_ln_launch(w.x32, true, D, pending, D, true, m->F(p + "norm1.weight"), m->F(p + "norm1.bias"), w.y, M, D, c.eps, s))) return rc;
+        if ((rc = yv_ln2_launch(w.x32, true, D, have ? w.d : nullptr, have ? w.d2 : nullptr, D, true, m->F(p + "norm1.weight"), m->F(p + "norm1.bias"), w.y, M, D, c.eps, s))) return rc;
         ep = GemmEpilogue{w.qkv, m->F(p + "attn.qkv.bias"), nullptr, nullptr, 0, false, false, false};
         if ((rc = yv_gemm_launch(w.y, m->B(p + "attn.qkv.weight"), M, 3 * D, D, ep, s))) return rc;
         if ((rc = yv_attention_launch(w.qkv, w.y, cc, T, c.heads, D / c.heads, s))) return rc;
         ep = GemmEpilogue{w.d, m->F(p + "attn.proj.bias"), nullptr, nullptr, 0, false, false, false};
         if ((rc = yv_gemm_launch(w.y, m->B(p + "attn.proj.weight"), M, D, D, ep, s))) return rc;
-        if ((rc = yv_ln_launch(w.x32, true, D, w.d, D, true, m->F(p + "norm2.weight"), m->F(p + "norm2.bias"), w.y, M, D, c.eps, s))) return rc;
+        if ((rc = yv_ln_launch(w.x32, true, D, w.d, D, false, m->F(p + "norm2.weight"), m->F(p + "norm2.bias"), w.y, M, D, c.eps, s))) return rc;
         ep = GemmEpilogue{w.h, m->F(p + "mlp.fc1.bias"), nullptr, nullptr, 0, true, false, false};
         if ((rc = yv_gemm_launch(w.y, m->B(p + "mlp.fc1.weight"), M, c.mlp, D, ep, s))) return rc;
-        ep = GemmEpilogue{w.d, m->F(p + "mlp.fc2.bias"), nullptr, nullptr, 0, false, false, false};
+        ep = GemmEpilogue{w.d2, m->F(p + "mlp.fc2.bias"), nullptr, nullptr, 0, false, false, false};
         if ((rc = yv_gemm_launch(w.h, m->B(p + "mlp.fc2.weight"), M, D, c.mlp, ep, s))) return rc;
-        pending = w.d;
+        have = true;
       }
-      // final norm on the class-token rows only (+ the last fc2 delta), 1000-way head, wrapper MLP + argmax
-      if ((rc = yv_ln_launch(w.x32, true, (size_t)T * D, pending, (size_t)T * D, false, m->F("model.norm.weight"), m->F("model.norm.bias"), w.cls_ln, cc, D, c.eps, s))) return rc;
+      // final norm on the class-token rows only (+ both deltas of the last block), 1000-way head, wrapper MLP + argmax
+      if ((rc = yv_ln2_launch(w.x32, true, (size_t)T * D, w.d, w.d2, (size_t)T * D, false, m->F("model.norm.weight"), m->F("model.norm.bias"), w.cls_ln, cc, D, c.eps, s))) return rc;
     }
     ep = GemmEpilogue{w.hidden, m->F("model.head.bias"), nullptr, nullptr, 0, false, true, false};
     if ((rc = yv_gemm_launch(w.cls_ln, m->B("model.head.weight"), cc, c.head_out, D, ep, s))) return rc;

@@ -15,8 +15,8 @@ constexpr int LN_MAXCH = 4;    // dim <= 1024 (chunks of 256 = 32 lanes x 8 elem
 
 template <bool XF32>
 __global__ void __launch_bounds__(LN_WARPS * 32)
-layernorm_kernel(const void *xv, size_t in_stride, const __nv_bfloat16 *__restrict__ delta, size_t delta_stride,
-                 int writeback, const float *__restrict__ gamma, const float *__restrict__ beta,
+layernorm_kernel(const void *xv, size_t in_stride, const __nv_bfloat16 *__restrict__ delta,
+                 const __nv_bfloat16 *__restrict__ delta2, size_t delta_stride, int writeback, const float *__restrict__ gamma, const float *__restrict__ beta,
                  __nv_bfloat16 *__restrict__ y, int rows, int dim, float eps) {
   const int lane = threadIdx.x & 31;
   const int row = blockIdx.x * LN_WARPS + (threadIdx.x >> 5);
@@ -50,6 +50,16 @@ layernorm_kernel(const void *xv, size_t in_stride, const __nv_bfloat16 *__restri
           const float2 f = __bfloat1622float2(h[k]);
           v[c][2 * k] += f.x;
           v[c][2 * k + 1] += f.y;
+        }
+        if (delta2) {    // second pending delta ((x + delta) + delta2, the order of two separate adds)
+          const uint4 u2 = *reinterpret_cast<const uint4 *>(delta2 + (size_t)row * delta_stride + e);
+          const __nv_bfloat162 *h2 = reinterpret_cast<const __nv_bfloat162 *>(&u2);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) {
+            const float2 f = __bfloat1622float2(h2[k]);
+            v[c][2 * k] += f.x;
+            v[c][2 * k + 1] += f.y;
+          }
         }
         if (XF32 && writeback) {
           float4 *p = reinterpret_cast<float4 *>((float *)const_cast<void *>(xv) + (size_t)row * in_stride + e);
@@ -157,13 +167,21 @@ wrapper_head_kernel(const float *__restrict__ hidden, int ld, const float *__res
 int yv_ln_launch(const void *x, bool x_f32, size_t in_stride, const __nv_bfloat16 *delta, size_t delta_stride,
                  bool writeback, const float *gamma, const float *beta, __nv_bfloat16 *y, int rows, int dim, float eps,
                  cudaStream_t s) {
+  return yv_ln2_launch(x, x_f32, in_stride, delta, nullptr, delta_stride, writeback, gamma, beta, y, rows, dim, eps, s);
+}
+
+int yv_ln2_launch(const void *x, bool x_f32, size_t in_stride, const __nv_bfloat16 *delta, const __nv_bfloat16 *delta2,
+                  size_t delta_stride,
+                 bool writeback, const float *gamma, const float *beta, __nv_bfloat16 *y, int rows, int dim, float eps,
+                 cudaStream_t s) {
   YV_REQUIRE(rows >= 1 && dim >= 256 && dim % 256 == 0 && dim <= 256 * LN_MAXCH, "layernorm: dim=%d must be a multiple of 256, <= %d", dim, 256 * LN_MAXCH);
   YV_REQUIRE(x && gamma && beta && y, "layernorm: null pointer");
   YV_REQUIRE(in_stride % 8 == 0, "layernorm: row stride must be a multiple of 8 elements");
   const int grid = (rows + LN_WARPS - 1) / LN_WARPS;
-  YvProf prof(YV_K_LN, s, (double)rows * dim * ((x_f32 ? 6.0 : 4.0) + (delta ? 2.0 : 0.0) + (delta && writeback ? 4.0 : 0.0)));
-  if (x_f32) layernorm_kernel<true><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, delta, delta_stride, writeback ? 1 : 0, gamma, beta, y, rows, dim, eps);
-  else layernorm_kernel<false><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, delta, delta_stride, 0, gamma, beta, y, rows, dim, eps);
+  YV_REQUIRE(!delta2 || delta, "layernorm: delta2 needs delta");
+  YvProf prof(YV_K_LN, s, (double)rows * dim * ((x_f32 ? 6.0 : 4.0) + (delta ? 2.0 : 0.0) + (delta2 ? 2.0 : 0.0) + (delta && writeback ? 4.0 : 0.0)));
+  if (x_f32) layernorm_kernel<true><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, delta, delta2, delta_stride, writeback ? 1 : 0, gamma, beta, y, rows, dim, eps);
+  else layernorm_kernel<false><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, delta, delta2, delta_stride, 0, gamma, beta, y, rows, dim, eps);
   YV_LAUNCH_CHECK();
   return YV_OK;
 }
