@@ -164,17 +164,45 @@ __device__ __forceinline__ float normalise(float v) {
   return __fmul_rn(__fsub_rn(v, 127.5f), (float)(1.0 / 127.5));
 }
 
+// exact u8 -> fp32 without the conversion pipe: the byte becomes the low mantissa bits of 2^23
+__device__ __forceinline__ float byte_f32(unsigned word, int k) {
+  return __fsub_rn(__uint_as_float(__byte_perm(word, 0x4B000000u, 0x7440 | k)), 8388608.f);
+}
+// Six consecutive bytes (two RGB pixels) starting at byte offset o of a 4-byte-aligned buffer:
+// lo = bytes 0..3, hi = bytes 4..5.  Three aligned word loads + two funnel shifts instead of six
+// byte loads; the last 12 bytes of the buffer take the byte path so nothing is read past `total`.
+__device__ __noinline__ void fetch6_tail(const uint8_t *__restrict__ base, size_t o, size_t total, unsigned &lo,
+                                         unsigned &hi) {
+  unsigned b[6];
+#pragma unroll
+  for (int k = 0; k < 6; ++k) b[k] = (o + k < total) ? (unsigned)base[o + k] : 0u;
+  lo = b[0] | (b[1] << 8) | (b[2] << 16) | (b[3] << 24);
+  hi = b[4] | (b[5] << 8);
+}
+__device__ __forceinline__ void fetch6(const uint8_t *__restrict__ base, size_t o, size_t total, unsigned &lo,
+                                       unsigned &hi) {
+  if (o + 12 <= total) {
+    const unsigned *w = reinterpret_cast<const unsigned *>(base) + (o >> 2);
+    const unsigned w0 = __ldg(w), w1 = __ldg(w + 1), w2 = __ldg(w + 2);
+    const unsigned sh = ((unsigned)o & 3u) * 8u;
+    lo = __funnelshift_r(w0, w1, sh);
+    hi = __funnelshift_r(w1, w2, sh);
+  } else {
+    fetch6_tail(base, o, total, lo, hi);
+  }
+}
+
 constexpr int CR_T = 256;
 constexpr int CR_PX = 8;     // output pixels per thread (one 16-byte bf16 store per channel)
 
 // One thread = 8 consecutive output x pixels of one output row, all 3 channels.
 // Thread order inside a crop is (patch, row-in-patch, 8-px segment) so that the 16-byte stores
 // of a warp are contiguous in the patch-major output (512 B per channel for patch 16).
-template <int INTERP, int LAYOUT>
+template <int INTERP, int LAYOUT, bool WORDS>
 __global__ void __launch_bounds__(CR_T)
 crop_resize_kernel(const uint8_t *__restrict__ images, int H, int W, const int4 *__restrict__ crop_box,
                    const int32_t *__restrict__ crop_img, int n, const int32_t *__restrict__ n_dev,
-                   int out, int patch, void *__restrict__ dst) {
+                   int out, int patch, size_t total, void *__restrict__ dst) {
   const int crop = blockIdx.y;
   if (crop >= n || (n_dev && crop >= *n_dev)) return;
   const int segs_per_patch = patch * patch / CR_PX;
@@ -200,22 +228,46 @@ crop_resize_kernel(const uint8_t *__restrict__ images, int H, int W, const int4 
       const int sx = bx.x + nearest_tap(ox0 + j, cw, out);
       const uint8_t *px = row + (size_t)sx * 3;
 #pragma unroll
-      for (int c = 0; c < 3; ++c) v[c][j] = normalise((float)px[c]);
+      for (int c = 0; c < 3; ++c) v[c][j] = normalise(byte_f32(px[c], 0));
     }
   } else {
     const AxisTap ty = bilinear_tap(oy, ch, out);
-    const uint8_t *r0 = img + ((size_t)(bx.y + ty.i0) * W) * 3;
-    const uint8_t *r1 = img + ((size_t)(bx.y + ty.i1) * W) * 3;
+    const size_t img_row = (size_t)crop_img[crop] * H;
+    const size_t r0 = (img_row + bx.y + ty.i0) * W * 3, r1 = (img_row + bx.y + ty.i1) * W * 3;
 #pragma unroll
     for (int j = 0; j < CR_PX; ++j) {
       const AxisTap tx = bilinear_tap(ox0 + j, cw, out);
-      const size_t xa = (size_t)(bx.x + tx.i0) * 3, xb = (size_t)(bx.x + tx.i1) * 3;
+      const size_t xa = (size_t)(bx.x + tx.i0) * 3;
+      float a0[3], a1[3], b0[3], b1[3];      // a = left tap, b = right tap; 0/1 = upper/lower row
+      if (WORDS) {
+        unsigned lo0, hi0, lo1, hi1;
+        fetch6(images, r0 + xa, total, lo0, hi0);
+        fetch6(images, r1 + xa, total, lo1, hi1);
+        const bool same = tx.i1 == tx.i0;     // right edge of the crop: both taps are the same pixel
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          a0[c] = byte_f32(lo0, c);
+          a1[c] = byte_f32(lo1, c);
+        }
+        b0[0] = byte_f32(lo0, 3); b0[1] = byte_f32(hi0, 0); b0[2] = byte_f32(hi0, 1);
+        b1[0] = byte_f32(lo1, 3); b1[1] = byte_f32(hi1, 0); b1[2] = byte_f32(hi1, 1);
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          b0[c] = same ? a0[c] : b0[c];
+          b1[c] = same ? a1[c] : b1[c];
+        }
+      } else {
+        const size_t xb = (size_t)(bx.x + tx.i1) * 3;
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+          a0[c] = byte_f32(images[r0 + xa + c], 0); b0[c] = byte_f32(images[r0 + xb + c], 0);
+          a1[c] = byte_f32(images[r1 + xa + c], 0); b1[c] = byte_f32(images[r1 + xb + c], 0);
+        }
+      }
 #pragma unroll
       for (int c = 0; c < 3; ++c) {
-        const float a00 = (float)r0[xa + c], a01 = (float)r0[xb + c];
-        const float a10 = (float)r1[xa + c], a11 = (float)r1[xb + c];
-        const float top = __fadd_rn(a00, __fmul_rn(tx.f, __fsub_rn(a01, a00)));
-        const float bot = __fadd_rn(a10, __fmul_rn(tx.f, __fsub_rn(a11, a10)));
+        const float top = __fadd_rn(a0[c], __fmul_rn(tx.f, __fsub_rn(b0[c], a0[c])));
+        const float bot = __fadd_rn(a1[c], __fmul_rn(tx.f, __fsub_rn(b1[c], a1[c])));
         v[c][j] = normalise(__fadd_rn(top, __fmul_rn(ty.f, __fsub_rn(bot, top))));
       }
     }
@@ -320,7 +372,14 @@ YV_EXPORT int yv_crop_resize(const uint8_t *images, int B, int H, int W, const i
   cudaStream_t s = (cudaStream_t)stream;
   const int4 *cb = (const int4 *)crop_box;
   YvProf prof(YV_K_CROP, s, (double)n * out_size * out_size * 3 * (layout == YV_LAYOUT_PATCH_BF16 ? 2 : 4));
-#define YV_CR(I, L) crop_resize_kernel<I, L><<<grid, CR_T, 0, s>>>(images, H, W, cb, crop_img, n, n_dev, out_size, patch, out)
+  // aligned word loads need a 4-byte-aligned image base (any CUDA allocation); otherwise byte loads
+  const size_t total = (size_t)B * H * W * 3;
+  const bool words = ((uintptr_t)images % 4) == 0;
+#define YV_CR(I, L)                                                                                              \
+  do {                                                                                                           \
+    if (words) crop_resize_kernel<I, L, true><<<grid, CR_T, 0, s>>>(images, H, W, cb, crop_img, n, n_dev, out_size, patch, total, out); \
+    else crop_resize_kernel<I, L, false><<<grid, CR_T, 0, s>>>(images, H, W, cb, crop_img, n, n_dev, out_size, patch, total, out);      \
+  } while (0)
   if (interp == YV_INTERP_NEAREST) {
     if (layout == YV_LAYOUT_PATCH_BF16) YV_CR(YV_INTERP_NEAREST, YV_LAYOUT_PATCH_BF16);
     else YV_CR(YV_INTERP_NEAREST, YV_LAYOUT_CHW_F32);

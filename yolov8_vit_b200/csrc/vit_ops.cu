@@ -119,46 +119,90 @@ __global__ void cls_rows_kernel(float *__restrict__ x32, const float *__restrict
 }
 
 // ------------------------------------------------------------------------------------ wrapper head
-// One CTA per crop: relu(h) [head_out] -> hid (<= 256) -> ncls (<= 32); fp32 throughout.
-constexpr int WH_T = 256;
+// One CTA per WH_CP crops: relu(h) [head_out] -> hid (<= 256) -> ncls (<= 32); fp32 throughout.
+// Each w1 row is read once per CTA (16-byte loads when VEC) and applied to all WH_CP crops, two rows
+// in flight per warp; the per-crop summation order does not depend on how crops are grouped.
+constexpr int WH_T = 512;
+constexpr int WH_CP = 2;
+template <bool VEC>
 __global__ void __launch_bounds__(WH_T)
 wrapper_head_kernel(const float *__restrict__ hidden, int ld, const float *__restrict__ w1,
                     const float *__restrict__ b1, const float *__restrict__ w3, const float *__restrict__ b3,
-                    int head_out, int hid, int ncls, float *__restrict__ logits, int32_t *__restrict__ top1) {
-  extern __shared__ float sh[];
-  float *s_in = sh;                 // [head_out]
-  float *s_mid = sh + head_out;     // [hid]
-  float *s_out = s_mid + hid;       // [ncls]
-  const int c = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  for (int i = tid; i < head_out; i += WH_T) s_in[i] = fmaxf(hidden[(size_t)c * ld + i], 0.f);
-  __syncthreads();
-  for (int j = warp; j < hid; j += WH_T / 32) {
-    const float *w = w1 + (size_t)j * head_out;
-    float acc = 0.f;
-    for (int i = lane; i < head_out; i += 32) acc += w[i] * s_in[i];
-#pragma unroll
-    for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
-    if (lane == 0) s_mid[j] = fmaxf(acc + b1[j], 0.f);
+                    int n, int head_out, int hid, int ncls, float *__restrict__ logits, int32_t *__restrict__ top1) {
+  extern __shared__ __align__(16) float sh[];
+  const int in_ld = (head_out + 3) & ~3;
+  float *s_in = sh;                          // [WH_CP][in_ld]
+  float *s_mid = s_in + WH_CP * in_ld;       // [WH_CP][hid]
+  float *s_out = s_mid + WH_CP * hid;        // [WH_CP][ncls]
+  const int c0 = blockIdx.x * WH_CP, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int i = tid; i < WH_CP * in_ld; i += WH_T) {
+    const int cc = i / in_ld, e = i - cc * in_ld;
+    s_in[i] = (c0 + cc < n && e < head_out) ? fmaxf(hidden[(size_t)(c0 + cc) * ld + e], 0.f) : 0.f;
   }
   __syncthreads();
-  for (int j = warp; j < ncls; j += WH_T / 32) {
+  for (int j0 = warp * 2; j0 < hid; j0 += (WH_T / 32) * 2) {
+    const int j1 = min(j0 + 1, hid - 1);
+    float acc[2][WH_CP];
+#pragma unroll
+    for (int r = 0; r < 2; ++r)
+#pragma unroll
+      for (int cc = 0; cc < WH_CP; ++cc) acc[r][cc] = 0.f;
+    if (VEC) {
+      const float4 *wa = reinterpret_cast<const float4 *>(w1 + (size_t)j0 * head_out);
+      const float4 *wb = reinterpret_cast<const float4 *>(w1 + (size_t)j1 * head_out);
+#pragma unroll 4
+      for (int i = lane; i < head_out / 4; i += 32) {
+        const float4 a = wa[i], b = wb[i];
+#pragma unroll
+        for (int cc = 0; cc < WH_CP; ++cc) {
+          const float4 x = *reinterpret_cast<const float4 *>(s_in + cc * in_ld + 4 * i);
+          acc[0][cc] += a.x * x.x; acc[0][cc] += a.y * x.y; acc[0][cc] += a.z * x.z; acc[0][cc] += a.w * x.w;
+          acc[1][cc] += b.x * x.x; acc[1][cc] += b.y * x.y; acc[1][cc] += b.z * x.z; acc[1][cc] += b.w * x.w;
+        }
+      }
+    } else {
+      const float *wa = w1 + (size_t)j0 * head_out, *wb = w1 + (size_t)j1 * head_out;
+      for (int i = lane; i < head_out; i += 32) {
+        const float a = wa[i], b = wb[i];
+#pragma unroll
+        for (int cc = 0; cc < WH_CP; ++cc) {
+          acc[0][cc] += a * s_in[cc * in_ld + i];
+          acc[1][cc] += b * s_in[cc * in_ld + i];
+        }
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < 2; ++r)
+#pragma unroll
+      for (int cc = 0; cc < WH_CP; ++cc) {
+        float v = acc[r][cc];
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+        const int j = r ? j0 + 1 : j0;
+        if (lane == 0 && j < hid) s_mid[cc * hid + j] = fmaxf(v + b1[j], 0.f);
+      }
+  }
+  __syncthreads();
+  for (int q = warp; q < WH_CP * ncls; q += WH_T / 32) {
+    const int cc = q / ncls, j = q - cc * ncls;
     const float *w = w3 + (size_t)j * hid;
     float acc = 0.f;
-    for (int i = lane; i < hid; i += 32) acc += w[i] * s_mid[i];
+    for (int i = lane; i < hid; i += 32) acc += w[i] * s_mid[cc * hid + i];
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
     if (lane == 0) {
       acc += b3[j];
-      s_out[j] = acc;
-      logits[(size_t)c * ncls + j] = acc;
+      s_out[cc * ncls + j] = acc;
+      if (c0 + cc < n) logits[(size_t)(c0 + cc) * ncls + j] = acc;
     }
   }
   __syncthreads();
-  if (tid == 0) {
+  if (tid < WH_CP && c0 + tid < n) {
+    const float *o = s_out + tid * ncls;
     int best = 0;
     for (int j = 1; j < ncls; ++j)
-      if (s_out[j] > s_out[best]) best = j;
-    top1[c] = best;
+      if (o[j] > o[best]) best = j;
+    top1[c0 + tid] = best;
   }
 }
 
@@ -277,10 +321,13 @@ int yv_wrapper_head_launch(const float *hidden, int ld_hidden, const float *w1, 
                            const float *b3, int n, int head_out, int hid, int ncls, float *logits, int32_t *top1,
                            cudaStream_t s) {
   YV_REQUIRE(n >= 1 && head_out >= 1 && hid >= 1 && ncls >= 1, "wrapper head: bad shape");
-  const size_t smem = (size_t)(head_out + hid + ncls) * sizeof(float);
+  const size_t smem = (size_t)WH_CP * (((head_out + 3) & ~3) + hid + ncls) * sizeof(float);
   YV_REQUIRE(smem <= 48 * 1024, "wrapper head: %zu bytes of shared memory exceed 48 KB", smem);
   YvProf prof(YV_K_HEAD, s, 0.0);
-  wrapper_head_kernel<<<n, WH_T, smem, s>>>(hidden, ld_hidden, w1, b1, w3, b3, head_out, hid, ncls, logits, top1);
+  const int grid = (n + WH_CP - 1) / WH_CP;
+  const bool vec = head_out % 4 == 0 && hid % 4 == 0 && (reinterpret_cast<uintptr_t>(w1) & 15) == 0;
+  if (vec) wrapper_head_kernel<true><<<grid, WH_T, smem, s>>>(hidden, ld_hidden, w1, b1, w3, b3, n, head_out, hid, ncls, logits, top1);
+  else wrapper_head_kernel<false><<<grid, WH_T, smem, s>>>(hidden, ld_hidden, w1, b1, w3, b3, n, head_out, hid, ncls, logits, top1);
   YV_LAUNCH_CHECK();
   return YV_OK;
 }
