@@ -17,6 +17,7 @@ namespace {
 
 constexpr int DEC_NT = 128;      // threads per tile
 constexpr int DEC_UNROLL = 8;    // class rows in flight per thread
+constexpr int DEC_GS = 256;      // tiles per image handled by the parallel gather
 
 template <int VEC> struct RowVec;
 template <> struct RowVec<4> {
@@ -208,22 +209,62 @@ decode_filter_kernel(const float *__restrict__ head, int nc, int A, float conf, 
   if (!s_last) return;
   __threadfence();
 
-  // running offset over tiles (tiles is small: A/TILE); staged reads go through L2 (.cg)
+  // Gather, parallel form: tile counts -> exclusive offsets (warp 0), then every staged candidate is one
+  // independent copy (binary search of its tile), so the last tile pays two memory latencies instead of one
+  // per tile (the serial per-tile walk was a 17 us tail per image: 4.4 -> 5.5 TB/s at the bench shape).
+  // Staged reads go through L2 (.cg).  Serial walk kept for > DEC_GS tiles.
+  __shared__ int s_cnt[DEC_GS], s_off[DEC_GS], s_total;
   int off = 0;
-  for (int t = 0; t < tiles; ++t) {
-    const int n = __ldcg(&st.tile_count[b * tiles + t]);
-    const size_t src = ((size_t)b * tiles + t) * TILE;
-    for (int i = tid; i < n; i += DEC_NT) {
-      const int dst = off + i;
-      if (dst < cap) {
-        const size_t o = (size_t)b * cap + dst;
-        out_box[o] = __ldcg(&st.box[src + i]);
-        out_score[o] = __ldcg(&st.score[src + i]);
-        out_label[o] = __ldcg(&st.label[src + i]);
-        out_anchor[o] = __ldcg(&st.anchor[src + i]);
+  if (tiles <= DEC_GS) {
+    for (int t = tid; t < tiles; t += DEC_NT) s_cnt[t] = __ldcg(&st.tile_count[b * tiles + t]);
+    __syncthreads();
+    if (tid < 32) {
+      int carry = 0;
+      for (int base = 0; base < tiles; base += 32) {
+        const int v = base + lane < tiles ? s_cnt[base + lane] : 0;
+        int inc = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+          int u = __shfl_up_sync(0xffffffffu, inc, d);
+          if (lane >= d) inc += u;
+        }
+        if (base + lane < tiles) s_off[base + lane] = carry + inc - v;
+        carry += __shfl_sync(0xffffffffu, inc, 31);
       }
+      if (lane == 0) s_total = carry;
     }
-    off += n;
+    __syncthreads();
+    off = s_total;
+    const int lim = off < cap ? off : cap;
+    for (int idx = tid; idx < lim; idx += DEC_NT) {
+      int lo = 0, hi = tiles - 1;
+      while (lo < hi) {                                 // last tile whose offset is <= idx (it is non-empty)
+        const int mid = (lo + hi + 1) >> 1;
+        if (s_off[mid] <= idx) lo = mid; else hi = mid - 1;
+      }
+      const size_t src = ((size_t)b * tiles + lo) * TILE + (idx - s_off[lo]);
+      const size_t o = (size_t)b * cap + idx;
+      out_box[o] = __ldcg(&st.box[src]);
+      out_score[o] = __ldcg(&st.score[src]);
+      out_label[o] = __ldcg(&st.label[src]);
+      out_anchor[o] = __ldcg(&st.anchor[src]);
+    }
+  } else {
+    for (int t = 0; t < tiles; ++t) {
+      const int n = __ldcg(&st.tile_count[b * tiles + t]);
+      const size_t src = ((size_t)b * tiles + t) * TILE;
+      for (int i = tid; i < n; i += DEC_NT) {
+        const int dst = off + i;
+        if (dst < cap) {
+          const size_t o = (size_t)b * cap + dst;
+          out_box[o] = __ldcg(&st.box[src + i]);
+          out_score[o] = __ldcg(&st.score[src + i]);
+          out_label[o] = __ldcg(&st.label[src + i]);
+          out_anchor[o] = __ldcg(&st.anchor[src + i]);
+        }
+      }
+      off += n;
+    }
   }
   if (tid == 0) {
     out_count[b] = off;
