@@ -222,3 +222,54 @@ def test_efficient_nms_equals_torchvision_batched_nms(thr):
     assert k[0, :int(n[0])].cpu().tolist() == torchvision.ops.nms(bx, sc, 0.5).tolist() == [0, 1, 2]
     k, n = ops.nms_batched(bx[None].to(DEV), sc[None].to(DEV), None, 0.5, 0)          # custom_nms suppresses equality
     assert k[0, :int(n[0])].cpu().tolist() == [0, 2]
+
+
+@pytest.mark.parametrize("B,S,max_det,cap_frac", [(3, 64, 100, 1.0), (37, 200, 100, 1.0), (700, 24, 10, 1.0),
+                                                   (5, 400, 300, 1.0), (16, 128, 100, 0.4)])
+def test_build_crops_vs_oracle(B, S, max_det, cap_frac):
+    """Crop list (round -> dilate -> clamp -> valid-crop compaction in (image, rank) order) against the
+    oracle's round_boxes + dilate_box: degenerate boxes (invalid crops), more keeps than max_det, more than
+    one 512-image scan block, max_det above one 128-slot sweep, and an overflowing crop_cap."""
+    g = torch.Generator().manual_seed(B * 1000 + S)
+    W, H = 640, 480
+    xy = torch.rand(B, S, 2, generator=g) * torch.tensor([W, H]) * 1.1 - 20.0
+    wh = torch.rand(B, S, 2, generator=g) * 120.0
+    wh[torch.rand(B, S, generator=g) < 0.15] = 0.2                    # rounds to an empty box -> invalid crop
+    boxes = torch.cat([xy, xy + wh], -1).contiguous()
+    scores = torch.rand(B, S, generator=g)
+    labels = torch.randint(0, 80, (B, S), generator=g, dtype=torch.int32)
+    anchors = torch.randint(0, 8400, (B, S), generator=g, dtype=torch.int32)
+    keep_counts = torch.randint(0, min(S, max_det + 40) + 1, (B,), generator=g, dtype=torch.int32)
+    keep = torch.stack([torch.randperm(S, generator=g) for _ in range(B)]).to(torch.int32)
+    ref_total = 0
+    ref = []
+    for b in range(B):
+        nk = min(int(keep_counts[b]), max_det)
+        for k in range(nk):
+            i = int(keep[b, k])
+            q = O.round_boxes(boxes[b, i]).tolist()
+            x0, y0, x1, y1, ok = O.dilate_box(*q, W, H)
+            ref.append((b, k, q, [x0, y0, x1, y1], ok, i))
+            ref_total += int(ok)
+    cap = max(1, int(ref_total * cap_frac))
+    cl = ops.build_crops(boxes.to(DEV), scores.to(DEV), labels.to(DEV), anchors.to(DEV), keep.to(DEV),
+                         keep_counts.to(DEV), max_det, W, H, crop_cap=cap)
+    assert int(cl.n_crops) == ref_total
+    assert torch.equal(cl.det_count.cpu(), keep_counts.clamp(max=max_det))
+    det_box, det_cb, det_crop = cl.det_box.cpu(), cl.det_crop_box.cpu(), cl.det_crop.cpu()
+    det_score, det_label, det_anchor = cl.det_score.cpu(), cl.det_label.cpu(), cl.det_anchor.cpu()
+    crop_box, crop_img, crop_det = cl.crop_box.cpu(), cl.crop_img.cpu(), cl.crop_det.cpu()
+    rank = 0
+    filled = torch.zeros(B, max_det, dtype=torch.bool)
+    for b, k, q, c, ok, i in ref:
+        filled[b, k] = True
+        assert det_box[b, k].tolist() == q and det_cb[b, k].tolist() == c
+        assert det_score[b, k] == scores[b, i] and det_label[b, k] == labels[b, i] and det_anchor[b, k] == anchors[b, i]
+        if ok and rank < cap:
+            assert int(det_crop[b, k]) == rank
+            assert crop_box[rank].tolist() == c and int(crop_img[rank]) == b and int(crop_det[rank]) == b * max_det + k
+        else:
+            assert int(det_crop[b, k]) == -1
+        rank += int(ok)
+    assert bool((det_crop[~filled] == -1).all()) and bool((det_label[~filled] == -1).all())
+    assert bool((det_box[~filled] == 0).all()) and bool((det_score[~filled] == 0).all())

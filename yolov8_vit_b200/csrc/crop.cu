@@ -41,10 +41,14 @@ __global__ void dilate_kernel(const int4 *__restrict__ in, int n, int W, int H, 
 // torch.round(x).to(int32): round half to even, then C-style truncating cast (values are integral)
 __device__ __forceinline__ int round_i32(float v) { return (int)rintf(v); }
 
-constexpr int BC_T = 1024;
+constexpr int BC_T = 512;
+constexpr int BC_K = 4;      // detections per lane in flight (4 x 32 = 128 >= the usual max_det of 100)
 
-// One CTA.  Thread-per-image walk (<= max_det detections each), block scan of the per-image
-// valid counts, then the same walk writes the compacted crop list in (image, rank) order.
+// One CTA (the crop list is one global prefix over images).  A warp owns an image at a time and walks its
+// max_det slots 32 x BC_K at a time with all loads of a lane issued back to back, so an image costs one
+// memory round trip instead of max_det dependent ones; stores are coalesced over k.  Pass 1 writes the
+// per-detection arrays and counts the valid crops per image, a block scan turns the counts into offsets,
+// pass 2 ranks the valid crops inside the image with ballots and writes the compacted (image, rank)-ordered list.
 __global__ void __launch_bounds__(BC_T)
 build_crops_kernel(const float4 *__restrict__ boxes, const float *__restrict__ scores,
                    const int32_t *__restrict__ labels, const int32_t *__restrict__ anchors,
@@ -57,42 +61,74 @@ build_crops_kernel(const float4 *__restrict__ boxes, const float *__restrict__ s
                    int32_t *__restrict__ crop_img, int32_t *__restrict__ crop_det, int crop_cap,
                    int32_t *__restrict__ n_crops) {
   __shared__ int s_warp[BC_T / 32];
+  __shared__ int s_cnt[BC_T], s_off[BC_T];
   __shared__ int s_carry;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid == 0) s_carry = 0;
   __syncthreads();
   for (int b0 = 0; b0 < B; b0 += BC_T) {
-    const int b = b0 + tid;
-    int nk = 0, nvalid = 0;
-    if (b < B) {
-      nk = min(keep_counts[b], max_det);
-      det_count[b] = nk;
-      for (int k = 0; k < max_det; ++k) {
-        const size_t o = (size_t)b * max_det + k;
-        if (k < nk) {
-          const int id = keep[(size_t)b * stride + k];
-          const float4 f = boxes[(size_t)b * stride + id];
-          int4 q = make_int4(round_i32(f.x), round_i32(f.y), round_i32(f.z), round_i32(f.w));
-          int4 c;
-          const bool ok = dilate_clamp(q.x, q.y, q.z, q.w, W, H, num, den, mode, c);
-          det_box[o] = q;
-          det_crop_box[o] = c;
-          det_score[o] = scores[(size_t)b * stride + id];
-          det_label[o] = labels ? labels[(size_t)b * stride + id] : 0;
-          det_anchor[o] = anchors ? anchors[(size_t)b * stride + id] : id;
-          det_crop[o] = ok ? 0 : -1;   // provisional: rank filled in below
-          nvalid += ok ? 1 : 0;
-        } else {
-          det_box[o] = make_int4(0, 0, 0, 0);
-          det_crop_box[o] = make_int4(0, 0, 0, 0);
-          det_score[o] = 0.f;
-          det_label[o] = -1;
-          det_anchor[o] = -1;
-          det_crop[o] = -1;
+    const int nb = min(BC_T, B - b0);
+    // ---- pass 1: per-detection arrays + valid-crop count per image
+    for (int bi = warp; bi < nb; bi += BC_T / 32) {
+      const int b = b0 + bi;
+      const int nk = min(keep_counts[b], max_det);
+      const size_t ib = (size_t)b * stride;
+      int nvalid = 0;
+      for (int k0 = 0; k0 < max_det; k0 += 32 * BC_K) {
+        int id[BC_K];
+        float4 f[BC_K];
+        float sc[BC_K];
+        int lb[BC_K], an[BC_K];
+#pragma unroll
+        for (int u = 0; u < BC_K; ++u) {
+          const int k = k0 + u * 32 + lane;
+          id[u] = k < nk ? keep[ib + k] : -1;
+        }
+#pragma unroll
+        for (int u = 0; u < BC_K; ++u) {
+          if (id[u] >= 0) {
+            f[u] = boxes[ib + id[u]];
+            sc[u] = scores[ib + id[u]];
+            lb[u] = labels ? labels[ib + id[u]] : 0;
+            an[u] = anchors ? anchors[ib + id[u]] : id[u];
+          }
+        }
+#pragma unroll
+        for (int u = 0; u < BC_K; ++u) {
+          const int k = k0 + u * 32 + lane;
+          bool ok = false;
+          if (k < max_det) {
+            const size_t o = (size_t)b * max_det + k;
+            if (id[u] >= 0) {
+              const int4 q = make_int4(round_i32(f[u].x), round_i32(f[u].y), round_i32(f[u].z), round_i32(f[u].w));
+              int4 c;
+              ok = dilate_clamp(q.x, q.y, q.z, q.w, W, H, num, den, mode, c);
+              det_box[o] = q;
+              det_crop_box[o] = c;
+              det_score[o] = sc[u];
+              det_label[o] = lb[u];
+              det_anchor[o] = an[u];
+              det_crop[o] = ok ? 0 : -1;   // provisional: rank filled in by pass 2
+            } else {
+              det_box[o] = make_int4(0, 0, 0, 0);
+              det_crop_box[o] = make_int4(0, 0, 0, 0);
+              det_score[o] = 0.f;
+              det_label[o] = -1;
+              det_anchor[o] = -1;
+              det_crop[o] = -1;
+            }
+          }
+          nvalid += __popc(__ballot_sync(0xffffffffu, ok));
         }
       }
+      if (lane == 0) {
+        det_count[b] = nk;
+        s_cnt[bi] = nvalid;
+      }
     }
-    // block exclusive scan of nvalid
+    __syncthreads();
+    // ---- block exclusive scan of the per-image counts (thread tid <-> image b0 + tid)
+    const int nvalid = tid < nb ? s_cnt[tid] : 0;
     int incl = nvalid;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
@@ -111,25 +147,45 @@ build_crops_kernel(const float4 *__restrict__ boxes, const float *__restrict__ s
       s_warp[lane] = inc2 - v;
     }
     __syncthreads();
-    int off = s_carry + s_warp[warp] + incl - nvalid;
-    if (b < B) {
-      for (int k = 0; k < nk; ++k) {
-        const size_t o = (size_t)b * max_det + k;
-        if (det_crop[o] == 0) {
-          if (off < crop_cap) {
-            crop_box[off] = det_crop_box[o];
-            crop_img[off] = b;
-            crop_det[off] = (int32_t)o;
-            det_crop[o] = off;
-          } else {
-            det_crop[o] = -1;
+    const int excl = s_carry + s_warp[warp] + incl - nvalid;
+    s_off[tid] = excl;
+    __syncthreads();
+    if (tid == BC_T - 1) s_carry = excl + nvalid;     // block total carried into the next BC_T images
+    // ---- pass 2: rank the valid crops of each image, write the compacted list
+    for (int bi = warp; bi < nb; bi += BC_T / 32) {
+      const int b = b0 + bi;
+      const int nk = min(keep_counts[b], max_det);
+      int off = s_off[bi];
+      for (int k0 = 0; k0 < nk; k0 += 32 * BC_K) {
+        int4 c[BC_K];
+        bool ok[BC_K];
+#pragma unroll
+        for (int u = 0; u < BC_K; ++u) {
+          const int k = k0 + u * 32 + lane;
+          const size_t o = (size_t)b * max_det + k;
+          ok[u] = k < nk && det_crop[o] == 0;         // this lane's own pass-1 store
+          if (ok[u]) c[u] = det_crop_box[o];
+        }
+#pragma unroll
+        for (int u = 0; u < BC_K; ++u) {
+          const int k = k0 + u * 32 + lane;
+          const size_t o = (size_t)b * max_det + k;
+          const unsigned m = __ballot_sync(0xffffffffu, ok[u]);
+          if (ok[u]) {
+            const int dst = off + __popc(m & lanemask_lt());
+            if (dst < crop_cap) {
+              crop_box[dst] = c[u];
+              crop_img[dst] = b;
+              crop_det[dst] = (int32_t)o;
+              det_crop[o] = dst;
+            } else {
+              det_crop[o] = -1;
+            }
           }
-          ++off;
+          off += __popc(m);
         }
       }
     }
-    __syncthreads();
-    if (tid == BC_T - 1) s_carry = off;   // the last thread's running offset = block total
     __syncthreads();
   }
   if (tid == 0) n_crops[0] = s_carry;
