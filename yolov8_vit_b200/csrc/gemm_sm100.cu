@@ -36,12 +36,15 @@ constexpr int UMMA_K = 16;
 constexpr int A_BYTES = BM * BK * 2;   // 16 KB
 constexpr int B_BYTES = BNH * BK * 2;  // 16 KB
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-constexpr int NUM_EPI_WARPS = 8;
-constexpr int GEMM_THREADS = (4 + NUM_EPI_WARPS) * 32;
+// Epilogue warps per CTA: 8 (two 128-column groups x 4 TMEM lane quarters) or 16 (four 64-column groups).  16 warps
+// hide the TMEM-load / smem-transpose latency of a heavy epilogue (GELU) better, at 96 registers per thread.
+constexpr int gemm_threads(int new_) { return (4 + new_) * 32; }
 constexpr int TMEM_COLS = 512;         // 2 accumulator stages x BN
 constexpr int BAR_BYTES = 256;          // mbarriers + TMEM slot
-constexpr int EPI_BYTES = NUM_EPI_WARPS * 32 * 16 * 4;   // per warp: 32 rows x 16 fp32, XOR-swizzled 16-byte segments
-constexpr size_t SMEM_BYTES = (size_t)STAGES * STAGE_BYTES + 1024 /*align slack*/ + BAR_BYTES + EPI_BYTES;
+// per epilogue warp: 32 rows x 16 fp32 staging, XOR-swizzled 16-byte segments
+constexpr size_t smem_bytes(int new_) {
+  return (size_t)STAGES * STAGE_BYTES + 1024 /*align slack*/ + BAR_BYTES + (size_t)new_ * 32 * 16 * 4;
+}
 
 // GELU in the epilogue.  The reference's nn.GELU is the erf form x * Phi(x); the first version evaluated it with
 // a degree-8 minimax polynomial for erf (|error| < 6e-5, ~10 issue slots per element), which cost 45 us of the
@@ -73,10 +76,12 @@ __device__ __forceinline__ void gelu4(float4 &v) {
 // position-table (patch embedding) and residual operands, MODE 2 the folded LayerNorm (row statistics +
 // column sums), MODE 3 the fused residual update (fp32 stream read-modify-write + bf16 copy + row statistics).
 constexpr int EPI_PLAIN = 0, EPI_EXTRA = 1, EPI_LNFOLD = 2, EPI_RESID = 3;
-template <bool GELU, bool OUT_F32, int MODE>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+template <bool GELU, bool OUT_F32, int MODE, int NEW>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(gemm_threads(NEW), 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const GemmEpilogue ep, int M, int N, int K) {
+  constexpr int EPI_COLS = BN * 4 / NEW;       // columns per epilogue warp
+  static_assert(MODE < EPI_LNFOLD || EPI_COLS == GEMM_STAT_COLS, "row-statistics slot = one epilogue warp's column group");
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
   uint64_t *bars = (uint64_t *)(smem + (size_t)STAGES * STAGE_BYTES);
@@ -98,7 +103,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // full: one arrive per producer of the pair (+ the bytes of both); empty / tfull: one multicast
     // tcgen05.commit; tempty (leader's copy is the one waited on): every epilogue warp of both CTAs
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 2); mbar_init(&empty[i], 1); }
-    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 2 * NUM_EPI_WARPS); }
+    for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 2 * NEW); }
     fence_barrier_init();
   }
   if (warp == 2) {
@@ -167,15 +172,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // The TMEM load of chunk c+1 is issued as soon as chunk c is in smem, hiding its latency.
     const int ew = warp - 4;
     const int q = warp & 3;                        // TMEM lane quarter this warp may access
-    const int half = ew >> 2;                      // column half of the tile
+    const int cg = ew >> 2;                        // column group of the tile (EPI_COLS columns)
     float *stg = reinterpret_cast<float *>(smem + (size_t)STAGES * STAGE_BYTES + BAR_BYTES) + ew * (32 * 16);
     const int trow = lane >> 2, tseg = lane & 3;   // transposed role: row-in-group, 16-byte segment
-    constexpr int NCH = BN / 2 / 16;               // 16-column chunks per warp
+    constexpr int NCH = EPI_COLS / 16;             // 16-column chunks per warp
     uint32_t it = 0;
     for (int tile = pair; tile < num_tiles; tile += npairs, ++it) {
       const uint32_t as = it & 1u, aph = (it >> 1) & 1u;
       const int m0 = (tile / n_tiles) * PM + (int)rank * BM, n0 = (tile % n_tiles) * BN;
-      const int colw = n0 + half * (BN / 2) + tseg * 4;       // this thread's first column (chunk 0)
+      const int colw = n0 + cg * EPI_COLS + tseg * 4;       // this thread's first column (chunk 0)
       float4 bias4[NCH];
 #pragma unroll
       for (int ch = 0; ch < NCH; ++ch) {
@@ -210,11 +215,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           float2 st = make_float2(0.f, 0.f);
           if (rok[i]) {                            // fixed-order sum of the producer's per-column-block partials
             const float2 *sp = reinterpret_cast<const float2 *>(ep.row_stats) + (size_t)row * ep.ln_slots;
-            float2 t[8];                           // all loads in flight at once (ln_slots <= 8)
+            float2 t[16];                          // all loads in flight at once (ln_slots <= 16)
 #pragma unroll
-            for (int j = 0; j < 8; ++j) t[j] = j < ep.ln_slots ? __ldg(sp + j) : make_float2(0.f, 0.f);
+            for (int j = 0; j < 16; ++j) t[j] = j < ep.ln_slots ? __ldg(sp + j) : make_float2(0.f, 0.f);
 #pragma unroll
-            for (int j = 0; j < 8; ++j) { st.x += t[j].x; st.y += t[j].y; }
+            for (int j = 0; j < 16; ++j) { st.x += t[j].x; st.y += t[j].y; }
           }
           ln_mu[i] = st.x * invd;
           ln_rstd[i] = rsqrtf(fmaxf(st.y * invd - ln_mu[i] * ln_mu[i], 0.f) + ep.ln_eps);
@@ -245,7 +250,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       }
       mbar_wait(&tfull[as], aph);
       tc_fence_after();
-      const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + half * (BN / 2);
+      const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + cg * EPI_COLS;
       uint32_t r[16];
       if (ep.dbg != 2) tmem_ld_32x16(tbase, r);
 #pragma unroll
@@ -336,9 +341,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           float a = rs_sum[i], b = rs_sq[i];
           a += __shfl_xor_sync(0xffffffffu, a, 1); b += __shfl_xor_sync(0xffffffffu, b, 1);
           a += __shfl_xor_sync(0xffffffffu, a, 2); b += __shfl_xor_sync(0xffffffffu, b, 2);
-          if (tseg == 0 && rok[i]) {               // one slot per 128-column block: deterministic, no atomics
-            const int slot = (n0 >> 7) + half;
-            reinterpret_cast<float2 *>(ep.stats_out)[(size_t)(m0 + q * 32 + i * 8 + trow) * (N >> 7) + slot] = make_float2(a, b);
+          if (tseg == 0 && rok[i]) {               // one slot per EPI_COLS-column block: deterministic, no atomics
+            const int slot = n0 / EPI_COLS + cg;
+            reinterpret_cast<float2 *>(ep.stats_out)[(size_t)(m0 + q * 32 + i * 8 + trow) * (N / EPI_COLS) + slot] = make_float2(a, b);
           }
         }
       }
@@ -376,13 +381,14 @@ void init_once() {
     return;
   }
   g_encode = (PFN_encodeTiled)fn;
-#define YV_SET(G, F, X)                                                                                       \
+#define YV_SET(G, F, X, W)                                                                                    \
   if (e == cudaSuccess)                                                                                     \
-    e = cudaFuncSetAttribute(gemm_bf16_kernel<G, F, X>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)SMEM_BYTES);
+    e = cudaFuncSetAttribute(gemm_bf16_kernel<G, F, X, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes(W));
   e = cudaSuccess;
-  YV_SET(false, false, 0) YV_SET(false, false, 1) YV_SET(false, true, 0) YV_SET(false, true, 1)
-  YV_SET(true, false, 0) YV_SET(true, false, 1) YV_SET(true, true, 0) YV_SET(true, true, 1)
-  YV_SET(false, false, 2) YV_SET(true, false, 2) YV_SET(false, false, 3)
+  YV_SET(false, false, 0, 8) YV_SET(false, true, 0, 8) YV_SET(true, false, 0, 8) YV_SET(true, true, 0, 8)
+  YV_SET(false, false, 0, 16) YV_SET(false, true, 0, 16) YV_SET(true, false, 0, 16) YV_SET(true, true, 0, 16)
+  YV_SET(false, false, 1, 8) YV_SET(false, true, 1, 8) YV_SET(true, false, 1, 8) YV_SET(true, true, 1, 8)
+  YV_SET(false, false, 2, 16) YV_SET(true, false, 2, 16) YV_SET(false, false, 3, 16)
 #undef YV_SET
   if (e != cudaSuccess) {
     g_init_status = yv_cuda_fail(e, "cudaFuncSetAttribute(gemm smem)", __FILE__, __LINE__);
@@ -441,20 +447,26 @@ int yv_gemm_launch(const void *A, const void *W, int M, int N, int K, const Gemm
   YV_REQUIRE(!(lnfold && (extra || resid || ep.out_f32)) && !(resid && (extra || ep.gelu || ep.out_f32)),
              "yv_gemm: unsupported epilogue combination");
   YV_REQUIRE(!lnfold || (ep.col_s && ep.ln_dim > 0), "yv_gemm: folded LayerNorm needs col_s and ln_dim");
-  YV_REQUIRE(!lnfold || ep.ln_slots >= 1, "yv_gemm: folded LayerNorm needs ln_slots >= 1");
+  YV_REQUIRE(!lnfold || (ep.ln_slots >= 1 && ep.ln_slots <= 16), "yv_gemm: folded LayerNorm needs 1 <= ln_slots <= 16");
   YV_REQUIRE(!resid || (ep.stats_out && N % 128 == 0), "yv_gemm: fused residual needs stats_out and N %% 128 == 0");
-#define YV_GO(G, F, X) gemm_bf16_kernel<G, F, X><<<grid, GEMM_THREADS, SMEM_BYTES, s>>>(tmA, tmB, ep, M, N, K)
+  // epilogue warps of the plain mode: 16 when the epilogue is heavy (GELU), else 8; YV_GEMM_EPI_WARPS=8|16 forces
+  // one (A/B timing).  The patch-embed mode keeps 8 (it spills at 96 registers), the statistics modes need 16.
+  static const int force = []() { const char *e = getenv("YV_GEMM_EPI_WARPS"); return e ? atoi(e) : 0; }();
+  const bool w16 = force == 16 || (force != 8 && ep.gelu);
+#define YV_GO(G, F, X, W) gemm_bf16_kernel<G, F, X, W><<<grid, gemm_threads(W), smem_bytes(W), s>>>(tmA, tmB, ep, M, N, K)
+#define YV_GO0(G, F) do { if (w16) YV_GO(G, F, 0, 16); else YV_GO(G, F, 0, 8); } while (0)
   if (lnfold) {
-    if (ep.gelu) YV_GO(true, false, 2); else YV_GO(false, false, 2);
+    if (ep.gelu) YV_GO(true, false, 2, 16); else YV_GO(false, false, 2, 16);
   } else if (resid) {
-    YV_GO(false, false, 3);
+    YV_GO(false, false, 3, 16);
   } else if (ep.gelu) {
-    if (ep.out_f32) { if (extra) YV_GO(true, true, 1); else YV_GO(true, true, 0); }
-    else { if (extra) YV_GO(true, false, 1); else YV_GO(true, false, 0); }
+    if (ep.out_f32) { if (extra) YV_GO(true, true, 1, 8); else YV_GO0(true, true); }
+    else { if (extra) YV_GO(true, false, 1, 8); else YV_GO0(true, false); }
   } else {
-    if (ep.out_f32) { if (extra) YV_GO(false, true, 1); else YV_GO(false, true, 0); }
-    else { if (extra) YV_GO(false, false, 1); else YV_GO(false, false, 0); }
+    if (ep.out_f32) { if (extra) YV_GO(false, true, 1, 8); else YV_GO0(false, true); }
+    else { if (extra) YV_GO(false, false, 1, 8); else YV_GO0(false, false); }
   }
+#undef YV_GO0
 #undef YV_GO
   YV_LAUNCH_CHECK();
   return YV_OK;

@@ -4,6 +4,10 @@
 #include <cuda_bf16.h>
 #include <cuda.h>
 
+// width of one row-statistics slot of the fused residual / folded LayerNorm modes (= the column group of one
+// epilogue warp)
+constexpr int GEMM_STAT_COLS = 64;
+
 struct GemmEpilogue {
   void *out;                        // [rows, N] bf16 or f32 (row remapped when group_rows > 0)
   const float *bias;                // [N] or null
@@ -23,7 +27,7 @@ struct GemmEpilogue {
   int ln_slots = 0;
   float ln_eps = 0.f;
   // Residual update fused into the producer GEMM (mode 3): x32[m, n] += acc + bias (fp32, in place),
-  // out = bf16(x32) and stats_out[m][n / 128] = (sum, sum of squares) of the new entries of that 128-column
+  // out = bf16(x32) and stats_out[m][n / GEMM_STAT_COLS] = (sum, sum of squares) of the new entries of that column
   // block (one slot per block: deterministic, nothing to zero).  null = off.
   float *x32 = nullptr;
   float *stats_out = nullptr;

@@ -89,7 +89,7 @@ struct VitWs {
   float *x32;
   __nv_bfloat16 *y, *d, *d2, *qkv, *h, *cls_ln;
   float *hidden;
-  float *stats[2];      // folded-LayerNorm pipeline: per-row partial (sum, sum of squares), dim / 128 slots
+  float *stats[2];      // folded-LayerNorm pipeline: per-row partial (sum, sum of squares), dim / GEMM_STAT_COLS slots
   size_t total;
 };
 
@@ -107,7 +107,7 @@ VitWs vit_ws(const yv_vit *m, void *base, int chunk) {
   w.h = (__nv_bfloat16 *)(b + o);      o = yv_align_up(o + M * c.mlp * 2, 1024);
   w.cls_ln = (__nv_bfloat16 *)(b + o); o = yv_align_up(o + (size_t)chunk * c.dim * 2, 1024);
   w.hidden = (float *)(b + o);         o = yv_align_up(o + (size_t)chunk * c.head_out * 4, 1024);
-  for (int i = 0; i < 2; ++i) { w.stats[i] = (float *)(b + o); o = yv_align_up(o + M * (c.dim / 128) * 8, 1024); }
+  for (int i = 0; i < 2; ++i) { w.stats[i] = (float *)(b + o); o = yv_align_up(o + M * (c.dim / GEMM_STAT_COLS) * 8, 1024); }
   w.total = o;
   return w;
 }
@@ -291,7 +291,7 @@ YV_EXPORT int yv_vit_forward(yv_vit_t *m, const void *patches_bf16, int n, float
       //     and the per-row partial (sum, sum of squares) the next folded LayerNorm needs.
       // HBM traffic per token per block drops from 49 KB to 43 KB and 24 kernel launches disappear.
       __nv_bfloat16 *xb = w.d;
-      const int slots = D / 128;
+      const int slots = D / GEMM_STAT_COLS;
       if ((rc = yv_row_stats_launch(w.x32, xb, w.stats[0], slots, M, D, s))) return rc;
       for (int i = 0; i < c.depth; ++i) {
         const std::string p = "model.blocks." + std::to_string(i) + ".";
