@@ -76,15 +76,16 @@ __device__ __forceinline__ void gelu4(float4 &v) {
 // position-table (patch embedding) and residual operands, MODE 2 the folded LayerNorm (row statistics +
 // column sums), MODE 3 the fused residual update (fp32 stream read-modify-write + bf16 copy + row statistics).
 constexpr int EPI_PLAIN = 0, EPI_EXTRA = 1, EPI_LNFOLD = 2, EPI_RESID = 3;
-template <bool GELU, bool OUT_F32, int MODE, int NEW>
+template <bool GELU, bool OUT_F32, int MODE, int NEW, bool DIRECT = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(gemm_threads(NEW), 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 const GemmEpilogue ep, int M, int N, int K) {
+                 const __grid_constant__ CUtensorMap tmD, const GemmEpilogue ep, int M, int N, int K) {
   constexpr int EPI_COLS = BN * 4 / NEW;       // columns per epilogue warp
   static_assert(MODE < EPI_LNFOLD || EPI_COLS == GEMM_STAT_COLS, "row-statistics slot = one epilogue warp's column group");
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  uint64_t *bars = (uint64_t *)(smem + (size_t)STAGES * STAGE_BYTES);
+  uint8_t *epi_smem = smem + (size_t)STAGES * STAGE_BYTES;        // 1024-byte aligned (TMA-store swizzle atoms)
+  uint64_t *bars = (uint64_t *)(epi_smem + (size_t)NEW * 32 * 16 * 4);
   uint64_t *full = bars, *empty = bars + STAGES;
   uint64_t *tfull = bars + 2 * STAGES, *tempty = bars + 2 * STAGES + 2;
   uint32_t *tmem_slot = (uint32_t *)(bars + 2 * STAGES + 4);
@@ -162,6 +163,81 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         umma_commit_pair(&tfull[as]);              // accumulator complete -> both CTAs' epilogues
       }
     }
+  } else if (warp >= 4 && DIRECT) {
+    // ===================== epilogue, TMA-store form (bf16 output): TMEM -> registers -> smem -> TMA =====================
+    // tcgen05.ld hands every thread one accumulator ROW.  Bias (a broadcast load per chunk), GELU and the bf16
+    // conversion happen on that layout; the thread drops its 32 columns (64 B) into the warp's 2 KB staging
+    // block in the 64-byte-swizzle pattern (conflict-free 16-byte stores) and one lane hands the 32 x 32 block to
+    // the TMA unit (cp.async.bulk.tensor store).  No LSU global stores at all: the staged form spends 8 line
+    // slots per store instruction on 32-byte row pieces, and those stores are what bounds the K = 768 GEMMs
+    // (YV_GEMM_DBG=1).  Rows >= M / columns >= N are clipped by the tensor map.
+    const int ew = warp - 4;
+    const int q = warp & 3;
+    const int cg = ew >> 2;
+    static_assert(!DIRECT || EPI_COLS == 64, "TMA-store epilogue: two 32-column halves per warp");
+    uint8_t *stg = epi_smem + ew * 2048;
+    const uint32_t sw = (uint32_t)(lane >> 1) & 3u;
+    uint32_t it = 0;
+    for (int tile = pair; tile < num_tiles; tile += npairs, ++it) {
+      const uint32_t as = it & 1u, aph = (it >> 1) & 1u;
+      const int m0 = (tile / n_tiles) * PM + (int)rank * BM, n0 = (tile % n_tiles) * BN;
+      const int row0 = m0 + q * 32;
+      const int col0 = n0 + cg * EPI_COLS;
+      mbar_wait(&tfull[as], aph);
+      tc_fence_after();
+      const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + cg * EPI_COLS;
+      uint32_t r[2][16];
+      if (ep.dbg != 2) tmem_ld_32x16(tbase, r[0]);
+#pragma unroll
+      for (int ch = 0; ch < 4; ++ch) {
+        if (ep.dbg == 2) break;
+        const int col = col0 + ch * 16;
+        float4 b4[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          b4[j] = (ep.bias && col + 4 * j < N) ? __ldg(reinterpret_cast<const float4 *>(ep.bias + col + 4 * j))
+                                               : make_float4(0.f, 0.f, 0.f, 0.f);
+        tmem_ld_wait();
+        if (ch + 1 < 4) tmem_ld_32x16(tbase + (ch + 1) * 16, r[(ch + 1) & 1]);
+        float4 v[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const uint32_t *rr = r[ch & 1] + 4 * j;
+          v[j] = make_float4(__uint_as_float(rr[0]) + b4[j].x, __uint_as_float(rr[1]) + b4[j].y,
+                             __uint_as_float(rr[2]) + b4[j].z, __uint_as_float(rr[3]) + b4[j].w);
+          if (GELU) gelu4(v[j]);
+        }
+        if ((ch & 1) == 0) {                       // the previous store of this warp has read the block
+          if (lane == 0) bulk_wait_read0();
+          __syncwarp();
+        }
+#pragma unroll
+        for (int j = 0; j < 2; ++j) {
+          __nv_bfloat162 h0 = __floats2bfloat162_rn(v[2 * j].x, v[2 * j].y), h1 = __floats2bfloat162_rn(v[2 * j].z, v[2 * j].w);
+          __nv_bfloat162 h2 = __floats2bfloat162_rn(v[2 * j + 1].x, v[2 * j + 1].y), h3 = __floats2bfloat162_rn(v[2 * j + 1].z, v[2 * j + 1].w);
+          uint4 u;
+          u.x = *reinterpret_cast<unsigned *>(&h0); u.y = *reinterpret_cast<unsigned *>(&h1);
+          u.z = *reinterpret_cast<unsigned *>(&h2); u.w = *reinterpret_cast<unsigned *>(&h3);
+          const uint32_t c16 = (uint32_t)((ch & 1) * 2 + j);             // 16-byte piece of the 64-byte row
+          *reinterpret_cast<uint4 *>(stg + lane * 64 + ((c16 ^ sw) << 4)) = u;
+        }
+        if (ch & 1) {
+          fence_proxy_async_smem();
+          __syncwarp();
+          if (lane == 0 && ep.dbg != 1 && col0 + (ch >> 1) * 32 < N && row0 < M) {
+            tma_store_2d(&tmD, stg, col0 + (ch >> 1) * 32, row0);
+            bulk_commit();
+          }
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) {
+        if (rank == 0) mbar_arrive(&tempty[as]);
+        else mbar_arrive_remote(&tempty[as], 0);
+      }
+    }
+    if (lane == 0) bulk_wait0();
   } else if (warp >= 4) {
     // ===================== epilogue: TMEM -> registers -> smem transpose -> global =====================
     // tcgen05.ld hands every thread one accumulator ROW (32 lanes x 16 columns per load).  Storing
@@ -173,7 +249,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int ew = warp - 4;
     const int q = warp & 3;                        // TMEM lane quarter this warp may access
     const int cg = ew >> 2;                        // column group of the tile (EPI_COLS columns)
-    float *stg = reinterpret_cast<float *>(smem + (size_t)STAGES * STAGE_BYTES + BAR_BYTES) + ew * (32 * 16);
+    float *stg = reinterpret_cast<float *>(epi_smem) + ew * (32 * 16);
     const int trow = lane >> 2, tseg = lane & 3;   // transposed role: row-in-group, 16-byte segment
     constexpr int NCH = EPI_COLS / 16;             // 16-column chunks per warp
     uint32_t it = 0;
@@ -387,6 +463,11 @@ void init_once() {
   e = cudaSuccess;
   YV_SET(false, false, 0, 8) YV_SET(false, true, 0, 8) YV_SET(true, false, 0, 8) YV_SET(true, true, 0, 8)
   YV_SET(false, false, 0, 16) YV_SET(false, true, 0, 16) YV_SET(true, false, 0, 16) YV_SET(true, true, 0, 16)
+#define YV_SETD(G, F)                                                                                         \
+  if (e == cudaSuccess)                                                                                     \
+    e = cudaFuncSetAttribute(gemm_bf16_kernel<G, F, 0, 16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes(16));
+  YV_SETD(false, false) YV_SETD(true, false)
+#undef YV_SETD
   YV_SET(false, false, 1, 8) YV_SET(false, true, 1, 8) YV_SET(true, false, 1, 8) YV_SET(true, true, 1, 8)
   YV_SET(false, false, 2, 16) YV_SET(true, false, 2, 16) YV_SET(false, false, 3, 16)
 #undef YV_SET
@@ -396,13 +477,15 @@ void init_once() {
 }
 
 // row-major bf16 [rows, cols]; box = box_rows x 64 columns, 128-byte swizzle, zero OOB fill
-int make_tmap(CUtensorMap *m, const void *ptr, uint64_t rows, uint64_t cols, uint32_t box_rows) {
+// (operands: box_cols = 64, 128-byte swizzle; TMA-store epilogue: 32 x 32 box, 64-byte swizzle)
+int make_tmap(CUtensorMap *m, const void *ptr, uint64_t rows, uint64_t cols, uint32_t box_rows, uint32_t box_cols = BK,
+              CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B) {
   cuuint64_t dims[2] = {cols, rows};
   cuuint64_t strides[1] = {cols * 2};
-  cuuint32_t box[2] = {(cuuint32_t)BK, box_rows};
+  cuuint32_t box[2] = {box_cols, box_rows};
   cuuint32_t estr[2] = {1, 1};
   CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(ptr), dims, strides, box, estr,
-                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     yv_set_error("cuTensorMapEncodeTiled failed (%d) for [%llu x %llu] bf16 at %p", (int)r, (unsigned long long)rows,
@@ -449,12 +532,21 @@ int yv_gemm_launch(const void *A, const void *W, int M, int N, int K, const Gemm
   YV_REQUIRE(!lnfold || (ep.col_s && ep.ln_dim > 0), "yv_gemm: folded LayerNorm needs col_s and ln_dim");
   YV_REQUIRE(!lnfold || (ep.ln_slots >= 1 && ep.ln_slots <= 16), "yv_gemm: folded LayerNorm needs 1 <= ln_slots <= 16");
   YV_REQUIRE(!resid || (ep.stats_out && N % 128 == 0), "yv_gemm: fused residual needs stats_out and N %% 128 == 0");
-  // epilogue warps of the plain mode: 16 when the epilogue is heavy (GELU), else 8; YV_GEMM_EPI_WARPS=8|16 forces
-  // one (A/B timing).  The patch-embed mode keeps 8 (it spills at 96 registers), the statistics modes need 16.
+  // epilogue warps of the plain mode: 16 (measured +1.2 % on the whole step against 8; fc1 179 -> 168 us);
+  // YV_GEMM_EPI_WARPS=8 selects the 8-warp form, YV_GEMM_TMA_STORE=0 turns the TMA-store epilogue of bf16 outputs off (A/B timing).  The patch-embed mode keeps 8 (it spills at 96 registers), the statistics modes need 16.
   static const int force = []() { const char *e = getenv("YV_GEMM_EPI_WARPS"); return e ? atoi(e) : 0; }();
-  const bool w16 = force == 16 || (force != 8 && ep.gelu);
-#define YV_GO(G, F, X, W) gemm_bf16_kernel<G, F, X, W><<<grid, gemm_threads(W), smem_bytes(W), s>>>(tmA, tmB, ep, M, N, K)
-#define YV_GO0(G, F) do { if (w16) YV_GO(G, F, 0, 16); else YV_GO(G, F, 0, 8); } while (0)
+  const bool w16 = force != 8;
+  static const bool direct = []() { const char *e = getenv("YV_GEMM_TMA_STORE"); return !(e && e[0] == '0'); }();
+  const bool tma_out = direct && !extra && !lnfold && !resid && !ep.out_f32;
+  CUtensorMap tmD = tmA;                       // placeholder unless the TMA-store epilogue runs
+  if (tma_out && (rc = make_tmap(&tmD, ep.out, (uint64_t)M, (uint64_t)N, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
+#define YV_GO(G, F, X, W) gemm_bf16_kernel<G, F, X, W><<<grid, gemm_threads(W), smem_bytes(W), s>>>(tmA, tmB, tmD, ep, M, N, K)
+#define YV_GO0(G, F)                                                                                                    \
+  do {                                                                                                                  \
+    if (tma_out) gemm_bf16_kernel<G, false, 0, 16, true><<<grid, gemm_threads(16), smem_bytes(16), s>>>(tmA, tmB, tmD, ep, M, N, K); \
+    else if (w16) YV_GO(G, F, 0, 16);                                                                                   \
+    else YV_GO(G, F, 0, 8);                                                                                             \
+  } while (0)
   if (lnfold) {
     if (ep.gelu) YV_GO(true, false, 2, 16); else YV_GO(false, false, 2, 16);
   } else if (resid) {
