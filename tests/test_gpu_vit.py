@@ -206,3 +206,22 @@ def test_submit_host_pipelined_batches(full_model):
         r = pend.result()
         assert torch.equal(outs[k], refs[k]) and torch.equal(r.records.cpu(), refs[k]), k
         pend = nxt
+
+
+def test_submit_host_launch_ahead(full_model):
+    """Serving-loop order of bench.py's e2e: batch k+1 is submitted AND launched (its ViT queued behind batch
+    k's) before result(k); every batch still gets exactly the records, logits and top-1 of its resident run."""
+    m, _ = full_model
+    hp = HotPath(m, HotPathConfig())
+    batches = [(synth.make_head(5, 80, 8400, n_obj=2 + i % 2, n_jit=10, seed=60 + i).pin_memory(),
+                synth.make_images(5, 640, 640, seed=70 + i).pin_memory()) for i in range(4)]
+    refs = [hp(h.to(DEV), im.to(DEV)) for h, im in batches]
+    outs = [torch.empty(5, 100, 8).pin_memory() for _ in range(4)]
+    pend = hp.submit_host(*batches[0], outs[0], device=DEV, slices=2).launch()
+    for k in range(4):
+        nxt = hp.submit_host(*batches[k + 1], outs[k + 1], device=DEV, slices=2).launch() if k < 3 else None
+        r = pend.result()
+        assert r is pend.result()                                  # idempotent
+        assert torch.equal(outs[k], refs[k].records.cpu()) and torch.equal(r.records, refs[k].records), k
+        assert r.n_crops == refs[k].n_crops and torch.equal(r.top1, refs[k].top1) and torch.equal(r.logits, refs[k].logits)
+        pend = nxt

@@ -198,7 +198,16 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           b4[j] = (ep.bias && col + 4 * j < N) ? __ldg(reinterpret_cast<const float4 *>(ep.bias + col + 4 * j))
                                                : make_float4(0.f, 0.f, 0.f, 0.f);
         tmem_ld_wait();
-        if (ch + 1 < 4) tmem_ld_32x16(tbase + (ch + 1) * 16, r[(ch + 1) & 1]);
+        if (ch + 1 < 4) {
+          tmem_ld_32x16(tbase + (ch + 1) * 16, r[(ch + 1) & 1]);
+        } else {                                   // the accumulator is in registers: hand it back to the MMA warp now
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) {
+            if (rank == 0) mbar_arrive(&tempty[as]);
+            else mbar_arrive_remote(&tempty[as], 0);
+          }
+        }
         float4 v[4];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
@@ -230,11 +239,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           }
         }
       }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) {
-        if (rank == 0) mbar_arrive(&tempty[as]);
-        else mbar_arrive_remote(&tempty[as], 0);
+      if (ep.dbg == 2) {                           // (measurement mode: nothing was read)
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) {
+          if (rank == 0) mbar_arrive(&tempty[as]);
+          else mbar_arrive_remote(&tempty[as], 0);
+        }
       }
     }
     if (lane == 0) bulk_wait0();

@@ -158,8 +158,9 @@ class HotPath:
         """Asynchronous half of :meth:`run_host`: enqueues the sliced upload and the per-slice decode ->
         custom_nms -> crop list on the high-priority front stream and returns at once.  ``.result()`` of the
         returned handle runs the ViT part and delivers the records.  Two staging slots alternate, so a server
-        loop ``nxt = submit_host(batch i+1); cur.result(); cur = nxt`` uploads batch i+1 while batch i is in the
-        ViT -- the end-to-end rate then equals the resident rate (bench.py's `e2e`)."""
+        loop ``nxt = submit_host(batch i+1).launch(); cur.result(); cur = nxt`` uploads batch i+1 while batch i is
+        in the ViT and has batch i+1's ViT queued behind it -- the end-to-end rate then approaches the resident
+        rate (bench.py's `e2e`).  At most two batches may be in flight (two slots)."""
         if self.model is None:
             raise ValueError("the host-buffer path needs a classifier")
         if head_h.is_cuda or imgs_h.is_cuda:
@@ -218,10 +219,17 @@ class PendingHost:
         self.hp, self.st, self.cls, self.bounds, self.dev = hp, st, cls, bounds, dev
         self.out_records_h, self.vit_chunk, self.ramp, self.front = out_records_h, vit_chunk, ramp, front
         self._res = None
+        self._launched = False
+        self._done = None
 
-    def result(self) -> HotPathResult:
-        if self._res is not None:
-            return self._res
+    def launch(self) -> "PendingHost":
+        """Enqueues the rest of the batch on the caller's stream -- per slice: wait for its crop count (a 4-byte
+        host sync on work that ran on the front stream), crop-resize into the patch buffer, ViT over fixed chunks;
+        then the records and their download -- and returns without waiting for the GPU.  A serving loop calls
+        ``submit_host(k+1).launch()`` BEFORE ``result()`` of batch k, so the GPU already holds batch k+1's work
+        when batch k finishes (no idle gap while the host prepares the next batch)."""
+        if self._launched:
+            return self
         hp, st, cls, bounds, dev = self.hp, self.st, self.cls, self.bounds, self.dev
         c, model, vit_chunk = hp.cfg, hp.model, self.vit_chunk
         slices, B = len(cls), bounds[-1]
@@ -264,15 +272,25 @@ class PendingHost:
             ops.pack_results(cls[i], st["top1"][offs[i]:] if total else None, out=rec[a:b])
         if self.out_records_h is not None:
             self.out_records_h.copy_(rec, non_blocking=True)
-        if st["free"] is None:
-            st["free"] = torch.cuda.Event()
-        st["free"].record(main)                # the slot's staging buffers may be overwritten after this point
-        main.synchronize()
-        # results are copied out of the slot's crop-indexed buffers: the next-but-one submit reuses them
+        # results are copied out of the slot's crop-indexed buffers (the next-but-one submit reuses them)
         self._res = HotPathResult(records=rec, det_count=torch.cat([cl.det_count for cl in cls]), n_crops=total,
                                   logits=st["logits"][:total].clone() if total else None,
                                   top1=st["top1"][:total].clone() if total else None)
+        if st["free"] is None:
+            st["free"] = torch.cuda.Event()
+        st["free"].record(main)                # the slot's staging buffers may be overwritten after this point
+        self._done = torch.cuda.Event()
+        self._done.record(main)
         self.cls = None
+        self._launched = True
+        return self
+
+    def result(self) -> HotPathResult:
+        """Waits for this batch only (an event, not the whole stream: a later batch may already be queued)."""
+        self.launch()
+        if self._done is not None:
+            self._done.synchronize()
+            self._done = None
         return self._res
 
 
