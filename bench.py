@@ -39,8 +39,8 @@ IMG = 640
 SEED = 20240410 + 1
 FLOP_PER_CROP = 35.128e9           # SURVEY.md §8d (ViT-B/16 + heads)
 # ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch, mean of the four block GEMMs
-# at M = 50 432 (profiles/r01_vit_ncu_v4.md): (378.6 + 263.8 + 117.5 + 343.1) / 4 MB
-GEMM_DRAM_BYTES_PER_LAUNCH = 275.8e6
+# at M = 50 432 (profiles/r01_vit_ncu_v5.md): (380.2 + 261.6 + 118.1 + 339.5) / 4 MB
+GEMM_DRAM_BYTES_PER_LAUNCH = 274.9e6
 
 
 def parse():
@@ -289,7 +289,7 @@ def run_ours(args):
             "roofline": {"bound": "tensor", "kernel": "gemm_bf16_kernel (tcgen05)", "achieved": achieved,
                          "peak": tf_sus, "unit": "TFLOP/s", "frac": achieved / tf_sus, "traffic": GEMM_DRAM_BYTES_PER_LAUNCH,
                          "traffic_note": "mean dram read+write bytes of the qkv/proj/fc1/fc2 launches of a 256-crop "
-                                         "chunk, ncu --set full (profiles/r01_vit_ncu_v4.md)",
+                                         "chunk, ncu --set full (profiles/r01_vit_ncu_v5.md)",
                          "peak_source": f"{which} bf16_tflops_sustained (kernel timed inside a long step)",
                          "launches_per_step": g["launches"] / args.steps,
                          "flops_per_launch": per_launch_flops, "ms_per_launch": per_launch_ms,
