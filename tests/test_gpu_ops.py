@@ -273,3 +273,26 @@ def test_build_crops_vs_oracle(B, S, max_det, cap_frac):
         rank += int(ok)
     assert bool((det_crop[~filled] == -1).all()) and bool((det_label[~filled] == -1).all())
     assert bool((det_box[~filled] == 0).all()) and bool((det_score[~filled] == 0).all())
+
+
+def test_crop_image_edges_and_unaligned_buffers():
+    """The bilinear gather reads two RGB pixels as three aligned 32-bit words: crops that end on the last
+    pixel of the last image (buffer tail -> byte path), odd image sizes (row starts at every alignment, total
+    size not a multiple of 4), 1-pixel-wide / 1-pixel-high crops (both taps the same pixel), and an image
+    tensor whose base is not 4-byte aligned (byte-load kernel) all stay bit-exact against the oracle."""
+    H, W = 37, 53
+    imgs = synth.make_images(3, H, W, seed=91)
+    boxes = torch.tensor([[0, 0, W, H], [W - 1, H - 1, W, H], [W - 2, H - 3, W, H], [0, H - 1, W, H],
+                          [W - 1, 0, W, H], [5, 7, 6, 30], [11, 13, 40, 14], [1, 1, 2, 2], [W - 7, H - 5, W - 1, H - 1]],
+                         dtype=torch.int32)
+    idx = torch.tensor([2, 2, 2, 2, 2, 0, 1, 1, 2], dtype=torch.int32)
+    n = boxes.shape[0]
+    raw = torch.zeros(imgs.numel() + 8, dtype=torch.uint8, device=DEV)
+    for off in (0, 1, 2, 3):                                   # off = 0: word loads; 1..3: unaligned base
+        view = raw[off:off + imgs.numel()].view(imgs.shape)
+        view.copy_(imgs)
+        for interp in ("bilinear", "nearest"):
+            got = ops.crop_resize(view, boxes.to(DEV), idx.to(DEV), n, interp, 32, 16, "chw").cpu()
+            for i in range(n):
+                ref = O.crop_resize_norm(imgs[idx[i]].numpy(), boxes[i].numpy(), 32, interp)
+                assert np.array_equal(got[i].numpy(), ref), (off, interp, i)

@@ -295,7 +295,14 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
 // (32 KB) = 245 KB = 3.8k cycles -- exactly the measured period, independent of the number of softmax
 // warps (2/3/4/5/6 column groups: 121/115/118/136/152 us).  Reading S once (scores held in registers
 // between the passes) cuts the softmax to 3.1k cycles but needs 96+ registers per thread; with the output
-// duty folded into the same warps it spilled and was slower.  Next: 512-thread layout with 128 registers.
+// duty folded into the same warps it spilled and was slower.  A clean single-read version was then built with
+// warpgroup register re-allocation (setmaxnreg: TMA/MMA group 40, output group 56, the four softmax groups 96
+// registers = the 61 440 registers a 768-thread CTA owns; the inc must sit at the top of the role branch for
+// ptxas to honour it, and it can only draw on the CTA's own pool) and the tail-key mask applied once as -inf:
+// correct, no spills, 118 us per 268-crop launch -- the same as this two-pass kernel.  So the TMEM read port is
+// NOT what bounds the softmax; what remains per 128 x 208 tile and SM sub-partition is 208 MUFU.EX2 warp
+// instructions at 8 cycles (1664 cycles) plus the bf16 packs and ~1000 issue slots in a dependent chain
+// (max -> smem exchange -> exp -> pack -> tcgen05.st).  The simpler two-pass kernel is kept.
 constexpr int AP_THREADS = 24 * 32;              // TMA, MMA, alloc, spare, 16 softmax, 4 output
 constexpr int AP_Q_BYTES = 256 * AT_DH * 2;         // 32 KB: both query tiles of a unit
 constexpr int AP_STAGE = AP_Q_BYTES + 2 * AT_KV_BYTES;   // 96 KB
