@@ -57,4 +57,17 @@ for interp in ("bilinear", "nearest"):
     ms = timed(lambda: ops.crop_resize(imgs, cb, ci, 256, interp, 224, 16, "patch"))
     wb = 256 * 224 * 224 * 3 * 2
     out[f"cfg3_crop_{interp}"] = {"ms": ms, "write_GBs": wb / ms / 1e6}
+del imgs
+# row f1: raw Detect-head decode (DFL + anchors fused into the filter), batch 128: the 80 class rows of every
+# anchor are streamed (algorithmic bytes), the 64 DFL rows are touched for kept anchors only
+raw = synth.make_raw_head(128, 80, synth.LEVELS_640, n_obj=4, seed=11).to(dev)
+ms = timed(lambda: ops.decode_filter_raw(raw, synth.LEVELS_640, 0.35))
+out["f1_raw_decode_b128"] = {"ms": ms, "GBs": 128 * 80 * 8400 * 4 / ms / 1e6, "tensor_GB": raw.numel() * 4 / 1e9}
+del raw
+# row f2: letterbox + BGR->RGB + /255 + CHW blob of the detector input, 64 frames 1080x1920 -> 640x640
+frames = synth.make_images(64, 1080, 1920, seed=12).to(dev)
+ms = timed(lambda: ops.letterbox_blob(frames, (640, 640), bgr=True))
+wb = 64 * 3 * 640 * 640 * 4
+out["f2_letterbox_64x1080p"] = {"ms": ms, "read_GB": frames.numel() / 1e9, "write_GB": wb / 1e9,
+                                "GBs": (frames.numel() + wb) / ms / 1e6}
 print(json.dumps(out))
