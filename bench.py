@@ -51,6 +51,8 @@ def parse():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--batch", type=int, default=B_PER_GPU, help="images per GPU")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--e2e-vit-chunk", type=int, default=0,
+                    help="crops per ViT pass in the host-buffer loop (0 = the API's default: auto)")
     return ap.parse_args()
 
 
@@ -215,11 +217,12 @@ def run_ours(args):
         (pinned head + images -> sliced upload + detection on the front stream) is issued before
         result(batch k) (ViT + records -> pinned host buffer), so every step's 1.04 GB upload and its record
         download are inside the timed region but overlap the previous step's ViT."""
-        pend = hp.submit_host(head_h, imgs_h, rec_h2[0], device=dev).launch()
+        pend = hp.submit_host(head_h, imgs_h, rec_h2[0], device=dev, vit_chunk=args.e2e_vit_chunk or None).launch()
         r = None
         for k in range(steps):
             # batch k+1: upload + detection on the front stream, its ViT queued behind batch k's
-            nxt = hp.submit_host(head_h, imgs_h, rec_h2[(k + 1) & 1], device=dev).launch() if k + 1 < steps else None
+            nxt = hp.submit_host(head_h, imgs_h, rec_h2[(k + 1) & 1], device=dev,
+                                 vit_chunk=args.e2e_vit_chunk or None).launch() if k + 1 < steps else None
             r = pend.result()
             if world > 1:          # the gather runs beside batch k+1's queued ViT, not behind it
                 with torch.cuda.stream(gstream):

@@ -154,7 +154,7 @@ class HotPath:
         st["patches"], st["logits"], st["top1"], st["cap"] = new[0], new[1], new[2], cap
 
     def submit_host(self, head_h: torch.Tensor, imgs_h: torch.Tensor, out_records_h: torch.Tensor | None = None,
-                    device="cuda:0", slices: int = 8, vit_chunk: int = 256, ramp=()) -> "PendingHost":
+                    device="cuda:0", slices: int = 8, vit_chunk: int | None = None, ramp=()) -> "PendingHost":
         """Asynchronous half of :meth:`run_host`: enqueues the sliced upload and the per-slice decode ->
         custom_nms -> crop list on the high-priority front stream and returns at once.  ``.result()`` of the
         returned handle runs the ViT part and delivers the records.  Two staging slots alternate, so a server
@@ -196,14 +196,14 @@ class HotPath:
         return PendingHost(self, st, cls, bounds, dev, out_records_h, vit_chunk, ramp, front)
 
     def run_host(self, head_h: torch.Tensor, imgs_h: torch.Tensor, out_records_h: torch.Tensor | None = None,
-                 device="cuda:0", slices: int = 8, vit_chunk: int = 256, ramp=()) -> HotPathResult:
+                 device="cuda:0", slices: int = 8, vit_chunk: int | None = None, ramp=()) -> HotPathResult:
         """The same path from HOST buffers (pinned memory recommended): head [B,4+nc,A] f32 and images
         [B,H,W,3] u8 on the CPU -> records on the CPU (`out_records_h`, pinned, optional).
 
         The batch is cut into `slices` image slices.  A high-priority "front" stream uploads slice
         after slice and runs decode -> custom_nms -> crop list on each as soon as it has landed; the
         caller's stream gathers the crops of every finished slice into one patch buffer and runs
-        the ViT over fixed `vit_chunk`-crop chunks as soon as enough crops exist, so the upload of
+        the ViT over `vit_chunk`-crop chunks as soon as enough crops exist (None = auto, see launch()), so the upload of
         slice i+1.. overlaps the ViT of slice ..i (`ramp` = smaller first chunks, e.g. (64, 128); measured
         not to pay off: small chunks run the GEMMs at half efficiency).  Host syncs: one 4-byte crop count per
         slice (it sizes the ViT launches) and the final record download.  = submit_host(...).result().
@@ -232,6 +232,12 @@ class PendingHost:
             return self
         hp, st, cls, bounds, dev = self.hp, self.st, self.cls, self.bounds, self.dev
         c, model, vit_chunk = hp.cfg, hp.model, self.vit_chunk
+        if vit_chunk is None:
+            # auto: while an earlier batch is still in the ViT this batch's upload is hidden anyway, so its ViT
+            # runs as ONE pass once all slices are in (fewest launches, no remainder pass: 43.5 vs 46.7 ms per
+            # batch); on an idle GPU the ViT starts on 256-crop chunks as soon as the first slices have landed
+            prev = getattr(hp, "_last_done", None)
+            vit_chunk = (1 << 30) if (prev is not None and not prev.query()) else 256
         slices, B = len(cls), bounds[-1]
         main = torch.cuda.current_stream(dev)
         total = done = 0
@@ -281,6 +287,7 @@ class PendingHost:
         st["free"].record(main)                # the slot's staging buffers may be overwritten after this point
         self._done = torch.cuda.Event()
         self._done.record(main)
+        hp._last_done = self._done
         self.cls = None
         self._launched = True
         return self

@@ -58,7 +58,6 @@ class ViTModel:
             check(load().yv_vit_create(ctypes.byref(c), ctypes.byref(h)), "yv_vit_create")
         self._h = h
         self._ws = None
-        self._ws_crops = 0
 
     def __del__(self):
         h = getattr(self, "_h", None)
@@ -84,10 +83,9 @@ class ViTModel:
         return self
 
     def _workspace(self, n: int) -> torch.Tensor:
-        if self._ws is None or self._ws_crops < min(n, 256):
-            nb = load().yv_vit_workspace_bytes(self._h, n)
+        nb = load().yv_vit_workspace_bytes(self._h, n)          # sized for min(n, the library's chunk)
+        if self._ws is None or self._ws.numel() < nb:
             self._ws = torch.empty(nb, dtype=torch.uint8, device=self.device)
-            self._ws_crops = min(n, 256)
         return self._ws
 
     def forward_patches(self, patches: torch.Tensor, n: int, return_hidden: bool = False,
