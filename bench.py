@@ -49,7 +49,11 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--batch", type=int, default=B_PER_GPU, help="images per GPU")
+    ap.add_argument("--batch", type=int, default=0, help="images per GPU (0 = the workload's own)")
+    ap.add_argument("--workload", default="north_star", choices=["north_star", "cfg4"],
+                    help="north_star: YOLOv8n-640, 256 images per GPU (weak scaling; the driver's line). "
+                         "cfg4: BASELINE.json configs[3], YOLOv8s-1280 head [512,84,33600] + 512 images "
+                         "1280x1280 sharded over the ranks (strong scaling: 512 / N images per GPU)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--e2e-vit-chunk", type=int, default=0,
                     help="crops per ViT pass in the host-buffer loop (0 = the API's default: auto)")
@@ -64,7 +68,23 @@ def peaks():
     return 6650.0, 1590.0, 1400.0, "fallback"
 
 
+def set_workload(args):
+    """Select the synthetic workload; returns the scaling kind ("weak" / "strong")."""
+    global ANCHORS, IMG
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if args.workload == "cfg4":
+        ANCHORS, IMG = 33600, 1280                 # 160^2 + 80^2 + 40^2 anchors of a 1280x1280 input
+        args.batch = args.batch or 512 // world
+        return "strong"
+    args.batch = args.batch or B_PER_GPU
+    return "weak"
+
+
 def workload_name(batch):
+    if IMG == 1280:
+        return (f"cfg4: YOLOv8s-1280 head [{batch},{4 + NC},{ANCHORS}] f32 + {batch} images {IMG}x{IMG} u8 per GPU "
+                f"(512 images over the ranks), {N_OBJ} objects x {N_JIT} candidates/img -> conf .35 -> custom_nms "
+                f".45 -> dilate a=0.1 -> 224 bilinear crop -> ViT-B/16 (+wrapper head)")
     return (f"YOLOv8n-640 head [{batch},{4 + NC},{ANCHORS}] f32 + {batch} images {IMG}x{IMG} u8 per GPU, "
             f"{N_OBJ} objects x {N_JIT} candidates/img -> conf .35 -> custom_nms .45 -> dilate a=0.1 -> "
             f"224 bilinear crop -> ViT-B/16 (+wrapper head)")
@@ -170,7 +190,7 @@ def run_reference(args):
     print(json.dumps({
         "impl": "reference", "metric": "images/sec detect-post->NMS->crop->ViT-B/16", "value": val,
         "unit": "images/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
         "dtype": "f32", "data": "synthetic", "config": {"workload": workload_name(args.batch), "sample": sample},
         "cpu_baseline": {"value": val, "unit": "images/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -284,10 +304,11 @@ def run_ours(args):
         out = {
             "metric": "images/sec detect-post->NMS->crop->ViT-B/16", "value": world * B * args.steps / (ms * 1e-3),
             "unit": "images/s", "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
-            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic",
             "config": {"workload": workload_name(B), "images_per_gpu": B, "crops_per_gpu": n_crops,
-                       "l2": "inputs larger than L2 (head 722 MB + images 315 MB per step)",
+                       "l2": f"inputs larger than L2 (head {head_h.numel() * 4 / 1e6:.0f} MB + images "
+                             f"{imgs_h.numel() / 1e6:.0f} MB per step)",
                        "parallelism": f"batch-sharded x{world}, final NCCL all-gather of records"},
             "roofline": {"bound": "tensor", "kernel": "gemm_bf16_kernel (tcgen05)", "achieved": achieved,
                          "peak": tf_sus, "unit": "TFLOP/s", "frac": achieved / tf_sus, "traffic": GEMM_DRAM_BYTES_PER_LAUNCH,
@@ -317,6 +338,7 @@ def run_ours(args):
 
 if __name__ == "__main__":
     a = parse()
+    a.scaling = set_workload(a)
     if a.impl == "reference":
         run_reference(a)
     else:
