@@ -38,9 +38,10 @@ ANCHORS = 8400
 IMG = 640
 SEED = 20240410 + 1
 FLOP_PER_CROP = 35.128e9           # SURVEY.md §8d (ViT-B/16 + heads)
-# ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch, mean of the four block GEMMs
-# at M = 50 432 (profiles/r01_vit_ncu_v5.md): (380.2 + 261.6 + 118.1 + 339.5) / 4 MB
-GEMM_DRAM_BYTES_PER_LAUNCH = 274.9e6
+# ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch, mean of the four block GEMMs of the
+# one-pass ViT at M = 1072 crops x 197 = 211 184 rows (profiles/r01_vit_ncu_v7.md): (1624 + 1250 + 610 + 1576) / 4 MB
+# = 5.99 KB per token row; scaled by the run's own row count below (the driver's workload gives exactly 1072 crops)
+GEMM_DRAM_BYTES_PER_ROW = 1265e6 / 211184
 
 
 def parse():
@@ -311,9 +312,11 @@ def run_ours(args):
                              f"{imgs_h.numel() / 1e6:.0f} MB per step)",
                        "parallelism": f"batch-sharded x{world}, final NCCL all-gather of records"},
             "roofline": {"bound": "tensor", "kernel": "gemm_bf16_kernel (tcgen05)", "achieved": achieved,
-                         "peak": tf_sus, "unit": "TFLOP/s", "frac": achieved / tf_sus, "traffic": GEMM_DRAM_BYTES_PER_LAUNCH,
-                         "traffic_note": "mean dram read+write bytes of the qkv/proj/fc1/fc2 launches of a 256-crop "
-                                         "chunk, ncu --set full (profiles/r01_vit_ncu_v5.md)",
+                         "peak": tf_sus, "unit": "TFLOP/s", "frac": achieved / tf_sus,
+                         "traffic": GEMM_DRAM_BYTES_PER_ROW * n_crops * 197,
+                         "traffic_note": "mean dram read+write bytes of the qkv/proj/fc1/fc2 launches of the one-pass "
+                                         "ViT (M = crops x 197 rows), ncu --set full (profiles/r01_vit_ncu_v7.md: "
+                                         "1265 MB at 1072 crops = the algorithmic bytes)",
                          "peak_source": f"{which} bf16_tflops_sustained (kernel timed inside a long step)",
                          "launches_per_step": g["launches"] / args.steps,
                          "flops_per_launch": per_launch_flops, "ms_per_launch": per_launch_ms,
