@@ -4,6 +4,7 @@
 //   K7  softmax attention per (crop, head) on tensor cores (mma.sync m16n8k16 bf16 -> f32,
 //       ldmatrix-fed, online softmax in registers)
 //   K8  class-token rows, and the Network_Wrapper head (ReLU -> 1000x128 -> ReLU -> 128x5) + argmax
+#include <cstdlib>
 #include "common.cuh"
 #include "vit_ops.cuh"
 
@@ -13,7 +14,10 @@ namespace {
 constexpr int LN_WARPS = 8;
 constexpr int LN_MAXCH = 4;    // dim <= 1024 (chunks of 256 = 32 lanes x 8 elements)
 
-template <bool XF32>
+// CS: streaming cache operators on the operands nobody re-reads soon (the fp32 stream and the consumed deltas:
+// ld.global.cs / st.global.cs = evict-first), so that y -- the A operand of the GEMM launched next -- is what
+// stays in the 126 MB L2.
+template <bool XF32, bool CS = false>
 __global__ void __launch_bounds__(LN_WARPS * 32)
 layernorm_kernel(const void *xv, size_t in_stride, const __nv_bfloat16 *__restrict__ delta,
                  const __nv_bfloat16 *__restrict__ delta2, size_t delta_stride, int writeback, const float *__restrict__ gamma, const float *__restrict__ beta,
@@ -29,7 +33,7 @@ layernorm_kernel(const void *xv, size_t in_stride, const __nv_bfloat16 *__restri
       const int e = c * 256 + lane * 8;
       if (XF32) {
         const float4 *p = reinterpret_cast<const float4 *>((const float *)xv + (size_t)row * in_stride + e);
-        const float4 a = p[0], b = p[1];
+        const float4 a = CS ? __ldcs(p) : p[0], b = CS ? __ldcs(p + 1) : p[1];
         v[c][0] = a.x; v[c][1] = a.y; v[c][2] = a.z; v[c][3] = a.w;
         v[c][4] = b.x; v[c][5] = b.y; v[c][6] = b.z; v[c][7] = b.w;
       } else {
@@ -43,7 +47,8 @@ layernorm_kernel(const void *xv, size_t in_stride, const __nv_bfloat16 *__restri
         }
       }
       if (delta) {     // fused residual add: x += delta (the bf16 output of the preceding proj / fc2 GEMM)
-        const uint4 u = *reinterpret_cast<const uint4 *>(delta + (size_t)row * delta_stride + e);
+        const uint4 *dp = reinterpret_cast<const uint4 *>(delta + (size_t)row * delta_stride + e);
+        const uint4 u = CS ? __ldcs(dp) : *dp;
         const __nv_bfloat162 *h = reinterpret_cast<const __nv_bfloat162 *>(&u);
 #pragma unroll
         for (int k = 0; k < 4; ++k) {
@@ -52,7 +57,8 @@ layernorm_kernel(const void *xv, size_t in_stride, const __nv_bfloat16 *__restri
           v[c][2 * k + 1] += f.y;
         }
         if (delta2) {    // second pending delta ((x + delta) + delta2, the order of two separate adds)
-          const uint4 u2 = *reinterpret_cast<const uint4 *>(delta2 + (size_t)row * delta_stride + e);
+          const uint4 *dp2 = reinterpret_cast<const uint4 *>(delta2 + (size_t)row * delta_stride + e);
+          const uint4 u2 = CS ? __ldcs(dp2) : *dp2;
           const __nv_bfloat162 *h2 = reinterpret_cast<const __nv_bfloat162 *>(&u2);
 #pragma unroll
           for (int k = 0; k < 4; ++k) {
@@ -63,8 +69,13 @@ layernorm_kernel(const void *xv, size_t in_stride, const __nv_bfloat16 *__restri
         }
         if (XF32 && writeback) {
           float4 *p = reinterpret_cast<float4 *>((float *)const_cast<void *>(xv) + (size_t)row * in_stride + e);
-          p[0] = make_float4(v[c][0], v[c][1], v[c][2], v[c][3]);
-          p[1] = make_float4(v[c][4], v[c][5], v[c][6], v[c][7]);
+          if (CS) {
+            __stcs(p, make_float4(v[c][0], v[c][1], v[c][2], v[c][3]));
+            __stcs(p + 1, make_float4(v[c][4], v[c][5], v[c][6], v[c][7]));
+          } else {
+            p[0] = make_float4(v[c][0], v[c][1], v[c][2], v[c][3]);
+            p[1] = make_float4(v[c][4], v[c][5], v[c][6], v[c][7]);
+          }
         }
       }
     }
@@ -224,7 +235,9 @@ int yv_ln2_launch(const void *x, bool x_f32, size_t in_stride, const __nv_bfloat
   const int grid = (rows + LN_WARPS - 1) / LN_WARPS;
   YV_REQUIRE(!delta2 || delta, "layernorm: delta2 needs delta");
   YvProf prof(YV_K_LN, s, (double)rows * dim * ((x_f32 ? 6.0 : 4.0) + (delta ? 2.0 : 0.0) + (delta2 ? 2.0 : 0.0) + (delta && writeback ? 4.0 : 0.0)));
-  if (x_f32) layernorm_kernel<true><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, delta, delta2, delta_stride, writeback ? 1 : 0, gamma, beta, y, rows, dim, eps);
+  static const bool cs = [] { const char *e = getenv("YV_LN_STREAM"); return e && e[0] == '1'; }();   // A/B switch
+  if (x_f32 && cs) layernorm_kernel<true, true><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, delta, delta2, delta_stride, writeback ? 1 : 0, gamma, beta, y, rows, dim, eps);
+  else if (x_f32) layernorm_kernel<true><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, delta, delta2, delta_stride, writeback ? 1 : 0, gamma, beta, y, rows, dim, eps);
   else layernorm_kernel<false><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, delta, delta2, delta_stride, 0, gamma, beta, y, rows, dim, eps);
   YV_LAUNCH_CHECK();
   return YV_OK;
