@@ -1,15 +1,16 @@
 #!/bin/bash
-# A/B on one box: LayerNorm with streaming cache operators (YV_LN_STREAM=1) vs default, alternating runs
+# A/B on one box: LayerNorm with streaming cache operators (YV_LN_STREAM=1) and / or reversed row walk
+# (YV_LN_REVERSE=1) vs default, alternating runs
 mkdir -p gpurun_out
 timeout 300 python -m pytest tests/test_gpu_vit.py -q -m gpu --timeout=300 -p no:cacheprovider -x 2>&1 | tail -n 3
-YV_LN_STREAM=1 timeout 300 python -m pytest tests/test_gpu_vit.py -q -m gpu --timeout=300 -p no:cacheprovider -x 2>&1 | tail -n 3
+YV_LN_STREAM=1 YV_LN_REVERSE=1 timeout 300 python -m pytest tests/test_gpu_vit.py -q -m gpu --timeout=300 -p no:cacheprovider -x 2>&1 | tail -n 3
 for i in 1 2; do
-  for v in 0 1; do
-    YV_LN_STREAM=$v timeout 300 python bench.py --no-cpu-baseline --steps 8 > gpurun_out/ln_ab_${v}_$i.json 2> gpurun_out/ln_ab.err
+  for v in 00 10 01 11; do
+    YV_LN_STREAM=${v:0:1} YV_LN_REVERSE=${v:1:1} timeout 300 python bench.py --no-cpu-baseline --steps 8 > gpurun_out/ln_ab_${v}_$i.json 2> gpurun_out/ln_ab.err
     python - <<PY
 import json
 d=json.loads(open('gpurun_out/ln_ab_${v}_$i.json').read().strip().splitlines()[-1])
-print('YV_LN_STREAM=$v run $i', round(d['value'],1), 'e2e', round(d['e2e']['value'],1), 'ln', d['stages_ms_per_step']['layernorm'], 'gemm', d['stages_ms_per_step']['gemm_tcgen05'], 'attn', d['stages_ms_per_step']['attention'], d['clocks']['sm_mhz'])
+print('YV_LN_STREAM/REVERSE=$v run $i', round(d['value'],1), 'e2e', round(d['e2e']['value'],1), 'ln', d['stages_ms_per_step']['layernorm'], 'gemm', d['stages_ms_per_step']['gemm_tcgen05'], 'attn', d['stages_ms_per_step']['attention'], d['clocks']['sm_mhz'])
 PY
   done
 done

@@ -21,9 +21,12 @@ template <bool XF32, bool CS = false>
 __global__ void __launch_bounds__(LN_WARPS * 32)
 layernorm_kernel(const void *xv, size_t in_stride, const __nv_bfloat16 *__restrict__ delta,
                  const __nv_bfloat16 *__restrict__ delta2, size_t delta_stride, int writeback, const float *__restrict__ gamma, const float *__restrict__ beta,
-                 __nv_bfloat16 *__restrict__ y, int rows, int dim, float eps) {
+                 __nv_bfloat16 *__restrict__ y, int rows, int dim, float eps, int reverse) {
   const int lane = threadIdx.x & 31;
-  const int row = blockIdx.x * LN_WARPS + (threadIdx.x >> 5);
+  // reverse: walk the rows from the end -- the rows the preceding GEMM wrote last are still in L2, and the rows
+  // written last here (the low ones) are the first the next GEMM reads
+  const int blk = reverse ? (int)(gridDim.x - 1 - blockIdx.x) : (int)blockIdx.x;
+  const int row = blk * LN_WARPS + (threadIdx.x >> 5);
   if (row >= rows) return;
   const int nch = dim >> 8;
   float v[LN_MAXCH][8];
@@ -235,10 +238,11 @@ int yv_ln2_launch(const void *x, bool x_f32, size_t in_stride, const __nv_bfloat
   const int grid = (rows + LN_WARPS - 1) / LN_WARPS;
   YV_REQUIRE(!delta2 || delta, "layernorm: delta2 needs delta");
   YvProf prof(YV_K_LN, s, (double)rows * dim * ((x_f32 ? 6.0 : 4.0) + (delta ? 2.0 : 0.0) + (delta2 ? 2.0 : 0.0) + (delta && writeback ? 4.0 : 0.0)));
-  static const bool cs = [] { const char *e = getenv("YV_LN_STREAM"); return e && e[0] == '1'; }();   // A/B switch
-  if (x_f32 && cs) layernorm_kernel<true, true><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, delta, delta2, delta_stride, writeback ? 1 : 0, gamma, beta, y, rows, dim, eps);
-  else if (x_f32) layernorm_kernel<true><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, delta, delta2, delta_stride, writeback ? 1 : 0, gamma, beta, y, rows, dim, eps);
-  else layernorm_kernel<false><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, delta, delta2, delta_stride, 0, gamma, beta, y, rows, dim, eps);
+  static const bool cs = [] { const char *e = getenv("YV_LN_STREAM"); return e && e[0] == '1'; }();   // A/B switches
+  static const int rev = [] { const char *e = getenv("YV_LN_REVERSE"); return (e && e[0] == '1') ? 1 : 0; }();
+  if (x_f32 && cs) layernorm_kernel<true, true><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, delta, delta2, delta_stride, writeback ? 1 : 0, gamma, beta, y, rows, dim, eps, rev);
+  else if (x_f32) layernorm_kernel<true><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, delta, delta2, delta_stride, writeback ? 1 : 0, gamma, beta, y, rows, dim, eps, rev);
+  else layernorm_kernel<false><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, delta, delta2, delta_stride, 0, gamma, beta, y, rows, dim, eps, rev);
   YV_LAUNCH_CHECK();
   return YV_OK;
 }
