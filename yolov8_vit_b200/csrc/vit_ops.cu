@@ -23,11 +23,14 @@ layernorm_kernel(const void *xv, size_t in_stride, const __nv_bfloat16 *__restri
                  const __nv_bfloat16 *__restrict__ delta2, size_t delta_stride, int writeback, const float *__restrict__ gamma, const float *__restrict__ beta,
                  __nv_bfloat16 *__restrict__ y, int rows, int dim, float eps, int reverse) {
   const int lane = threadIdx.x & 31;
+  const int nblk = (rows + LN_WARPS - 1) / LN_WARPS;
+  // grid == nblk: one 8-row block per CTA; a smaller (persistent) grid strides over the blocks.
   // reverse: walk the rows from the end -- the rows the preceding GEMM wrote last are still in L2, and the rows
   // written last here (the low ones) are the first the next GEMM reads
-  const int blk = reverse ? (int)(gridDim.x - 1 - blockIdx.x) : (int)blockIdx.x;
+  for (int bi = blockIdx.x; bi < nblk; bi += gridDim.x) {
+  const int blk = reverse ? nblk - 1 - bi : bi;
   const int row = blk * LN_WARPS + (threadIdx.x >> 5);
-  if (row >= rows) return;
+  if (row >= rows) continue;
   const int nch = dim >> 8;
   float v[LN_MAXCH][8];
 #pragma unroll
@@ -122,6 +125,7 @@ layernorm_kernel(const void *xv, size_t in_stride, const __nv_bfloat16 *__restri
       *reinterpret_cast<uint4 *>(y + (size_t)row * dim + e) = u;
     }
   }
+  }  // block loop
 }
 
 // ------------------------------------------------------------------------------------ cls rows
@@ -235,11 +239,13 @@ int yv_ln2_launch(const void *x, bool x_f32, size_t in_stride, const __nv_bfloat
   YV_REQUIRE(rows >= 1 && dim >= 256 && dim % 256 == 0 && dim <= 256 * LN_MAXCH, "layernorm: dim=%d must be a multiple of 256, <= %d", dim, 256 * LN_MAXCH);
   YV_REQUIRE(x && gamma && beta && y, "layernorm: null pointer");
   YV_REQUIRE(in_stride % 8 == 0, "layernorm: row stride must be a multiple of 8 elements");
-  const int grid = (rows + LN_WARPS - 1) / LN_WARPS;
   YV_REQUIRE(!delta2 || delta, "layernorm: delta2 needs delta");
   YvProf prof(YV_K_LN, s, (double)rows * dim * ((x_f32 ? 6.0 : 4.0) + (delta ? 2.0 : 0.0) + (delta2 ? 2.0 : 0.0) + (delta && writeback ? 4.0 : 0.0)));
   static const bool cs = [] { const char *e = getenv("YV_LN_STREAM"); return e && e[0] == '1'; }();   // A/B switches
   static const int rev = [] { const char *e = getenv("YV_LN_REVERSE"); return (e && e[0] == '1') ? 1 : 0; }();
+  static const int persist = [] { const char *e = getenv("YV_LN_PERSIST"); return e ? atoi(e) : 0; }();   // CTAs per SM
+  int grid = (rows + LN_WARPS - 1) / LN_WARPS;
+  if (persist > 0 && grid > yv_num_sms() * persist) grid = yv_num_sms() * persist;
   if (x_f32 && cs) layernorm_kernel<true, true><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, delta, delta2, delta_stride, writeback ? 1 : 0, gamma, beta, y, rows, dim, eps, rev);
   else if (x_f32) layernorm_kernel<true><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, delta, delta2, delta_stride, writeback ? 1 : 0, gamma, beta, y, rows, dim, eps, rev);
   else layernorm_kernel<false><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, delta, delta2, delta_stride, 0, gamma, beta, y, rows, dim, eps, rev);
