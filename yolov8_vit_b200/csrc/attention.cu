@@ -7,7 +7,9 @@
 // (crop, head) -- one warp per 16 rows, Q fragments in registers -- and walks ALL keys in blocks of 64 with
 // the online-softmax recurrence (running max / sum in registers, exp2 domain); every K / V block is staged
 // through padded shared memory (ldmatrix conflict-free), P stays in registers as the A operand of P V.
-// 55 KB of shared memory per CTA -> several CTAs per SM hide the staging.  T <= 256 never comes here: the
+// K / V blocks are double-buffered with cp.async (block kb+1 lands while block kb is in the tensor cores); the query
+// rows are split evenly over the CTAs of a (crop, head) (785 tokens: 4 CTAs x 13 warps = 832 rows, not 4 x 256) and
+// warps whose rows are all past T only help with the staging.  T <= 256 never comes here: the
 // tcgen05 kernels of attention_sm100.cu handle it.  This is the functional path for the reference-literal
 // B/8 model; a tcgen05 multi-block variant is the "next" item of DESIGN.md.
 #include "common.cuh"
@@ -40,6 +42,11 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   return *reinterpret_cast<uint32_t *>(&h);
 }
 
+__device__ __forceinline__ void cp_async16(void *dst, const void *src) {
+  const uint32_t a = (uint32_t)__cvta_generic_to_shared(dst);
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(a), "l"(src) : "memory");
+}
+
 __global__ void __launch_bounds__(512)
 attention_long_kernel(const __nv_bfloat16 *__restrict__ qkv, __nv_bfloat16 *__restrict__ out, int T, int heads,
                       float scale_log2e) {
@@ -48,10 +55,10 @@ attention_long_kernel(const __nv_bfloat16 *__restrict__ qkv, __nv_bfloat16 *__re
   const int nkb = (T + ATT_KB - 1) / ATT_KB;
   const int qrows = nw * 16;
   __nv_bfloat16 *Qs = reinterpret_cast<__nv_bfloat16 *>(att_smem);
-  __nv_bfloat16 *Ks = Qs + (size_t)qrows * ATT_LD;          // one 64-key block
-  __nv_bfloat16 *Vs = Ks + (size_t)ATT_KB * ATT_LD;
+  __nv_bfloat16 *KV = Qs + (size_t)qrows * ATT_LD;          // 2 buffers x (K block, V block) of 64 keys
+  constexpr size_t KV_BUF = (size_t)2 * ATT_KB * ATT_LD;
 
-  const int head = blockIdx.x, crop = blockIdx.y, q0 = blockIdx.z * 256;
+  const int head = blockIdx.x, crop = blockIdx.y, q0 = blockIdx.z * qrows;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int D = heads * ATT_DH;
   const __nv_bfloat16 *base = qkv + (size_t)crop * T * 3 * D + (size_t)head * ATT_DH;
@@ -79,20 +86,32 @@ attention_long_kernel(const __nv_bfloat16 *__restrict__ qkv, __nv_bfloat16 *__re
 #pragma unroll
   for (int j = 0; j < 8; ++j) { o[j][0] = o[j][1] = o[j][2] = o[j][3] = 0.f; }
   float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+  const bool active = q0 + warp * 16 < T;         // warp-uniform: warps past the last token only stage
 
-  for (int kb = 0; kb < nkb; ++kb) {
-    __syncthreads();                              // the previous block's K / V are no longer read
+  auto stage = [&](int kb) {                      // K / V block kb -> buffer kb & 1 (asynchronous copies)
+    __nv_bfloat16 *Kd = KV + (size_t)(kb & 1) * KV_BUF, *Vd = Kd + (size_t)ATT_KB * ATT_LD;
     for (int i = tid; i < ATT_KB * 8; i += blockDim.x) {
       const int r = i >> 3, c = i & 7, key = kb * ATT_KB + r;
-      uint4 k = zero, v = zero;
       if (key < T) {
-        k = *reinterpret_cast<const uint4 *>(base + (size_t)key * 3 * D + D + c * 8);
-        v = *reinterpret_cast<const uint4 *>(base + (size_t)key * 3 * D + 2 * D + c * 8);
+        cp_async16(Kd + (size_t)r * ATT_LD + c * 8, base + (size_t)key * 3 * D + D + c * 8);
+        cp_async16(Vd + (size_t)r * ATT_LD + c * 8, base + (size_t)key * 3 * D + 2 * D + c * 8);
+      } else {
+        *reinterpret_cast<uint4 *>(Kd + (size_t)r * ATT_LD + c * 8) = zero;
+        *reinterpret_cast<uint4 *>(Vd + (size_t)r * ATT_LD + c * 8) = zero;
       }
-      *reinterpret_cast<uint4 *>(Ks + (size_t)r * ATT_LD + c * 8) = k;
-      *reinterpret_cast<uint4 *>(Vs + (size_t)r * ATT_LD + c * 8) = v;
     }
-    __syncthreads();
+  };
+  stage(0);
+  asm volatile("cp.async.commit_group;" ::: "memory");
+
+  for (int kb = 0; kb < nkb; ++kb) {
+    __syncthreads();                              // block kb-1 is no longer read: its buffer takes block kb+1
+    if (kb + 1 < nkb) stage(kb + 1);
+    asm volatile("cp.async.commit_group;" ::: "memory");
+    asm volatile("cp.async.wait_group 1;" ::: "memory");      // this thread's copies of block kb have landed
+    __syncthreads();                              // ... and everybody else's
+    if (!active) continue;
+    const __nv_bfloat16 *Ks = KV + (size_t)(kb & 1) * KV_BUF, *Vs = Ks + (size_t)ATT_KB * ATT_LD;
     float s[8][4];
 #pragma unroll
     for (int j = 0; j < 8; ++j) { s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f; }
@@ -169,6 +188,7 @@ attention_long_kernel(const __nv_bfloat16 *__restrict__ qkv, __nv_bfloat16 *__re
     }
   }
 
+  if (!active) return;
   // finalise: row sums across the quad, normalise, store bf16
   l0 += __shfl_xor_sync(0xffffffffu, l0, 1);
   l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
@@ -191,12 +211,12 @@ int yv_attention_long_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n
   YV_REQUIRE(dh == ATT_DH, "attention: head dim %d unsupported (need %d)", dh, ATT_DH);
   YV_REQUIRE(n >= 1 && n <= 65535 && heads >= 1 && T >= 1, "attention: bad shape");
   const int qblocks = (T + 255) / 256;
-  const int rows = T < 256 ? T : 256;
-  const int nw = (rows + 15) / 16;
-  const size_t smem = (size_t)(nw * 16 + 2 * ATT_KB) * ATT_LD * sizeof(__nv_bfloat16);
+  const int groups = (T + 15) / 16;                       // 16-row query groups, spread evenly over the CTAs
+  const int nw = (groups + qblocks - 1) / qblocks;        // <= 16 warps
+  const size_t smem = (size_t)(nw * 16 + 4 * ATT_KB) * ATT_LD * sizeof(__nv_bfloat16);
   static bool attr_set = false;
   if (!attr_set) {
-    YV_CUDA(cudaFuncSetAttribute(attention_long_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 64 * 1024));
+    YV_CUDA(cudaFuncSetAttribute(attention_long_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 80 * 1024));
     attr_set = true;
   }
   dim3 grid(heads, n, qblocks);
