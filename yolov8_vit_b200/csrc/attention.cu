@@ -3,12 +3,12 @@
 // timm Attention.forward (vit_base_patch8_224, the reference-literal model of utils/class_config.py:21):
 // qkv [n, T, 3, heads, dh] -> per head softmax(q k^T * dh^-0.5) v.
 //
-// mma.sync.m16n8k16 (bf16 x bf16 -> f32) flash-style kernel: a CTA owns up to 256 query rows of one
-// (crop, head) -- one warp per 16 rows, Q fragments in registers -- and walks ALL keys in blocks of 64 with
+// mma.sync.m16n8k16 (bf16 x bf16 -> f32) flash-style kernel: a CTA owns up to 160 query rows of one
+// (crop, head) -- one warp per 16 rows, Q staged once in shared memory -- and walks ALL keys in blocks of 64 with
 // the online-softmax recurrence (running max / sum in registers, exp2 domain); every K / V block is staged
 // through padded shared memory (ldmatrix conflict-free), P stays in registers as the A operand of P V.
 // K / V blocks are double-buffered with cp.async (block kb+1 lands while block kb is in the tensor cores); the query
-// rows are split evenly over the CTAs of a (crop, head) (785 tokens: 4 CTAs x 13 warps = 832 rows, not 4 x 256) and
+// rows are split evenly over the CTAs of a (crop, head) (785 tokens: 5 CTAs x 10 warps = 800 rows, not 4 x 256) and
 // warps whose rows are all past T only help with the staging.  T <= 256 never comes here: the
 // tcgen05 kernels of attention_sm100.cu handle it.  This is the functional path for the reference-literal
 // B/8 model; a tcgen05 multi-block variant is the "next" item of DESIGN.md.
@@ -47,7 +47,9 @@ __device__ __forceinline__ void cp_async16(void *dst, const void *src) {
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(a), "l"(src) : "memory");
 }
 
-__global__ void __launch_bounds__(512)
+constexpr int ATT_MAXW = 10;       // warps per CTA: 2 CTAs x 10 warps per SM at <= 102 registers
+
+__global__ void __launch_bounds__(ATT_MAXW * 32, 2)
 attention_long_kernel(const __nv_bfloat16 *__restrict__ qkv, __nv_bfloat16 *__restrict__ out, int T, int heads,
                       float scale_log2e) {
   extern __shared__ __align__(16) uint8_t att_smem[];
@@ -73,14 +75,9 @@ attention_long_kernel(const __nv_bfloat16 *__restrict__ qkv, __nv_bfloat16 *__re
   }
   __syncthreads();
 
-  // Q fragments of this warp's 16 rows: 4 k-steps of 16
-  uint32_t qf[4][4];
-  {
-    const int r = warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;
-    const int c = (lane >> 4) * 8;
-#pragma unroll
-    for (int ks = 0; ks < 4; ++ks) ldsm_x4(qf[ks], Qs + (size_t)r * ATT_LD + ks * 16 + c);
-  }
+  // Q fragments are re-read from shared memory at every k-step (4 extra ldmatrix per key block) instead of living
+  // in 16 registers: that is what lets two CTAs share an SM
+  const __nv_bfloat16 *qsrc = Qs + (size_t)(warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * ATT_LD + (lane >> 4) * 8;
 
   float o[8][4];
 #pragma unroll
@@ -118,14 +115,16 @@ attention_long_kernel(const __nv_bfloat16 *__restrict__ qkv, __nv_bfloat16 *__re
     const __nv_bfloat16 *Kb = Ks;
 #pragma unroll
     for (int ks = 0; ks < 4; ++ks) {
+      uint32_t qf[4];
+      ldsm_x4(qf, qsrc + ks * 16);
 #pragma unroll
       for (int np = 0; np < 4; ++np) {          // n-tile pairs (2 x 8 keys)
         uint32_t kf[4];
         const int r = np * 16 + (lane & 7) + (lane >> 4) * 8;
         const int c = ks * 16 + ((lane >> 3) & 1) * 8;
         ldsm_x4(kf, Kb + (size_t)r * ATT_LD + c);
-        mma_bf16(s[2 * np], qf[ks], kf[0], kf[1]);
-        mma_bf16(s[2 * np + 1], qf[ks], kf[2], kf[3]);
+        mma_bf16(s[2 * np], qf, kf[0], kf[1]);
+        mma_bf16(s[2 * np + 1], qf, kf[2], kf[3]);
       }
     }
     // scale into the exp2 domain, mask keys >= T
@@ -210,9 +209,9 @@ int yv_attention_long_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n
                              cudaStream_t s) {
   YV_REQUIRE(dh == ATT_DH, "attention: head dim %d unsupported (need %d)", dh, ATT_DH);
   YV_REQUIRE(n >= 1 && n <= 65535 && heads >= 1 && T >= 1, "attention: bad shape");
-  const int qblocks = (T + 255) / 256;
   const int groups = (T + 15) / 16;                       // 16-row query groups, spread evenly over the CTAs
-  const int nw = (groups + qblocks - 1) / qblocks;        // <= 16 warps
+  const int qblocks = (groups + ATT_MAXW - 1) / ATT_MAXW;
+  const int nw = (groups + qblocks - 1) / qblocks;        // <= ATT_MAXW warps
   const size_t smem = (size_t)(nw * 16 + 4 * ATT_KB) * ATT_LD * sizeof(__nv_bfloat16);
   static bool attr_set = false;
   if (!attr_set) {
