@@ -42,6 +42,11 @@ __device__ __forceinline__ uint32_t pack_bf16(float lo, float hi) {
   return *reinterpret_cast<uint32_t *>(&h);
 }
 
+__device__ __forceinline__ float ex2_approx(float x) {      // MUFU.EX2; -inf -> +0
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ void cp_async16(void *dst, const void *src) {
   const uint32_t a = (uint32_t)__cvta_generic_to_shared(dst);
   asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(a), "l"(src) : "memory");
@@ -127,17 +132,20 @@ attention_long_kernel(const __nv_bfloat16 *__restrict__ qkv, __nv_bfloat16 *__re
         mma_bf16(s[2 * np + 1], qf, kf[2], kf[3]);
       }
     }
-    // scale into the exp2 domain, mask keys >= T
-    const int key0 = kb * ATT_KB + (lane & 3) * 2;
+    // keys >= T exist only in the last block: mask there (warp-uniform branch); the block maximum is taken on the raw
+    // scores (scale > 0) and the scale is folded into the exponent's FMA
+    if (kb == nkb - 1) {
+      const int key0 = kb * ATT_KB + (lane & 3) * 2;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int k = key0 + j * 8;
+        if (k >= T) { s[j][0] = -INFINITY; s[j][2] = -INFINITY; }
+        if (k + 1 >= T) { s[j][1] = -INFINITY; s[j][3] = -INFINITY; }
+      }
+    }
     float bm0 = -INFINITY, bm1 = -INFINITY;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      const int k = key0 + j * 8;
-      const bool v0 = k < T, v1 = (k + 1) < T;
-      s[j][0] = v0 ? s[j][0] * scale_log2e : -INFINITY;
-      s[j][1] = v1 ? s[j][1] * scale_log2e : -INFINITY;
-      s[j][2] = v0 ? s[j][2] * scale_log2e : -INFINITY;
-      s[j][3] = v1 ? s[j][3] * scale_log2e : -INFINITY;
       bm0 = fmaxf(bm0, fmaxf(s[j][0], s[j][1]));
       bm1 = fmaxf(bm1, fmaxf(s[j][2], s[j][3]));
     }
@@ -145,17 +153,17 @@ attention_long_kernel(const __nv_bfloat16 *__restrict__ qkv, __nv_bfloat16 *__re
     bm0 = fmaxf(bm0, __shfl_xor_sync(0xffffffffu, bm0, 2));
     bm1 = fmaxf(bm1, __shfl_xor_sync(0xffffffffu, bm1, 1));
     bm1 = fmaxf(bm1, __shfl_xor_sync(0xffffffffu, bm1, 2));
-    const float mn0 = fmaxf(m0, bm0), mn1 = fmaxf(m1, bm1);
-    const float corr0 = exp2f(m0 - mn0), corr1 = exp2f(m1 - mn1);
+    const float mn0 = fmaxf(m0, bm0 * scale_log2e), mn1 = fmaxf(m1, bm1 * scale_log2e);
+    const float corr0 = ex2_approx(m0 - mn0), corr1 = ex2_approx(m1 - mn1);
     m0 = mn0;
     m1 = mn1;
     float rs0 = 0.f, rs1 = 0.f;
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      s[j][0] = exp2f(s[j][0] - mn0);
-      s[j][1] = exp2f(s[j][1] - mn0);
-      s[j][2] = exp2f(s[j][2] - mn1);
-      s[j][3] = exp2f(s[j][3] - mn1);
+      s[j][0] = ex2_approx(fmaf(s[j][0], scale_log2e, -mn0));
+      s[j][1] = ex2_approx(fmaf(s[j][1], scale_log2e, -mn0));
+      s[j][2] = ex2_approx(fmaf(s[j][2], scale_log2e, -mn1));
+      s[j][3] = ex2_approx(fmaf(s[j][3], scale_log2e, -mn1));
       rs0 += s[j][0] + s[j][1];
       rs1 += s[j][2] + s[j][3];
     }
