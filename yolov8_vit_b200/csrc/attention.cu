@@ -7,7 +7,8 @@
 // (crop, head) -- one warp per 16 rows, Q staged once in shared memory -- and walks ALL keys in blocks of 64 with
 // the online-softmax recurrence (running max / sum in registers, exp2 domain); every K / V block is staged
 // through padded shared memory (ldmatrix conflict-free), P stays in registers as the A operand of P V.
-// K / V blocks are double-buffered with cp.async (block kb+1 lands while block kb is in the tensor cores); the query
+// K / V blocks go through a 3-deep cp.async ring (blocks kb+1, kb+2 in flight while block kb is in the tensor cores,
+// one __syncthreads per block); the query
 // rows are split evenly over the CTAs of a (crop, head) (785 tokens: 5 CTAs x 10 warps = 800 rows, not 4 x 256) and
 // warps whose rows are all past T only help with the staging.  T <= 256 never comes here: the
 // tcgen05 kernels of attention_sm100.cu handle it.  This is the functional path for the reference-literal
@@ -62,7 +63,7 @@ attention_long_kernel(const __nv_bfloat16 *__restrict__ qkv, __nv_bfloat16 *__re
   const int nkb = (T + ATT_KB - 1) / ATT_KB;
   const int qrows = nw * 16;
   __nv_bfloat16 *Qs = reinterpret_cast<__nv_bfloat16 *>(att_smem);
-  __nv_bfloat16 *KV = Qs + (size_t)qrows * ATT_LD;          // 2 buffers x (K block, V block) of 64 keys
+  __nv_bfloat16 *KV = Qs + (size_t)qrows * ATT_LD;          // 3 buffers x (K block, V block) of 64 keys
   constexpr size_t KV_BUF = (size_t)2 * ATT_KB * ATT_LD;
 
   const int head = blockIdx.x, crop = blockIdx.y, q0 = blockIdx.z * qrows;
@@ -90,8 +91,8 @@ attention_long_kernel(const __nv_bfloat16 *__restrict__ qkv, __nv_bfloat16 *__re
   float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
   const bool active = q0 + warp * 16 < T;         // warp-uniform: warps past the last token only stage
 
-  auto stage = [&](int kb) {                      // K / V block kb -> buffer kb & 1 (asynchronous copies)
-    __nv_bfloat16 *Kd = KV + (size_t)(kb & 1) * KV_BUF, *Vd = Kd + (size_t)ATT_KB * ATT_LD;
+  auto stage = [&](int kb) {                      // K / V block kb -> buffer kb % 3 (asynchronous copies)
+    __nv_bfloat16 *Kd = KV + (size_t)(kb % 3) * KV_BUF, *Vd = Kd + (size_t)ATT_KB * ATT_LD;
     for (int i = tid; i < ATT_KB * 8; i += blockDim.x) {
       const int r = i >> 3, c = i & 7, key = kb * ATT_KB + r;
       if (key < T) {
@@ -105,15 +106,16 @@ attention_long_kernel(const __nv_bfloat16 *__restrict__ qkv, __nv_bfloat16 *__re
   };
   stage(0);
   asm volatile("cp.async.commit_group;" ::: "memory");
+  if (nkb > 1) stage(1);
+  asm volatile("cp.async.commit_group;" ::: "memory");
 
   for (int kb = 0; kb < nkb; ++kb) {
-    __syncthreads();                              // block kb-1 is no longer read: its buffer takes block kb+1
-    if (kb + 1 < nkb) stage(kb + 1);
-    asm volatile("cp.async.commit_group;" ::: "memory");
     asm volatile("cp.async.wait_group 1;" ::: "memory");      // this thread's copies of block kb have landed
-    __syncthreads();                              // ... and everybody else's
+    __syncthreads();          // ... and everybody else's; block kb-1 is no longer read: its buffer takes block kb+2
+    if (kb + 2 < nkb) stage(kb + 2);
+    asm volatile("cp.async.commit_group;" ::: "memory");
     if (!active) continue;
-    const __nv_bfloat16 *Ks = KV + (size_t)(kb & 1) * KV_BUF, *Vs = Ks + (size_t)ATT_KB * ATT_LD;
+    const __nv_bfloat16 *Ks = KV + (size_t)(kb % 3) * KV_BUF, *Vs = Ks + (size_t)ATT_KB * ATT_LD;
     float s[8][4];
 #pragma unroll
     for (int j = 0; j < 8; ++j) { s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f; }
@@ -220,10 +222,10 @@ int yv_attention_long_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n
   const int groups = (T + 15) / 16;                       // 16-row query groups, spread evenly over the CTAs
   const int qblocks = (groups + ATT_MAXW - 1) / ATT_MAXW;
   const int nw = (groups + qblocks - 1) / qblocks;        // <= ATT_MAXW warps
-  const size_t smem = (size_t)(nw * 16 + 4 * ATT_KB) * ATT_LD * sizeof(__nv_bfloat16);
+  const size_t smem = (size_t)(nw * 16 + 6 * ATT_KB) * ATT_LD * sizeof(__nv_bfloat16);
   static bool attr_set = false;
   if (!attr_set) {
-    YV_CUDA(cudaFuncSetAttribute(attention_long_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 80 * 1024));
+    YV_CUDA(cudaFuncSetAttribute(attention_long_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     attr_set = true;
   }
   dim3 grid(heads, n, qblocks);
