@@ -66,7 +66,8 @@ attention_long_kernel(const __nv_bfloat16 *__restrict__ qkv, __nv_bfloat16 *__re
   __nv_bfloat16 *KV = Qs + (size_t)qrows * ATT_LD;          // 3 buffers x (K block, V block) of 64 keys
   constexpr size_t KV_BUF = (size_t)2 * ATT_KB * ATT_LD;
 
-  const int head = blockIdx.x, crop = blockIdx.y, q0 = blockIdx.z * qrows;
+  // the query blocks of one (crop, head) are adjacent in launch order, so its K / V stay in L2 for all of them
+  const int head = blockIdx.y, crop = blockIdx.z, q0 = blockIdx.x * qrows;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int D = heads * ATT_DH;
   const __nv_bfloat16 *base = qkv + (size_t)crop * T * 3 * D + (size_t)head * ATT_DH;
@@ -228,7 +229,7 @@ int yv_attention_long_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n
     YV_CUDA(cudaFuncSetAttribute(attention_long_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     attr_set = true;
   }
-  dim3 grid(heads, n, qblocks);
+  dim3 grid(qblocks, heads, n);
   const float scale_log2e = (1.0f / sqrtf((float)dh)) * 1.4426950408889634f;
   YvProf prof(YV_K_ATTN, s, 4.0 * n * heads * (double)T * T * dh);
   attention_long_kernel<<<grid, nw * 32, smem, s>>>(qkv, out, T, heads, scale_log2e);
