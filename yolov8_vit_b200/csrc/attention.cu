@@ -172,10 +172,12 @@ attention_long_kernel(const __nv_bfloat16 *__restrict__ qkv, __nv_bfloat16 *__re
     }
     l0 = l0 * corr0 + rs0;
     l1 = l1 * corr1 + rs1;
+    if (__any_sync(0xffffffffu, corr0 != 1.f || corr1 != 1.f)) {   // the running maxima settle after a few blocks
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      o[j][0] *= corr0; o[j][1] *= corr0;
-      o[j][2] *= corr1; o[j][3] *= corr1;
+      for (int j = 0; j < 8; ++j) {
+        o[j][0] *= corr0; o[j][1] *= corr0;
+        o[j][2] *= corr1; o[j][3] *= corr1;
+      }
     }
     // O += P V
     const __nv_bfloat16 *Vb = Vs;
