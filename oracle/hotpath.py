@@ -1,8 +1,12 @@
 """CPU restatement of the reference hot path (TEST INFRASTRUCTURE, see oracle/__init__.py).
 
 Every function cites the reference location (relative to the upstream repo
-Voyager0587/yolov8-vit) whose behaviour it restates.  PARITY UNPINNED: the
-reference has no tests or golden vectors for any of these stages.
+Voyager0587/yolov8-vit) whose behaviour it restates.  The reference has no tests or
+golden vectors for any of these stages; what pins this file instead is the reference's
+OWN TEXT, extracted and executed by oracle/make_ref.py into oracle/_ref (custom_nms,
+crop_image, Network_Wrapper, make_anchors + the DFL fragment) and compared with the
+functions below in tests/test_ref.py, plus third-party libraries for the pieces the
+reference delegates (cv2 nearest resize, torch bilinear interpolate, torchvision ViT).
 
 Third-party arithmetic that is not in the reference tree:
   * torchvision.ops.box_iou (unpinned in requirements.txt:7; 0.26 used here)
@@ -320,6 +324,31 @@ def vit_forward(sd, x: torch.Tensor, cfg: ViTConfig = ViTConfig(), return_hidden
     y = torch.relu(hidden) @ sd["fc.1.weight"].t() + sd["fc.1.bias"]
     logits = torch.relu(y) @ sd["fc.3.weight"].t() + sd["fc.3.bias"]
     return (logits, hidden) if return_hidden else logits
+
+
+def timm_to_torchvision(sd) -> dict:
+    """Re-keys a ``Network_Wrapper.state_dict()`` in timm naming (``model.blocks.N...``) to the layout the same
+    wrapper has around ``torchvision.models.vit_b_16`` (``model.encoder.layers.encoder_layer_N...``); timm is
+    not installed, torchvision's ViT is the independent implementation of the same published architecture the
+    reference's own ``Network_Wrapper`` text (oracle/_ref) is executed around.  ``fc.*`` keys pass through."""
+    out = {}
+    top = {"model.cls_token": "model.class_token", "model.pos_embed": "model.encoder.pos_embedding",
+           "model.patch_embed.proj.weight": "model.conv_proj.weight", "model.patch_embed.proj.bias": "model.conv_proj.bias",
+           "model.norm.weight": "model.encoder.ln.weight", "model.norm.bias": "model.encoder.ln.bias",
+           "model.head.weight": "model.heads.head.weight", "model.head.bias": "model.heads.head.bias"}
+    blk = {"norm1.weight": "ln_1.weight", "norm1.bias": "ln_1.bias", "norm2.weight": "ln_2.weight", "norm2.bias": "ln_2.bias",
+           "attn.qkv.weight": "self_attention.in_proj_weight", "attn.qkv.bias": "self_attention.in_proj_bias",
+           "attn.proj.weight": "self_attention.out_proj.weight", "attn.proj.bias": "self_attention.out_proj.bias",
+           "mlp.fc1.weight": "mlp.0.weight", "mlp.fc1.bias": "mlp.0.bias", "mlp.fc2.weight": "mlp.3.weight", "mlp.fc2.bias": "mlp.3.bias"}
+    for k, v in sd.items():
+        if k in top:
+            out[top[k]] = v
+        elif k.startswith("model.blocks."):
+            _, _, i, rest = k.split(".", 3)
+            out[f"model.encoder.layers.encoder_layer_{i}.{blk[rest]}"] = v
+        else:
+            out[k] = v
+    return out
 
 
 # --------------------------------------------------------------------------- whole path

@@ -69,8 +69,11 @@ class ViTModel:
             self._h = None
 
     def load_state_dict(self, sd: dict, strict: bool = True):
-        """``sd``: Network_Wrapper.state_dict() layout (``model.*`` timm names + ``fc.1.*``/``fc.3.*``)."""
+        """``sd``: Network_Wrapper.state_dict() layout (``model.*`` timm names + ``fc.1.*``/``fc.3.*``), or the
+        same wrapper around ``torchvision.models.vit_b_16`` (``model.encoder.layers.encoder_layer_N...``,
+        SURVEY.md §5 'checkpoint')."""
         lib = load()
+        sd = torchvision_to_timm(sd)
         with torch.cuda.device(self.device):
             for k, v in sd.items():
                 t = v.detach().to(device=self.device, dtype=torch.float32).contiguous()
@@ -113,6 +116,41 @@ class ViTModel:
         return self.forward_patches(p, x.shape[0])[0]
 
     __call__ = forward
+
+
+_TV_TOP = {"model.class_token": "model.cls_token", "model.encoder.pos_embedding": "model.pos_embed",
+           "model.conv_proj.weight": "model.patch_embed.proj.weight", "model.conv_proj.bias": "model.patch_embed.proj.bias",
+           "model.encoder.ln.weight": "model.norm.weight", "model.encoder.ln.bias": "model.norm.bias",
+           "model.heads.head.weight": "model.head.weight", "model.heads.head.bias": "model.head.bias"}
+_TV_BLOCK = {"ln_1.weight": "norm1.weight", "ln_1.bias": "norm1.bias", "ln_2.weight": "norm2.weight",
+             "ln_2.bias": "norm2.bias", "self_attention.in_proj_weight": "attn.qkv.weight",
+             "self_attention.in_proj_bias": "attn.qkv.bias", "self_attention.out_proj.weight": "attn.proj.weight",
+             "self_attention.out_proj.bias": "attn.proj.bias", "mlp.0.weight": "mlp.fc1.weight",
+             "mlp.0.bias": "mlp.fc1.bias", "mlp.3.weight": "mlp.fc2.weight", "mlp.3.bias": "mlp.fc2.bias",
+             # torchvision checkpoints older than 0.12 name the MLP layers linear_1 / linear_2
+             "mlp.linear_1.weight": "mlp.fc1.weight", "mlp.linear_1.bias": "mlp.fc1.bias",
+             "mlp.linear_2.weight": "mlp.fc2.weight", "mlp.linear_2.bias": "mlp.fc2.bias"}
+
+
+def torchvision_to_timm(sd: dict) -> dict:
+    """Re-keys a ``Network_Wrapper(torchvision vit_b_16)`` state dict to the timm names the packed model uses;
+    a dict that is already in timm naming is returned unchanged.  A bare torchvision ViT state dict (no
+    ``model.`` prefix, no ``fc.*``) is accepted too."""
+    if not any(k.startswith(("model.encoder.", "encoder.", "model.conv_proj", "conv_proj")) for k in sd):
+        return sd
+    out = {}
+    for k, v in sd.items():
+        kk = k if k.startswith(("model.", "fc.")) else "model." + k
+        if kk in _TV_TOP:
+            out[_TV_TOP[kk]] = v
+        elif kk.startswith("model.encoder.layers.encoder_layer_"):
+            i, rest = kk[len("model.encoder.layers.encoder_layer_"):].split(".", 1)
+            if rest not in _TV_BLOCK:
+                raise KeyError(f"unknown torchvision ViT parameter {k!r}")
+            out[f"model.blocks.{i}.{_TV_BLOCK[rest]}"] = v
+        else:
+            out[kk] = v
+    return out
 
 
 def patchify_bf16(x: torch.Tensor, patch: int) -> torch.Tensor:
