@@ -14,8 +14,16 @@ batch-sharded (weak scaling: per-GPU work fixed), no collective on the data path
             images and D2H of the records of EVERY step inside the timed region; the serving loop submits
             batch k+1 before collecting batch k, so uploads overlap the previous batch's ViT).
 `roofline`: the dominant kernel (tcgen05 GEMM): flops per launch / event-timed launch duration.
-`cpu_baseline` / `--impl reference`: the oracle (a verbatim restatement of the reference's torch
-            CPU path; the reference itself is not importable) on the host cores.
+`cpu_baseline` / `--impl reference`: the oracle (a restatement of the reference's torch CPU path, pinned to the
+            reference's own text by tests/test_ref.py; the reference itself is not importable) on the
+            host cores.  The cpu_baseline leg runs on the FIRST images of the very batch the GPU arm times, and its
+            results double as the post-timing self-check (`verified`): keep lists, crop boxes and top-1 of those
+            images must equal the GPU's.
+`extras`  : short extra passes that put the rest of BASELINE.json's metric / configs into the same record without
+            touching the headline: cfg2 decode GB/s + NMS us/img (64 x 768 candidates), the cfg5 NMS sweep
+            (32 x 30 000 boxes, thr .3-.7), cfg3 crops/s (256 crops), per-rank step times and the event-timed
+            duration of the final record gather; at N > 1 a cfg4 strong-scaling sub-record (512 images of
+            YOLOv8s-1280 over the ranks).  --no-extras skips them.
 """
 from __future__ import annotations
 
@@ -42,6 +50,8 @@ FLOP_PER_CROP = 35.128e9           # SURVEY.md §8d (ViT-B/16 + heads)
 # one-pass ViT at M = 1072 crops x 197 = 211 184 rows (profiles/r01_vit_ncu_v7.md): (1624 + 1250 + 610 + 1576) / 4 MB
 # = 5.99 KB per token row; scaled by the run's own row count below (the driver's workload gives exactly 1072 crops)
 GEMM_DRAM_BYTES_PER_ROW = 1265e6 / 211184
+GEMM_TRAFFIC_NOTE = ("mean dram read+write bytes of the qkv/proj/fc1/fc2 launches of the one-pass ViT (M = crops x 197 "
+                     "rows), ncu --set full (profiles/r01_vit_ncu_v7.md: 1265 MB at 1072 crops = the algorithmic bytes)")
 
 
 def parse():
@@ -56,6 +66,7 @@ def parse():
                          "cfg4: BASELINE.json configs[3], YOLOv8s-1280 head [512,84,33600] + 512 images "
                          "1280x1280 sharded over the ranks (strong scaling: 512 / N images per GPU)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the cfg2 / cfg3 / cfg5 / cfg4 extra passes")
     ap.add_argument("--e2e-vit-chunk", type=int, default=0,
                     help="crops per ViT pass in the host-buffer loop (0 = the API's default: auto)")
     return ap.parse_args()
@@ -138,34 +149,79 @@ def make_inputs(batch, seed):
 
 
 def vit_weights():
-    from oracle import hotpath as O      # only to GENERATE the seeded synthetic weights
-    return O.make_vit_weights(O.ViTConfig(), seed=SEED)
+    from yolov8_vit_b200 import synth
+    return synth.make_vit_weights(seed=SEED)      # seeded synthetic weights (no checkpoints exist in the tree)
 
 
-def cpu_pipeline(head, imgs, sd, threads):
-    """The reference's CPU path (oracle restatement) on `head`/`imgs`; returns (seconds, crops)."""
+def ref_custom_nms():
+    """The reference's OWN custom_nms text (README.md:62-83, extracted into oracle/_ref by oracle/make_ref.py) when
+    it is available, else None (-> the oracle's restatement).  The workload's scores are pairwise distinct, so the
+    snippet's unstable argsort is well defined."""
+    try:
+        from oracle import make_ref
+        if make_ref.available():
+            from oracle import _ref
+            return _ref.custom_nms
+    except Exception:
+        pass
+    return None
+
+
+CPU_KIND_NOTE = ("port: oracle restatement of the per-image loop (the reference's detector wrapper is an un-vendored "
+                 "submodule and timm is absent); custom_nms is the reference's own text when oracle/_ref is present")
+
+
+def cpu_pipeline(head, imgs, sd, threads, keep_results=False):
+    """The reference's CPU path (oracle restatement) on `head`/`imgs`; returns (seconds, crops[, results])."""
     import torch
     from oracle import hotpath as O
     torch.set_num_threads(threads)
+    nms = ref_custom_nms()
     t0 = time.perf_counter()
-    crops = 0
+    crops, res = 0, []
     for b in range(head.shape[0]):
-        r = O.pipeline_image(head[b], imgs[b].numpy(), sd)
+        r = O.pipeline_image(head[b], imgs[b].numpy(), sd, nms_fn=nms)
         crops += int(r["valid"].sum())
-    return time.perf_counter() - t0, crops
+        if keep_results:
+            res.append(r)
+    dt = time.perf_counter() - t0
+    return (dt, crops, res) if keep_results else (dt, crops)
 
 
-def cpu_baseline(sd, budget_s=15.0):
-    """Bounded sample of the same workload: images are added until ~budget_s of CPU work."""
+def cpu_baseline(sd, head, imgs, budget_s=15.0):
+    """Bounded sample of the same workload: the first images of the batch the GPU arm timed, as many as fit in
+    ~budget_s of CPU work.  Returns (cpu_baseline dict, per-image oracle results for the self-check)."""
     cores = os.cpu_count() or 1
-    head, imgs = make_inputs(64, SEED)
-    cpu_pipeline(head[:1], imgs[:1], sd, cores)                      # warm-up
-    t, c = cpu_pipeline(head[1:3], imgs[1:3], sd, cores)
-    n = int(max(2, min(61, budget_s / max(t / 2, 1e-3))))
-    t, c = cpu_pipeline(head[3:3 + n], imgs[3:3 + n], sd, cores)
-    return {"value": n / t, "unit": "images/s", "cores": cores, "kind": "port",
-            "sample": f"{n} images ({c} crops) of the same synthetic workload, oracle pipeline fp32, "
-                      f"torch {cores} threads, {t:.1f} s"}
+    cpu_pipeline(head[-1:], imgs[-1:], sd, cores)                    # warm-up (an image outside the sample)
+    t, c, res = cpu_pipeline(head[0:2], imgs[0:2], sd, cores, True)
+    n = int(max(8, min(61, head.shape[0] - 3, budget_s / max(t / 2, 1e-3))))
+    t, c, more = cpu_pipeline(head[2:2 + n], imgs[2:2 + n], sd, cores, True)
+    return ({"value": n / t, "unit": "images/s", "cores": cores, "kind": "port",
+             "sample": f"{n} images ({c} crops) of the timed batch itself, oracle pipeline fp32, "
+                       f"torch {cores} threads, {t:.1f} s", "note": CPU_KIND_NOTE,
+             "custom_nms": "reference text (oracle/_ref)" if ref_custom_nms() else "oracle restatement"}, res + more)
+
+
+def verify(oracle_results, r):
+    """Post-timing self-check, outside every timed region: the GPU result `r` (keep_intermediates) of the timed
+    batch against the oracle's results for its first images -- keep lists, rounded boxes, crop boxes and top-1."""
+    import numpy as np
+    keep, kc = r.keep.cpu(), r.keep_counts.cpu()
+    det_count, rec = r.crops.det_count.cpu(), r.records.cpu()
+    det_box, det_cb = r.crops.det_box.cpu().numpy(), r.crops.det_crop_box.cpu().numpy()
+    n_img = n_crop = 0
+    for b, ref in enumerate(oracle_results):
+        n = int(det_count[b])
+        if keep[b, :int(kc[b])].tolist()[:n] != ref["keep"].tolist():
+            return {"ok": False, "why": f"keep list of image {b} differs"}
+        if not (np.array_equal(det_box[b, :n], ref["box"]) and np.array_equal(det_cb[b, :n], ref["crop_box"])):
+            return {"ok": False, "why": f"boxes of image {b} differ"}
+        if "cls" in ref and rec[b, :n, 4].int().tolist() != ref["cls"].tolist():
+            return {"ok": False, "why": f"top-1 of image {b} differs"}
+        n_img += 1
+        n_crop += n
+    return {"ok": True, "images": n_img, "crops": n_crop,
+            "what": "keep lists + rounded / dilated boxes bit-exact and ViT top-1 identical vs the CPU oracle"}
 
 
 def run_reference(args):
@@ -193,12 +249,72 @@ def run_reference(args):
         "unit": "images/s", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": args.scaling, "vs_baseline": None,
         "dtype": "f32", "data": "synthetic", "config": {"workload": workload_name(args.batch), "sample": sample},
-        "cpu_baseline": {"value": val, "unit": "images/s", "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": val, "unit": "images/s", "cores": cores, "kind": "port", "sample": sample,
+                         "note": CPU_KIND_NOTE,
+                         "custom_nms": "reference text (oracle/_ref)" if ref_custom_nms() else "oracle restatement"},
         "e2e": {"value": val, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
 
 
 # ------------------------------------------------------------------------------------------ GPU
+def event_timed(fn, reps, flush=None):
+    """Median device time of `fn` in ms (CUDA events on the current stream; `flush` = L2 flush between reps)."""
+    import torch
+    for _ in range(3):
+        fn()
+    ts = []
+    for _ in range(reps):
+        if flush is not None:
+            flush.zero_()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); fn(); e1.record()
+        torch.cuda.synchronize()
+        ts.append(e0.elapsed_time(e1))
+    ts.sort()
+    return ts[len(ts) // 2]
+
+
+def run_extras(dev, model, hbm):
+    """cfg2 / cfg5 / cfg3 of BASELINE.json as short event-timed passes on one GPU (L2 flushed between reps)."""
+    import torch
+    from yolov8_vit_b200 import ops, synth
+    out = {}
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
+    # cfg2: decode + conf filter + custom_nms, batch 64 x 8400 anchors x 80 classes, 32 objects x 24 candidates
+    head = synth.make_head(64, 80, 8400, n_obj=32, n_jit=24, seed=synth.SEED0 + 2).to(dev)
+    ms = event_timed(lambda: ops.decode_filter(head, 0.35), 10, flush)
+    cand = ops.decode_filter(head, 0.35)
+    out["cfg2_decode"] = {"ms": ms, "gbs": head.numel() * 4 / ms / 1e6, "hbm_frac": head.numel() * 4 / ms / 1e6 / hbm,
+                          "shape": [64, 84, 8400]}
+    ms = event_timed(lambda: ops.nms_batched(cand[0], cand[1], cand[4], 0.45), 10, flush)
+    out["cfg2_nms"] = {"us_per_img": ms * 1e3 / 64, "ms": ms, "mean_candidates": float(cand[4].float().mean()), "iou": 0.45}
+    del head, cand
+    # cfg5: NMS stress, 32 images x 30 000 dense-overlap boxes, threshold sweep
+    boxes, scores = synth.make_nms_stress(32, 30000, seed=synth.SEED0 + 5)
+    boxes, scores = boxes.to(dev), scores.to(dev)
+    sweep = {}
+    for thr in (0.3, 0.4, 0.5, 0.6, 0.7):
+        ms = event_timed(lambda: ops.nms_batched(boxes, scores, None, thr), 3, flush)
+        _, kc = ops.nms_batched(boxes, scores, None, thr)
+        sweep[f"{thr:.1f}"] = {"us_per_img": ms * 1e3 / 32, "mean_keep": float(kc.float().mean())}
+    out["cfg5_nms_sweep"] = {"boxes_per_img": 30000, "batch": 32, "thr": sweep}
+    del boxes, scores
+    # cfg3: dilate + crop-resize 224 + ViT-B/16 forward, 256 crops
+    if model is not None:
+        imgs = synth.make_images(64, 640, 640, seed=synth.SEED0 + 3).to(dev)
+        cb = synth.make_boxes_int(256, 640, 640, seed=synth.SEED0 + 3).to(dev)
+        ci = (torch.arange(256, device=dev, dtype=torch.int32) % 64).contiguous()
+
+        def cfg3():
+            dil, _ = ops.dilate_boxes(cb, 640, 640)
+            p = ops.crop_resize(imgs, dil, ci, 256, "bilinear", 224, 16, "patch")
+            return model.forward_patches(p, 256)
+        ms = event_timed(cfg3, 5, flush)
+        out["cfg3_crop_vit"] = {"crops": 256, "ms": ms, "crops_per_s": 256 / ms * 1e3,
+                                "tflops_effective": 256 * FLOP_PER_CROP / ms / 1e9}
+    return out
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -223,9 +339,12 @@ def run_ours(args):
     head_h, imgs_h = make_inputs(B, SEED + 100 * rank)             # every rank owns its own shard
     head_h, imgs_h = head_h.pin_memory(), imgs_h.pin_memory()
     head_d, imgs_d = head_h.to(dev), imgs_h.to(dev)
-    rec_h = torch.empty(B, hp.cfg.max_det, 8, dtype=torch.float32).pin_memory()
-    rec_h2 = (rec_h, torch.empty_like(rec_h).pin_memory())         # two batches are in flight in the e2e loop
+    # the host-buffer loop alternates TWO different batches (the second: the same images in reverse order), so a
+    # stale or overwritten crop list would show up as wrong records
+    host_in = [(head_h, imgs_h), (head_h.flip(0).contiguous().pin_memory(), imgs_h.flip(0).contiguous().pin_memory())]
+    rec_h = [torch.empty(B, hp.cfg.max_det, 8, dtype=torch.float32).pin_memory() for _ in range(2)]
     gstream = torch.cuda.Stream(device=dev)
+    gather_ms = []
 
     def step_resident():
         r = hp(head_d, imgs_d)
@@ -233,25 +352,29 @@ def run_ours(args):
             gather_records(r.records, world * B)
         return r
 
-    def run_e2e(steps):
+    def run_e2e(steps, check=None):
         """K steps through the public host-buffer API, the way a serving loop uses it: submit_host(batch k+1)
         (pinned head + images -> sliced upload + detection on the front stream) is issued before
         result(batch k) (ViT + records -> pinned host buffer), so every step's 1.04 GB upload and its record
-        download are inside the timed region but overlap the previous step's ViT."""
-        pend = hp.submit_host(head_h, imgs_h, rec_h2[0], device=dev, vit_chunk=args.e2e_vit_chunk or None).launch()
-        r = None
+        download are inside the timed region but overlap the previous step's ViT.  `check` (untimed runs only):
+        [records of batch 0, records of batch 1] every step's download must equal."""
+        chunk = args.e2e_vit_chunk or None
+        pend = hp.submit_host(*host_in[0], rec_h[0], device=dev, vit_chunk=chunk).launch()
+        r, ok = None, True
         for k in range(steps):
             # batch k+1: upload + detection on the front stream, its ViT queued behind batch k's
-            nxt = hp.submit_host(head_h, imgs_h, rec_h2[(k + 1) & 1], device=dev,
-                                 vit_chunk=args.e2e_vit_chunk or None).launch() if k + 1 < steps else None
+            nxt = hp.submit_host(*host_in[(k + 1) & 1], rec_h[(k + 1) & 1], device=dev,
+                                 vit_chunk=chunk).launch() if k + 1 < steps else None
             r = pend.result()
+            if check is not None:
+                ok = ok and bool(torch.equal(rec_h[k & 1], check[k & 1]))
             if world > 1:          # the gather runs beside batch k+1's queued ViT, not behind it
                 with torch.cuda.stream(gstream):
                     r.records.record_stream(gstream)
                     gather_records(r.records, world * B)
                 gstream.synchronize()
             pend = nxt
-        return r
+        return r, ok
 
     def barrier():
         torch.cuda.synchronize()
@@ -269,30 +392,46 @@ def run_ours(args):
             r = fn()
         e1.record()
         barrier()
-        ms = e0.elapsed_time(e1)
+        own = e0.elapsed_time(e1)
+        ms, per_rank = own, [own]
         if world > 1:
-            t = torch.tensor([ms], device=dev)
-            dist.all_reduce(t, op=dist.ReduceOp.MAX)
-            ms = float(t.item())
-        return ms, r
+            t = torch.tensor([own], device=dev)
+            allt = [torch.zeros_like(t) for _ in range(world)]
+            dist.all_gather(allt, t)
+            per_rank = sorted(float(x.item()) for x in allt)
+            ms = per_rank[-1]
+        return ms, r, per_rank
 
     for _ in range(max(args.warmup, 3)):
         r = step_resident()
     w0 = time.monotonic()
-    ms, r = timed(step_resident, args.steps)
+    ms, r, per_rank = timed(step_resident, args.steps)
     windows = [(w0, time.monotonic())]
     # second pass of the same K steps with every launch event-bracketed on its stream: per-kernel
     # device time for the roofline (kept out of the headline timing: 2 events per launch)
-    ms_prof, _ = timed(step_resident, args.steps, prof=True)
+    ms_prof, _, _ = timed(step_resident, args.steps, prof=True)
     prof = _lib.prof_read()
     _lib.prof_enable(False)
     n_crops = r.n_crops
-    run_e2e(2)
+    if world > 1:                                  # event-timed duration of the final gather alone
+        for _ in range(5):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier()
+            e0.record(); gather_records(r.records, world * B); e1.record()
+            torch.cuda.synchronize()
+            gather_ms.append(e0.elapsed_time(e1))
+    # host-buffer loop: an untimed pass that also checks every download against the resident records of the same
+    # batch, then the timed pass
+    ref_rec = [hp(h.to(dev), im.to(dev)).records.cpu() for h, im in host_in]
+    _, e2e_ok = run_e2e(4, check=ref_rec)
     w0 = time.monotonic()
-    ms_e2e, _ = timed(lambda: run_e2e(args.steps), 1)
+    ms_e2e, _, _ = timed(lambda: run_e2e(args.steps)[0], 1)
     windows.append((w0, time.monotonic()))
     clk = clocks.stop(windows)                     # samples taken during the two timed regions
 
+    cfg4 = None
+    if world > 1 and not args.no_extras and args.workload == "north_star":
+        cfg4 = run_cfg4_strong(hp, dev, rank, world, barrier)
     if rank == 0:
         hbm, tf_burst, tf_sus, which = peaks()
         g = prof["gemm_tcgen05"]
@@ -314,29 +453,79 @@ def run_ours(args):
             "roofline": {"bound": "tensor", "kernel": "gemm_bf16_kernel (tcgen05)", "achieved": achieved,
                          "peak": tf_sus, "unit": "TFLOP/s", "frac": achieved / tf_sus,
                          "traffic": GEMM_DRAM_BYTES_PER_ROW * n_crops * 197,
-                         "traffic_note": "mean dram read+write bytes of the qkv/proj/fc1/fc2 launches of the one-pass "
-                                         "ViT (M = crops x 197 rows), ncu --set full (profiles/r01_vit_ncu_v7.md: "
-                                         "1265 MB at 1072 crops = the algorithmic bytes)",
+                         "traffic_note": GEMM_TRAFFIC_NOTE,
                          "peak_source": f"{which} bf16_tflops_sustained (kernel timed inside a long step)",
                          "launches_per_step": g["launches"] / args.steps,
                          "flops_per_launch": per_launch_flops, "ms_per_launch": per_launch_ms,
                          "share_of_step": g["ms"] / ms_prof},
             "stages_ms_per_step": stage_ms,
+            "step_tflops": {"achieved": n_crops * FLOP_PER_CROP * args.steps / (ms * 1e-3) / 1e12 , "peak": tf_sus,
+                            "frac": n_crops * FLOP_PER_CROP * args.steps / (ms * 1e-3) / 1e12 / tf_sus,
+                            "note": "whole step (all stages) per GPU against the sustained bf16 peak"},
             "decode_hbm": {"achieved_gbs": dec["work"] / max(dec["ms"], 1e-9) / 1e6, "peak_gbs": hbm,
                            "frac": dec["work"] / max(dec["ms"], 1e-9) / 1e6 / hbm},
             "nms_us_per_img": prof["nms"]["ms"] * 1e3 / (B * args.steps),
             "crops_per_s": world * n_crops * args.steps / (ms * 1e-3),
             "vit_tflops_effective": world * n_crops * FLOP_PER_CROP * args.steps / (ms * 1e-3) / 1e12,
+            "per_rank_ms_per_step": {"min": per_rank[0] / args.steps, "median": per_rank[len(per_rank) // 2] / args.steps,
+                                     "max": per_rank[-1] / args.steps},
             "e2e": {"value": world * B * args.steps / (ms_e2e * 1e-3), "unit": "images/s",
                     "h2d_bytes_per_step": head_h.numel() * 4 + imgs_h.numel(),
-                    "d2h_bytes_per_step": rec_h.numel() * 4 + 4, "ms_per_step": ms_e2e / args.steps},
+                    "d2h_bytes_per_step": rec_h[0].numel() * 4 + 4, "ms_per_step": ms_e2e / args.steps,
+                    "records_equal_resident": e2e_ok,
+                    "inputs": "two different batches alternate (the second = the first in reverse image order)"},
             "gpu_launches": launches, "clocks": clk,
         }
+        if gather_ms:
+            gather_ms.sort()
+            out["gather_records_ms"] = {"median": gather_ms[len(gather_ms) // 2], "max": gather_ms[-1],
+                                        "bytes_per_rank": r.records.numel() * 4}
+        if cfg4 is not None:
+            out["cfg4_strong"] = cfg4
+        if not args.no_extras and args.workload == "north_star":
+            out["extras"] = run_extras(dev, model, hbm)
         if not args.no_cpu_baseline and world == 1:
-            out["cpu_baseline"] = cpu_baseline(sd)
+            out["cpu_baseline"], oracle_res = cpu_baseline(sd, head_h, imgs_h)
+            v = verify(oracle_res, hp(head_d, imgs_d, keep_intermediates=True))
+            out["verified"] = bool(v.pop("ok")) and bool(e2e_ok)
+            out["verification"] = v
         print(json.dumps(out))
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
+
+
+def run_cfg4_strong(hp, dev, rank, world, barrier):
+    """BASELINE.json configs[3] as a sub-record at N > 1: 512 images of a YOLOv8s-1280 head [512,84,33600] +
+    512 images 1280x1280, sharded 512 / N per rank (strong scaling), final NCCL gather.  2 timed steps."""
+    import torch
+    import torch.distributed as dist
+    from yolov8_vit_b200 import synth
+    from yolov8_vit_b200.dist import gather_records
+    Bl = 512 // world
+    head = synth.make_head(Bl, nc=NC, A=33600, n_obj=N_OBJ, n_jit=N_JIT, img=1280, seed=SEED + 3 + 100 * rank).to(dev)
+    imgs = synth.make_images(Bl, 1280, 1280, seed=SEED + 4 + 100 * rank).to(dev)
+
+    def step():
+        r = hp(head, imgs)
+        gather_records(r.records, 512)
+        return r
+    for _ in range(2):
+        r = step()
+    barrier()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(2):
+        r = step()
+    e1.record()
+    barrier()
+    t = torch.tensor([e0.elapsed_time(e1), float(r.n_crops)], device=dev)
+    allt = [torch.zeros_like(t) for _ in range(world)]
+    dist.all_gather(allt, t)
+    ms = max(float(x[0]) for x in allt)
+    return {"workload": f"YOLOv8s-1280 head [512,84,33600] + 512 images 1280x1280 over {world} ranks ({Bl} per rank)",
+            "images_per_s": 512 * 2 / (ms * 1e-3), "ms_per_step": ms / 2, "steps": 2, "scaling": "strong",
+            "crops_total": int(sum(float(x[1]) for x in allt))}
 
 
 if __name__ == "__main__":

@@ -51,8 +51,11 @@ int yv_check_device(int dev);
  *   (x -/+ 0.5*w), then if unletterbox: (v - dwdh) / ratio.
  * Outputs, per image b, compacted in ASCENDING ANCHOR ORDER:
  *   boxes [B,cap,4] f32, scores [B,cap] f32, labels [B,cap] i32,
- *   anchors [B,cap] i32, counts [B] i32 (= number found; entries beyond
- *   `cap` are dropped, the count still reports them).
+ *   anchors [B,cap] i32, counts [B] i32 = entries WRITTEN = min(found, cap).
+ *   `cap` is a capacity bound, not a top-k: with cap < found the list is cut
+ *   in anchor order (the lowest anchors stay), so size it for the worst case
+ *   (cap = A never truncates).  A NaN class score wins the arg-max like
+ *   torch.max (first NaN's index) and passes the filter (!(NaN < conf)).
  * One kernel launch (+ one memset of the per-image tile counters).          */
 size_t yv_decode_filter_workspace_bytes(int B, int nc, int A);
 int yv_decode_filter(const float *head, int B, int nc, int A, float conf,
@@ -183,9 +186,14 @@ int yv_crop_resize(const uint8_t *images, int B, int H, int W,
 /* --- a5: ViT-B/{16,8} + Network_Wrapper head ------------------------------
  * utils/utils.py:59-87 (Network_Wrapper: timm ViT -> ReLU -> Linear(1000,128)
  * -> ReLU -> Linear(128,num_classes)); timm vit_base_patch{16,8}_224
- * architecture (pre-norm, LN eps 1e-6, erf-GELU, class token, learned
+ * architecture (pre-norm, LN eps 1e-6, GELU, class token, learned
  * pos-embed, final norm, class-token pooling).  bf16 operands, fp32
- * accumulation (tcgen05 / TMEM), fp32 LayerNorm and softmax statistics.     */
+ * accumulation (tcgen05 / TMEM), fp32 LayerNorm and softmax statistics.
+ * GELU: timm's nn.GELU is the erf form x * Phi(x); the fc1 epilogue
+ * evaluates the TANH form 0.5 x (1 + tanh(sqrt(2/pi) (x + 0.044715 x^3)))
+ * with tanh.approx.f32 -- a deliberate arithmetic deviation (|diff| <= 4.8e-4
+ * absolute per activation, below the bf16 rounding of the stored value) that
+ * is part of the 1e-2 logit tolerance, not a bit-exact restatement.          */
 typedef struct yv_vit yv_vit_t;
 typedef struct {
   int32_t img, patch, dim, depth, heads, mlp, head_out, hidden, num_classes;
@@ -212,13 +220,19 @@ int yv_vit_forward(yv_vit_t *m, const void *patches_bf16, int n,
 
 /* --- building blocks of a5, exported for the parity tests ------------------ */
 /* D[M,N] = A[M,K] * W[N,K]^T (+bias[N]) (+GELU) (+residual[M,N]); A, W bf16
- * row-major; D bf16 (out_f32 = 0) or f32.  tcgen05.mma, TMEM accumulators,
- * TMA-fed.  K % 64 == 0, N % 8 == 0.  residual is bf16 [M,N] (or NULL).     */
+ * row-major; D bf16 (out_type 0), f32 (1) or f16 (2).  tcgen05.mma, TMEM
+ * accumulators, TMA-fed.  K % 64 == 0, N % 8 == 0.  residual (or NULL) is bf16
+ * [M,N] for bf16 / f32 outputs; for an f16 output it is f16 and MAY ALIAS D --
+ * the ViT's residual-stream update x += A W^T + b, whose 32 x 32 boxes travel
+ * by TMA in both directions (no GELU with an f16 output).                     */
 #define YV_EPI_NONE 0
 #define YV_EPI_GELU 1
+#define YV_OUT_BF16 0
+#define YV_OUT_F32 1
+#define YV_OUT_F16 2
 int yv_gemm_bf16(const void *A, const void *W, const float *bias,
                  const void *residual, void *D, int M, int N, int K, int epi,
-                 int out_f32, yv_stream_t stream);
+                 int out_type, yv_stream_t stream);
 /* y = LayerNorm(x) * g + b over the last dim; x,y bf16 [rows,dim]; fp32 stats */
 int yv_layernorm_bf16(const void *x, const float *gamma, const float *beta,
                       void *y, int rows, int dim, float eps,

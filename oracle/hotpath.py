@@ -247,51 +247,10 @@ class ViTConfig:
 
 
 def make_vit_weights(cfg: ViTConfig = ViTConfig(), seed: int = 20240410, fc_gain: float = 8.0):
-    """Seeded synthetic ``Network_Wrapper.state_dict()`` (keys ``model.*`` in
-    timm naming + ``fc.1.*``/``fc.3.*``, utils/utils.py:59-69).  trunc-normal
-    0.02 like timm's init; ``fc`` scaled by ``fc_gain`` so top-1 margins are
-    well above bf16 noise (no trained weights exist in the tree).  Values are
-    rounded to bf16-representable fp32 so oracle and GPU see identical weights."""
-    g = torch.Generator().manual_seed(seed)
-    D, P = cfg.dim, cfg.patch
-
-    def tn(*shape, std=0.02):
-        t = torch.empty(*shape)
-        torch.nn.init.trunc_normal_(t, std=std, a=-2 * std, b=2 * std, generator=g)
-        return t.to(torch.bfloat16).to(torch.float32)
-
-    def small(*shape, std=0.02):
-        return (torch.randn(*shape, generator=g) * std).to(torch.bfloat16).to(torch.float32)
-
-    sd = {
-        "model.cls_token": tn(1, 1, D),
-        "model.pos_embed": tn(1, cfg.tokens, D),
-        "model.patch_embed.proj.weight": tn(D, 3, P, P),
-        "model.patch_embed.proj.bias": small(D),
-    }
-    for i in range(cfg.depth):
-        p = f"model.blocks.{i}."
-        sd[p + "norm1.weight"] = (1.0 + small(D, std=0.1)).to(torch.bfloat16).to(torch.float32)
-        sd[p + "norm1.bias"] = small(D)
-        sd[p + "attn.qkv.weight"] = tn(3 * D, D, std=0.04)
-        sd[p + "attn.qkv.bias"] = small(3 * D)
-        sd[p + "attn.proj.weight"] = tn(D, D)
-        sd[p + "attn.proj.bias"] = small(D)
-        sd[p + "norm2.weight"] = (1.0 + small(D, std=0.1)).to(torch.bfloat16).to(torch.float32)
-        sd[p + "norm2.bias"] = small(D)
-        sd[p + "mlp.fc1.weight"] = tn(cfg.mlp, D)
-        sd[p + "mlp.fc1.bias"] = small(cfg.mlp)
-        sd[p + "mlp.fc2.weight"] = tn(D, cfg.mlp)
-        sd[p + "mlp.fc2.bias"] = small(D)
-    sd["model.norm.weight"] = (1.0 + small(D, std=0.1)).to(torch.bfloat16).to(torch.float32)
-    sd["model.norm.bias"] = small(D)
-    sd["model.head.weight"] = tn(cfg.head_out, D, std=0.04)
-    sd["model.head.bias"] = small(cfg.head_out, std=0.2)
-    sd["fc.1.weight"] = tn(cfg.hidden, cfg.head_out, std=0.02 * fc_gain)
-    sd["fc.1.bias"] = small(cfg.hidden, std=0.1)
-    sd["fc.3.weight"] = tn(cfg.num_classes, cfg.hidden, std=0.02 * fc_gain)
-    sd["fc.3.bias"] = small(cfg.num_classes, std=0.1)
-    return sd
+    """Seeded synthetic ``Network_Wrapper.state_dict()``: the shared generator lives with the other synthetic
+    inputs (yolov8_vit_b200/synth.py) so that the product-side processes never import ``oracle/``."""
+    from yolov8_vit_b200 import synth
+    return synth.make_vit_weights(cfg, seed, fc_gain)
 
 
 @torch.no_grad()
@@ -355,15 +314,16 @@ def timm_to_torchvision(sd) -> dict:
 @torch.no_grad()
 def pipeline_image(head, image, sd=None, cfg: ViTConfig = ViTConfig(), conf=0.35, iou=0.45,
                    alpha=(1, 10), mode="full", interp="bilinear", max_det=100,
-                   ratio=1.0, dwdh=(0.0, 0.0)):
+                   ratio=1.0, dwdh=(0.0, 0.0), nms_fn=None):
     """One image through the whole second stage, in the order of the wrapper's
     per-image loop (YOLOTensorRT_yolodet_py_解读.md:64-100 + the authors' bracketed
     additions): decode + conf filter -> custom_nms -> round (D6)
     -> dilate + clamp -> crop/resize/normalise -> ViT -> argmax.  ``max_det``
     truncates the keep list in score order (engine top-100, test.ipynb:22).
+    ``nms_fn`` substitutes another implementation of ``custom_nms`` (the reference's own text from oracle/_ref).
     Returns a dict of per-detection arrays (keep order = descending score)."""
     boxes, scores, labels, anchors = decode_head(head, conf, ratio, dwdh)
-    keep = custom_nms(boxes, scores, iou)[:max_det]
+    keep = (nms_fn or custom_nms)(boxes, scores, iou)[:max_det]
     kb = round_boxes(boxes[keep]) if keep else torch.zeros(0, 4, dtype=torch.int32)
     H, W = image.shape[:2]
     crops, cboxes, valid = [], [], []

@@ -51,3 +51,59 @@ def test_gemm_many_tiles_persistent_phases():
     _close(ops.gemm_bf16(a, w, bias=bias, out_f32=True), ref, 1e-4, 2e-3)
     # determinism
     assert torch.equal(ops.gemm_bf16(a, w, bias=bias), ops.gemm_bf16(a, w, bias=bias))
+
+
+@pytest.mark.parametrize("M,N,K", [(197 * 5, 768, 768), (1000, 768, 3072), (129, 264, 128), (31, 40, 64), (256 * 5 + 7, 512, 256)])
+def test_gemm_fp16_residual_stream_update(M, N, K):
+    """The fused residual form: x16 = x16 + a w^T + b, residual boxes in and sums out by TMA (fp16 stream).  Row /
+    column counts that are not multiples of the 32 x 32 box exercise the clipped loads and stores; in place and
+    with a separate output.  Tolerance: fp16 output rounding (2^-11 relative) + accumulation-order noise."""
+    a, w, bias = _mk(M, N, K, seed=M + N + K + 1)
+    x = (torch.randn(M, N, device=DEV) * 1.5).to(torch.float16)
+    ref = x.float() + a.float() @ w.float().t() + bias
+    out = torch.full((M, N), float("nan"), dtype=torch.float16, device=DEV)
+    ops.gemm_bf16(a, w, bias=bias, residual=x, out=out)
+    _close(out, ref, 2e-3, 2e-3)
+    xi = x.clone()
+    ops.gemm_bf16(a, w, bias=bias, residual=xi, out=xi)                 # in place
+    assert torch.equal(xi, out)
+    # no residual, fp16 output (LSU form)
+    o2 = torch.empty(M, N, dtype=torch.float16, device=DEV)
+    ops.gemm_bf16(a, w, bias=bias, out=o2)
+    _close(o2, a.float() @ w.float().t() + bias, 2e-3, 2e-3)
+
+
+def test_gemm_fp16_stream_saturates_instead_of_overflowing():
+    a = torch.full((64, 64), 8.0, dtype=torch.bfloat16, device=DEV)
+    w = torch.full((32, 64), 8.0, dtype=torch.bfloat16, device=DEV)      # 64 * 64 = 4096 per output
+    x = torch.full((64, 32), 65000.0, dtype=torch.float16, device=DEV)
+    ops.gemm_bf16(a, w, residual=x, out=x)
+    assert bool(torch.isfinite(x).all()) and float(x.max()) == 65504.0
+
+
+@pytest.mark.parametrize("name,N,K,kw", [("qkv", 2304, 768, {}), ("proj", 768, 768, {"stream": True}),
+                                         ("fc1", 3072, 768, {"gelu": True}), ("fc2", 768, 3072, {"stream": True})])
+def test_gemm_block_shapes_at_bench_m(name, N, K, kw):
+    """The four block GEMMs at the BENCHMARKED row count (1072 crops x 197 = 211 184 rows, 825 row tiles, one
+    pass) against torch.matmul in fp32 on sampled rows: first / last rows, both sides of CTA-pair tile (256) and
+    TMA box (32) boundaries, and 64 random rows."""
+    M = 1072 * 197
+    g = torch.Generator(device="cpu").manual_seed(N + K)
+    a = (torch.randn(M, K, generator=g, dtype=torch.float32) * 0.5).to(torch.bfloat16).to(DEV)
+    w = (torch.randn(N, K, generator=g) * 0.05).to(torch.bfloat16).to(DEV)
+    bias = (torch.randn(N, generator=g) * 0.1).to(DEV)
+    rows = sorted(set([0, 1, 31, 32, 127, 128, 255, 256, 257, M // 2, 824 * 256 - 1, 824 * 256, M - 33, M - 32, M - 2, M - 1]
+                      + torch.randint(0, M, (64,), generator=g).tolist()))
+    ri = torch.tensor(rows, device=DEV)
+    base = a[ri].float() @ w.float().t() + bias
+    if kw.get("stream"):
+        x = (torch.randn(M, N, device=DEV) * 1.5).to(torch.float16)
+        ref = x[ri].float() + base
+        ops.gemm_bf16(a, w, bias=bias, residual=x, out=x)
+        _close(x[ri], ref, 2e-3, 2e-3)
+    elif kw.get("gelu"):
+        got = ops.gemm_bf16(a, w, bias=bias, gelu=True)
+        _close(got[ri], torch.nn.functional.gelu(base), 1e-2, 1e-2)
+    else:
+        got = ops.gemm_bf16(a, w, bias=bias)
+        _close(got[ri], base, 1e-2, 1e-2)

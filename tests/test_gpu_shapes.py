@@ -1,0 +1,174 @@
+"""GPU parity at the shapes that are BENCHMARKED and named in BASELINE.json (through the C-ABI):
+
+  * the bench workload itself: 256 images -> 1072 crops -> ONE ViT pass (M = 211 184 token rows):
+    keep lists and crop boxes bit-exact for all 256 images, logits <= 1e-2 / identical top-1 on 64 crops sampled
+    over the whole row range (first, last, CTA-pair-tile boundaries);
+  * > 2048 crops: the balanced multi-pass branch of yv_vit_forward;
+  * cfg5 at its stated size: 32 images x 30 000 boxes x thr {0.3, 0.4, 0.5, 0.6, 0.7}, keep lists bit-exact;
+  * a NaN class score in the decode (torch.max propagates NaN);
+  * two DISTINCT consecutive batches at bench scale through the launch-ahead host-buffer loop (the serving
+    loop bench.py times): every batch gets the records of its own resident run.
+"""
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import hotpath as O          # checker only
+from oracle import nms_c
+from yolov8_vit_b200 import HotPath, HotPathConfig, ViTConfig, ViTModel, ops, synth
+
+DEV = "cuda:0"
+REL_TOL = 1e-2
+BENCH_SEED = 20240410 + 1                # bench.py's SEED
+
+
+def rel_err(got, ref):
+    return float((got - ref).abs().max() / ref.abs().max())
+
+
+@pytest.fixture(scope="module")
+def bench_model():
+    sd = synth.make_vit_weights(ViTConfig(), seed=BENCH_SEED)
+    return ViTModel(ViTConfig(), DEV).load_state_dict(sd), sd
+
+
+def bench_inputs(batch=256, seed=BENCH_SEED):
+    """bench.py's make_inputs for the north-star workload (4 objects x 24 candidates per image)."""
+    head = synth.make_head(batch, nc=80, A=8400, n_obj=4, n_jit=24, img=640, seed=seed)
+    imgs = synth.make_images(batch, 640, 640, seed=seed + 1)
+    return head, imgs
+
+
+def test_bench_workload_one_pass_parity(bench_model):
+    m, sd = bench_model
+    head, imgs = bench_inputs()
+    r = HotPath(m, HotPathConfig())(head.to(DEV), imgs.to(DEV), keep_intermediates=True)
+    assert r.n_crops == 1072, r.n_crops                   # the workload the driver's line is quoted on
+    keep, kc = r.keep.cpu(), r.keep_counts.cpu()
+    det_count, det_box, det_cb = r.crops.det_count.cpu(), r.crops.det_box.cpu(), r.crops.det_crop_box.cpu()
+    det_crop = r.crops.det_crop.cpu()
+    crop_of = {}                                          # crop index -> (image, detection, crop box)
+    for b in range(256):
+        boxes, scores, labels, anchors = O.decode_head(head[b], 0.35)
+        ref_keep = nms_c.nms(boxes.numpy(), scores.numpy(), 0.45)[:100]
+        assert keep[b, :int(kc[b])].tolist() == ref_keep, b
+        n = int(det_count[b])
+        assert n == len(ref_keep)
+        rb = O.round_boxes(boxes[ref_keep])
+        assert torch.equal(det_box[b, :n], rb), b
+        for k in range(n):
+            x0, y0, x1, y1, ok = O.dilate_box(*rb[k].tolist(), 640, 640)
+            assert det_cb[b, k].tolist() == [x0, y0, x1, y1] and ok
+            crop_of[int(det_crop[b, k])] = (b, k, (x0, y0, x1, y1))
+    assert sorted(crop_of) == list(range(1072))
+    # 64 crops over the whole token-row range: first / last crops, the crops on both sides of CTA-pair tile
+    # boundaries (256 rows = 1.3 crops) in the middle and at the end, and random ones
+    g = torch.Generator().manual_seed(1)
+    sel = sorted(set([0, 1, 2, 535, 536, 537, 1069, 1070, 1071] + torch.randint(0, 1072, (80,), generator=g).tolist()))[:64]
+    x = torch.from_numpy(np.stack([O.crop_resize_norm(imgs[crop_of[c][0]].numpy(), crop_of[c][2], 224, "bilinear") for c in sel]))
+    ref = O.vit_forward(sd, x)
+    got = r.logits[sel].cpu()
+    assert rel_err(got, ref) <= REL_TOL, rel_err(got, ref)
+    assert r.top1[sel].cpu().tolist() == ref.argmax(1).tolist()
+    rec = r.records.cpu()
+    for c, row in zip(sel, ref.argmax(1).tolist()):
+        b, k, _ = crop_of[c]
+        assert int(rec[b, k, 4]) == row and rec[b, k, 7] == 1
+
+
+def test_vit_more_than_one_pass(bench_model):
+    """2100 crops > the 2048-crop pass limit: two balanced passes of 1050.  Rows are independent, so every crop
+    must get the logits it gets in a small batch; oracle on crops of both passes."""
+    m, sd = bench_model
+    imgs = synth.make_images(8, 640, 640, seed=3).to(DEV)
+    boxes = synth.make_boxes_int(2100, seed=5).to(DEV)
+    dil, valid = ops.dilate_boxes(boxes, 640, 640)
+    assert bool(valid.all())
+    idx = (torch.arange(2100, device=DEV) % 8).to(torch.int32)
+    p = ops.crop_resize(imgs, dil, idx, 2100, "bilinear", 224, 16, "patch")
+    la, ta = m.forward_patches(p, 2100)
+    for lo, hi in ((0, 40), (1030, 1070), (2060, 2100)):            # start, the pass boundary (1050), end
+        lb, tb = m.forward_patches(p[lo * 196:hi * 196].contiguous(), hi - lo)
+        assert torch.allclose(la[lo:hi], lb, rtol=1e-3, atol=1e-3) and torch.equal(ta[lo:hi], tb)
+    sel = [0, 1049, 1050, 1051, 2099]
+    chw = ops.crop_resize(imgs, dil[sel].contiguous(), idx[sel].contiguous(), len(sel), "bilinear", 224, 16, "chw")
+    ref = O.vit_forward(sd, chw.cpu())
+    assert rel_err(la[sel].cpu(), ref) <= REL_TOL
+    assert ta[sel].cpu().tolist() == ref.argmax(1).tolist()
+
+
+@pytest.mark.parametrize("thr", [0.3, 0.4, 0.5, 0.6, 0.7])
+def test_nms_cfg5_full_batch_bit_exact(thr):
+    """BASELINE.json configs[4] at its stated size: 32 images x 30 000 dense-overlap boxes, the whole threshold
+    sweep, every keep list against the C restatement of custom_nms (pinned to the reference's text in test_ref.py)."""
+    boxes, scores = synth.make_nms_stress(32, 30000, seed=synth.SEED0 + 5)
+    keep, kc = ops.nms_batched(boxes.to(DEV), scores.to(DEV), None, thr)
+    keep, kc = keep.cpu(), kc.cpu()
+    bn, sn = boxes.numpy(), scores.numpy()
+    for b in range(32):
+        assert keep[b, :int(kc[b])].tolist() == nms_c.nms(bn[b], sn[b], thr), (thr, b)
+
+
+def test_decode_nan_scores_follow_torch_max():
+    """A NaN class score wins the per-anchor arg-max like torch.max (the FIRST NaN's index) and passes the filter
+    (not (NaN < conf)); the kept score is NaN."""
+    head = synth.make_head(2, 80, 8400, n_obj=3, n_jit=5, seed=14)
+    nan = float("nan")
+    head[0, 4 + 0, 100] = nan                      # NaN in class 0
+    head[0, 4 + 7, 200] = nan                      # NaN in a later class
+    head[0, 4 + 9, 200] = nan                      # ... and a second one: the first wins
+    head[0, 4 + 79, 300] = nan                     # last class (the loop tail)
+    head[1, 4 + 33, 8399] = nan                    # last anchor
+    head[1, 4 + 2, 17] = nan; head[1, 4 + 3, 17] = 0.99       # a number after a NaN does not replace it
+    bx, sc, lb, an, cnt = [t.cpu() for t in ops.decode_filter(head.to(DEV), 0.35)]
+    for b in range(2):
+        rb, rs, rl, ra = O.decode_head(head[b], 0.35)
+        k = int(cnt[b])
+        assert k == rb.shape[0] and an[b, :k].tolist() == ra.tolist() and lb[b, :k].tolist() == rl.tolist()
+        assert torch.equal(torch.isnan(sc[b, :k]), torch.isnan(rs))
+        ok = ~torch.isnan(rs)
+        assert torch.equal(sc[b, :k][ok], rs[ok]) and torch.equal(bx[b, :k], rb)
+    a0 = an[0, :int(cnt[0])].tolist()
+    assert lb[0, a0.index(100)] == 0 and lb[0, a0.index(200)] == 7 and lb[0, a0.index(300)] == 79
+    a1 = an[1, :int(cnt[1])].tolist()
+    assert lb[1, a1.index(8399)] == 33 and lb[1, a1.index(17)] == 2
+
+
+def test_decode_count_is_clamped_to_cap():
+    head = synth.make_head(2, 80, 8400, n_obj=8, n_jit=24, seed=15)
+    full = [t.cpu() for t in ops.decode_filter(head.to(DEV), 0.35)]
+    assert int(full[4].min()) > 64
+    cut = [t.cpu() for t in ops.decode_filter(head.to(DEV), 0.35, cap=64)]
+    assert cut[4].tolist() == [64, 64]
+    for b in range(2):                             # the first `cap` candidates in anchor order
+        assert torch.equal(cut[3][b], full[3][b, :64]) and torch.equal(cut[1][b], full[1][b, :64])
+
+
+def test_host_loop_distinct_batches_at_bench_scale(bench_model):
+    """The serving loop of bench.py's `e2e` with DIFFERENT consecutive batches of 256 images (the ViT of batch k
+    runs for tens of ms while the front stream already uploads and post-processes batch k+1 and k+2): each batch
+    must deliver exactly the records / logits of its own resident run -- crop lists allocated on the front stream
+    stay alive until the caller's stream has packed the results."""
+    m, _ = bench_model
+    hp = HotPath(m, HotPathConfig())
+    batches = []
+    for i in range(3):
+        head, imgs = bench_inputs(256, BENCH_SEED + 10 * i)
+        if i == 1:
+            head = head.flip(0).contiguous()       # same content, different image order: different crop lists
+        batches.append((head.pin_memory(), imgs.pin_memory()))
+    refs = [hp(h.to(DEV), im.to(DEV)) for h, im in batches]
+    torch.cuda.synchronize()
+    order = [0, 1, 2, 0, 1, 2]
+    outs = [torch.empty(256, 100, 8).pin_memory() for _ in order]
+    pend = hp.submit_host(*batches[order[0]], outs[0], device=DEV).launch()
+    for k, bi in enumerate(order):
+        nxt = hp.submit_host(*batches[order[k + 1]], outs[k + 1], device=DEV).launch() if k + 1 < len(order) else None
+        r = pend.result()
+        assert r.n_crops == refs[bi].n_crops, k
+        assert torch.equal(outs[k], refs[bi].records.cpu()), k
+        assert torch.equal(r.records, refs[bi].records) and torch.equal(r.top1, refs[bi].top1), k
+        assert torch.equal(r.logits, refs[bi].logits), k
+        pend = nxt

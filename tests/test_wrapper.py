@@ -37,6 +37,30 @@ def test_path_to_list_and_trtmodule(tmp_path):
         TRTModule("best.engine", "cuda:0")
 
 
+def test_draw_image_draws_in_place():
+    """draw_image(image, box, cls) (app.py:16 imports it; 解读.md:35-45): rectangle + label in the class colour."""
+    from yolov8_vit_b200.YOLOTensorRT import draw_image, COLORS
+    img = np.zeros((120, 160, 3), np.uint8)
+    out = draw_image(img, [20, 40, 100, 90], 1)
+    assert out is img
+    assert tuple(img[40, 60]) == COLORS[1] and tuple(img[90, 60]) == COLORS[1]       # top / bottom edges
+    assert tuple(img[60, 20]) == COLORS[1] and tuple(img[60, 100]) == COLORS[1]      # left / right edges
+    assert (img[44:86, 24:96] == 0).all()                                            # interior untouched
+    assert (img[15:39, 20:120] == np.array(COLORS[1])).all(-1).any()                 # label text above the box
+
+
+def test_torchvision_state_dict_keys_map_to_timm_names():
+    from yolov8_vit_b200.vit import torchvision_to_timm
+    sd = O.make_vit_weights(O.ViTConfig(depth=2), seed=3)
+    tv = O.timm_to_torchvision(sd)
+    assert "model.encoder.layers.encoder_layer_1.self_attention.in_proj_weight" in tv and "fc.3.bias" in tv
+    back = torchvision_to_timm(tv)
+    assert set(back) == set(sd) and all(back[k] is sd[k] for k in sd)
+    assert torchvision_to_timm(sd) is sd                                             # already timm naming
+    bare = {k[len("model."):]: v for k, v in tv.items() if k.startswith("model.")}   # a plain torchvision ViT
+    assert set(torchvision_to_timm(bare)) == {k for k in sd if k.startswith("model.")}
+
+
 def test_generate_annotation_tags(tmp_path):
     p = generate_annotation("", "img1.jpg", "img1.jpg", [{"sort": "lose", "xmin": 1, "ymin": 2, "xmax": 30, "ymax": 40},
                                                          {"sort": 4, "xmin": 5, "ymin": 6, "xmax": 7, "ymax": 8}], str(tmp_path))

@@ -22,6 +22,9 @@ from .. import ops
 from ..pipeline import HotPath, HotPathConfig
 
 CLASSES = ["good", "broke", "lose", "uncovered", "circle"]          # utils/utils.py:174-181 order
+# one BGR colour per class (the upstream wrapper's config.COLORS is in the un-vendored submodule: any fixed
+# palette indexed like CLASSES serves, 解读.md:25)
+COLORS = [(0, 200, 0), (0, 0, 230), (0, 165, 255), (255, 128, 0), (200, 0, 200)]
 _SUFFIXES = (".bmp", ".dng", ".jpeg", ".jpg", ".mpo", ".png", ".tif", ".tiff", ".webp", ".pfm")
 
 
@@ -62,6 +65,22 @@ def det_postprocess(data):
     num_dets, bboxes, scores, labels = (d[0] for d in data)
     n = int(num_dets.item()) if num_dets.numel() == 1 else int(num_dets[0].item())
     return bboxes[:n], scores[:n], labels[:n]
+
+
+def draw_image(image: np.ndarray, box, cls):
+    """``draw_image(image, box, cls)`` of the wrapper (imported by app.py:16; described in
+    YOLOTensorRT_yolodet_py_解读.md:35-45): draws the box ``[xmin, ymin, xmax, ymax]`` with ``cv2.rectangle`` in the
+    class colour and the label ``CLASSES[cls]`` followed by the fixed ``:1`` the upstream code prints, with
+    ``cv2.putText`` at the box's top-left corner, IN PLACE on the BGR image.  Host-side visualisation (cv2),
+    not part of the GPU path; returns the image for convenience."""
+    import cv2
+    cls = int(cls)
+    color = COLORS[cls % len(COLORS)]
+    name = CLASSES[cls] if 0 <= cls < len(CLASSES) else str(cls)
+    x0, y0, x1, y1 = (int(v) for v in box)
+    cv2.rectangle(image, (x0, y0), (x1, y1), color, 2)
+    cv2.putText(image, f"{name}:1", (x0, max(y0 - 2, 0)), cv2.FONT_HERSHEY_SIMPLEX, 0.75, color, thickness=2)
+    return image
 
 
 def _model_of(net):

@@ -1,6 +1,9 @@
 // api.cu -- library-level entry points and error plumbing of libyv8vit.so.
 #include "common.cuh"
 #include <string.h>
+#include <atomic>
+#include <mutex>
+#include <nvtx3/nvToolsExt.h>   // header-only NVTX v3: a no-op unless a profiler injects itself
 
 static thread_local char g_err[512] = "";
 
@@ -16,14 +19,35 @@ int yv_cuda_fail(cudaError_t e, const char *what, const char *file, int line) {
   return YV_ECUDA;
 }
 
+// ---- per-device state: one process may drive several GPUs (ViTModel(device='cuda:1')) ------------------
+constexpr int YV_MAX_DEVICES = 64;
+
 int yv_num_sms() {
-  static int sms = 0;
-  if (sms == 0) {
-    int dev = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess) return 148;
-    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0) sms = 148;
+  static std::atomic<int> sms[YV_MAX_DEVICES];
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= YV_MAX_DEVICES) return 148;
+  int v = sms[dev].load(std::memory_order_relaxed);
+  if (v == 0) {
+    if (cudaDeviceGetAttribute(&v, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || v <= 0) v = 148;
+    sms[dev].store(v, std::memory_order_relaxed);
   }
-  return sms;
+  return v;
+}
+
+// Runs `fn` once per (slot, current device) -- cudaFuncSetAttribute(MaxDynamicSharedMemorySize) applies to the
+// current device only -- under a lock, so concurrent first use from several threads is safe.  A failing `fn`
+// is retried by the next caller.
+int yv_device_once(int slot, int (*fn)()) {
+  static std::mutex mu;
+  static bool done[YV_INIT_COUNT][YV_MAX_DEVICES];
+  int dev = 0;
+  YV_CUDA(cudaGetDevice(&dev));
+  YV_REQUIRE(slot >= 0 && slot < YV_INIT_COUNT && dev >= 0 && dev < YV_MAX_DEVICES, "yv_device_once: slot %d / device %d out of range", slot, dev);
+  std::lock_guard<std::mutex> lk(mu);
+  if (done[slot][dev]) return YV_OK;
+  const int rc = fn();
+  if (rc == YV_OK) done[slot][dev] = true;
+  return rc;
 }
 
 YV_EXPORT int yv_version(void) { return 100; }
@@ -41,8 +65,7 @@ YV_EXPORT int yv_check_device(int dev) {
   return YV_OK;
 }
 
-// ---- launch accounting + optional event profiling ------------------------------------------------
-#include <mutex>
+// ---- launch accounting + optional event profiling + NVTX ranges -------------------------------------
 #include <vector>
 namespace {
 struct ProfState {
@@ -62,6 +85,7 @@ cudaEvent_t prof_event() {
 }  // namespace
 
 void yv_prof_begin(int kind, cudaStream_t s, double work) {
+  nvtxRangePushA(yv_prof_kind_name(kind));       // one NVTX range per launch, named after the kernel class
   std::lock_guard<std::mutex> lk(g_prof.mu);
   g_prof.launches[kind] += 1;
   g_prof.work[kind] += work;
@@ -72,12 +96,15 @@ void yv_prof_begin(int kind, cudaStream_t s, double work) {
   }
 }
 void yv_prof_end(int kind, cudaStream_t s) {
-  std::lock_guard<std::mutex> lk(g_prof.mu);
-  if (g_prof.on && (g_prof.ev[kind].size() & 1)) {
-    cudaEvent_t e = prof_event();
-    cudaEventRecord(e, s);
-    g_prof.ev[kind].push_back(e);
+  {
+    std::lock_guard<std::mutex> lk(g_prof.mu);
+    if (g_prof.on && (g_prof.ev[kind].size() & 1)) {
+      cudaEvent_t e = prof_event();
+      cudaEventRecord(e, s);
+      g_prof.ev[kind].push_back(e);
+    }
   }
+  nvtxRangePop();
 }
 
 // on != 0: reset counters and start bracketing every kernel launch with CUDA events; 0: stop.

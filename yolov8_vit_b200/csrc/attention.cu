@@ -226,11 +226,11 @@ int yv_attention_long_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n
   const int qblocks = (groups + ATT_MAXW - 1) / ATT_MAXW;
   const int nw = (groups + qblocks - 1) / qblocks;        // <= ATT_MAXW warps
   const size_t smem = (size_t)(nw * 16 + 6 * ATT_KB) * ATT_LD * sizeof(__nv_bfloat16);
-  static bool attr_set = false;
-  if (!attr_set) {
+  int rc = yv_device_once(YV_INIT_ATTN_LONG, []() -> int {
     YV_CUDA(cudaFuncSetAttribute(attention_long_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-    attr_set = true;
-  }
+    return YV_OK;
+  });
+  if (rc) return rc;
   dim3 grid(qblocks, heads, n);
   const float scale_log2e = (1.0f / sqrtf((float)dh)) * 1.4426950408889634f;
   YvProf prof(YV_K_ATTN, s, 4.0 * n * heads * (double)T * T * dh);

@@ -638,12 +638,12 @@ int yv_attention_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, int
   if (rc) return rc;
   rc = yv_tmap_bf16_2d(&tmKV, qkv, (uint64_t)n * T, (uint64_t)3 * D, (uint32_t)NK);
   if (rc) return rc;
-  static bool attr_set = false;
-  if (!attr_set) {
+  rc = yv_device_once(YV_INIT_ATTN, []() -> int {
     YV_CUDA(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
     YV_CUDA(cudaFuncSetAttribute(attention_pipe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AP_SMEM));
-    attr_set = true;
-  }
+    return YV_OK;
+  });
+  if (rc) return rc;
   YvProf prof(YV_K_ATTN, s, 4.0 * n * heads * (double)T * T * dh);
   if (pipelined) {
     const int units = n * heads;

@@ -37,7 +37,10 @@ int yv_cuda_fail(cudaError_t e, const char *what, const char *file, int line);
   } while (0)
 
 static inline size_t yv_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
-int yv_num_sms();
+int yv_num_sms();                                  // of the CURRENT device (cached per device)
+// one-time setup per (slot, current device), thread-safe: cudaFuncSetAttribute and friends (api.cu)
+enum YvInitSlot { YV_INIT_GEMM = 0, YV_INIT_ATTN, YV_INIT_ATTN_LONG, YV_INIT_COUNT };
+int yv_device_once(int slot, int (*fn)());
 
 // ---- launch accounting / optional CUDA-event profiling (api.cu) ------------------------------
 enum YvKernelKind { YV_K_DECODE = 0, YV_K_NMS, YV_K_BUILD, YV_K_CROP, YV_K_GEMM, YV_K_LN, YV_K_ATTN, YV_K_HEAD, YV_K_MISC, YV_K_COUNT };

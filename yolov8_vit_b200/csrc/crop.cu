@@ -138,13 +138,14 @@ build_crops_kernel(const float4 *__restrict__ boxes, const float *__restrict__ s
     if (lane == 31) s_warp[warp] = incl;
     __syncthreads();
     if (warp == 0) {
-      int v = s_warp[lane], inc2 = v;
+      // s_warp has BC_T / 32 entries: lanes past that neither read nor write it
+      int v = lane < BC_T / 32 ? s_warp[lane] : 0, inc2 = v;
 #pragma unroll
       for (int d = 1; d < 32; d <<= 1) {
         int t = __shfl_up_sync(0xffffffffu, inc2, d);
         if (lane >= d) inc2 += t;
       }
-      s_warp[lane] = inc2 - v;
+      if (lane < BC_T / 32) s_warp[lane] = inc2 - v;
     }
     __syncthreads();
     const int excl = s_carry + s_warp[warp] + incl - nvalid;

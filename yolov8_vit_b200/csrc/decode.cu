@@ -76,7 +76,9 @@ decode_filter_kernel(const float *__restrict__ head, int nc, int A, float conf, 
 
   if (in_range) {
     const float *cp = hp + (size_t)BOXROWS * A + a0;
-    {  // class 0 initialises the running max (first max wins on ties: strict > below)
+    {  // class 0 initialises the running max.  Update rule = torch.max(dim): first max wins on ties, and a NaN
+       // score wins over every number and is never replaced (the first NaN's index is returned):
+       // !(v <= best) is "v > best or unordered", best == best locks a NaN that is already held
       RowVec<VEC> r;
       r.load(cp);
 #pragma unroll
@@ -91,14 +93,14 @@ decode_filter_kernel(const float *__restrict__ head, int nc, int A, float conf, 
       for (int u = 0; u < DEC_UNROLL; ++u)
 #pragma unroll
         for (int j = 0; j < VEC; ++j)
-          if (r[u].v[j] > best[j]) { best[j] = r[u].v[j]; lab[j] = c + u; }
+          if (!(r[u].v[j] <= best[j]) && best[j] == best[j]) { best[j] = r[u].v[j]; lab[j] = c + u; }
     }
     for (; c < nc; ++c) {
       RowVec<VEC> r;
       r.load(cp + (size_t)c * A);
 #pragma unroll
       for (int j = 0; j < VEC; ++j)
-        if (r.v[j] > best[j]) { best[j] = r.v[j]; lab[j] = c; }
+        if (!(r.v[j] <= best[j]) && best[j] == best[j]) { best[j] = r.v[j]; lab[j] = c; }
     }
     if (!RAW) {
 #pragma unroll
@@ -267,7 +269,7 @@ decode_filter_kernel(const float *__restrict__ head, int nc, int A, float conf, 
     }
   }
   if (tid == 0) {
-    out_count[b] = off;
+    out_count[b] = off < cap ? off : cap;   // what was written: with cap < candidates the list is cut in anchor order
     st.ticket[b] = 0u;   // ready for the next launch on this workspace
   }
 }

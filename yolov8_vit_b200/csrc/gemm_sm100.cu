@@ -9,7 +9,7 @@
 //   * the fp32 accumulator lives in TMEM, double buffered (2 x 256 columns = all 512), so the
 //     epilogue of tile i overlaps the MMAs of tile i+1;
 //   * 8 epilogue warps pull the accumulator back with tcgen05.ld (32 lanes x 16 columns), transpose
-//     it through padded shared memory so that global I/O is row-contiguous, apply bias / erf-GELU /
+//     it through padded shared memory so that global I/O is row-contiguous, apply bias / tanh-form GELU /
 //     residual / position-embedding and store bf16 or fp32;
 //   * persistent: one CTA per SM walks the tile list (n fastest, so the A rows of an m-block
 //     are served from L2 to its n-tiles while the weights stay L2 resident).
@@ -19,6 +19,7 @@
 #include "gemm_sm100.cuh"
 #include "sm100_ptx.cuh"
 
+#include <cuda_fp16.h>
 #include <cstdlib>
 #include <mutex>
 
@@ -31,20 +32,32 @@ constexpr int PM = 2 * BM;             // rows per tile of the CTA pair
 constexpr int BN = 256;
 constexpr int BNH = BN / 2;            // B rows each CTA of the pair stages
 constexpr int BK = 64;                 // 64 bf16 = 128 B = one swizzle atom row
-constexpr int STAGES = 6;
+constexpr int MAX_STAGES = 6;
 constexpr int UMMA_K = 16;
 constexpr int A_BYTES = BM * BK * 2;   // 16 KB
 constexpr int B_BYTES = BNH * BK * 2;  // 16 KB
 constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+// Epilogue forms (template parameter DIRECT):
+//   EPI_LSU   TMEM -> registers -> smem transpose -> LSU stores (fp32 / patch-embed / bf16-residual outputs)
+//   EPI_TMA   TMEM -> registers -> swizzled smem -> TMA store, bf16 output (qkv, fc1)
+//   EPI_TMA_RES  the same with the RESIDUAL ADD fused: the warp's 32 x 64 piece of the fp16 residual stream is
+//             fetched by TMA into the staging block while the tile's MMAs still run, added in place and stored
+//             back by TMA as fp16 (proj, fc2: x += y W^T + b without a single LSU global access)
+constexpr int EPI_LSU = 0, EPI_TMA = 1, EPI_TMA_RES = 2;
+// smem ring depth: the residual form needs 4 KB of staging per epilogue warp (both 32 x 32 boxes of the tile
+// resident at once) instead of 2 KB, paid for with one stage of the ring
+constexpr int gemm_stages(int direct) { return direct == EPI_TMA_RES ? 5 : 6; }
+constexpr int epi_warp_bytes(int direct) { return direct == EPI_TMA_RES ? 4096 : 2048; }
 // Epilogue warps per CTA: 8 (two 128-column groups x 4 TMEM lane quarters) or 16 (four 64-column groups).  16 warps
 // hide the TMEM-load / smem-transpose latency of a heavy epilogue (GELU) better, at 96 registers per thread.
 constexpr int gemm_threads(int new_) { return (4 + new_) * 32; }
 constexpr int TMEM_COLS = 512;         // 2 accumulator stages x BN
-constexpr int BAR_BYTES = 256;          // mbarriers + TMEM slot
-// per epilogue warp: 32 rows x 16 fp32 staging, XOR-swizzled 16-byte segments
-constexpr size_t smem_bytes(int new_) {
-  return (size_t)STAGES * STAGE_BYTES + 1024 /*align slack*/ + BAR_BYTES + (size_t)new_ * 32 * 16 * 4;
+constexpr int BAR_BYTES = 512;         // mbarriers (ring 2 x 6, accumulator 2 x 2, residual 16) + TMEM slot
+constexpr size_t smem_bytes(int new_, int direct) {
+  return (size_t)gemm_stages(direct) * STAGE_BYTES + 1024 /*align slack*/ + BAR_BYTES + (size_t)new_ * epi_warp_bytes(direct);
 }
+// output / residual element types
+constexpr int T_BF16 = 0, T_F32 = 1, T_F16 = 2;
 
 // GELU in the epilogue.  The reference's nn.GELU is the erf form x * Phi(x); the first version evaluated it with
 // a degree-8 minimax polynomial for erf (|error| < 6e-5, ~10 issue slots per element), which cost 45 us of the
@@ -72,23 +85,35 @@ __device__ __forceinline__ void gelu4(float4 &v) {
   gelu2(v.z, v.w);
 }
 
-// GELU / OUT_F32 select the epilogue arithmetic at compile time; MODE 1 compiles in the rarely used
-// position-table (patch embedding) and residual operands, MODE 2 the folded LayerNorm (row statistics +
-// column sums), MODE 3 the fused residual update (fp32 stream read-modify-write + bf16 copy + row statistics).
-constexpr int EPI_PLAIN = 0, EPI_EXTRA = 1, EPI_LNFOLD = 2, EPI_RESID = 3;
-template <bool GELU, bool OUT_F32, int MODE, int NEW, bool DIRECT = false>
+__device__ __forceinline__ uint32_t pack_h2(float a, float b) {          // fp16 pair, saturating (no inf in the stream)
+  const float lim = 65504.f;
+  __half2 h = __floats2half2_rn(fminf(fmaxf(a, -lim), lim), fminf(fmaxf(b, -lim), lim));
+  return *reinterpret_cast<uint32_t *>(&h);
+}
+__device__ __forceinline__ uint32_t pack_b2(float a, float b) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t *>(&h);
+}
+
+// GELU / OUT select the epilogue arithmetic at compile time; MODE 1 compiles in the rarely used position-table
+// (patch embedding) and residual operands of the LSU form.
+constexpr int EPI_PLAIN = 0, EPI_EXTRA = 1;
+template <bool GELU, int OUT, int MODE, int NEW, int DIRECT = EPI_LSU>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(gemm_threads(NEW), 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 const __grid_constant__ CUtensorMap tmD, const GemmEpilogue ep, int M, int N, int K) {
+                 const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmR,
+                 const GemmEpilogue ep, int M, int N, int K) {
   constexpr int EPI_COLS = BN * 4 / NEW;       // columns per epilogue warp
-  static_assert(MODE < EPI_LNFOLD || EPI_COLS == GEMM_STAT_COLS, "row-statistics slot = one epilogue warp's column group");
+  constexpr int STAGES = gemm_stages(DIRECT);
+  static_assert(MODE == EPI_PLAIN || MODE == EPI_EXTRA, "epilogue mode");
   extern __shared__ uint8_t smem_raw[];
   uint8_t *smem = (uint8_t *)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  uint8_t *epi_smem = smem + (size_t)STAGES * STAGE_BYTES;        // 1024-byte aligned (TMA-store swizzle atoms)
-  uint64_t *bars = (uint64_t *)(epi_smem + (size_t)NEW * 32 * 16 * 4);
-  uint64_t *full = bars, *empty = bars + STAGES;
-  uint64_t *tfull = bars + 2 * STAGES, *tempty = bars + 2 * STAGES + 2;
-  uint32_t *tmem_slot = (uint32_t *)(bars + 2 * STAGES + 4);
+  uint8_t *epi_smem = smem + (size_t)STAGES * STAGE_BYTES;        // 1024-byte aligned (TMA swizzle atoms)
+  uint64_t *bars = (uint64_t *)(epi_smem + (size_t)NEW * epi_warp_bytes(DIRECT));
+  uint64_t *full = bars, *empty = bars + MAX_STAGES;
+  uint64_t *tfull = bars + 2 * MAX_STAGES, *tempty = bars + 2 * MAX_STAGES + 2;
+  uint64_t *rbar = bars + 2 * MAX_STAGES + 4;                     // [16] residual boxes have landed (one per epilogue warp)
+  uint32_t *tmem_slot = (uint32_t *)(bars + 2 * MAX_STAGES + 4 + 16);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m_tiles = (M + PM - 1) / PM, n_tiles = (N + BN - 1) / BN;
@@ -99,12 +124,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmB);
+    if (DIRECT != EPI_LSU) prefetch_tmap(&tmD);
+    if (DIRECT == EPI_TMA_RES) prefetch_tmap(&tmR);
   }
   if (warp == 1 && lane == 0) {
     // full: one arrive per producer of the pair (+ the bytes of both); empty / tfull: one multicast
     // tcgen05.commit; tempty (leader's copy is the one waited on): every epilogue warp of both CTAs
     for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 2); mbar_init(&empty[i], 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 2 * NEW); }
+    for (int i = 0; i < 16; ++i) mbar_init(&rbar[i], 1);
     fence_barrier_init();
   }
   if (warp == 2) {
@@ -163,26 +191,42 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         umma_commit_pair(&tfull[as]);              // accumulator complete -> both CTAs' epilogues
       }
     }
-  } else if (warp >= 4 && DIRECT) {
-    // ===================== epilogue, TMA-store form (bf16 output): TMEM -> registers -> smem -> TMA =====================
-    // tcgen05.ld hands every thread one accumulator ROW.  Bias (a broadcast load per chunk), GELU and the bf16
-    // conversion happen on that layout; the thread drops its 32 columns (64 B) into the warp's 2 KB staging
-    // block in the 64-byte-swizzle pattern (conflict-free 16-byte stores) and one lane hands the 32 x 32 block to
-    // the TMA unit (cp.async.bulk.tensor store).  No LSU global stores at all: the staged form spends 8 line
-    // slots per store instruction on 32-byte row pieces, and those stores are what bounds the K = 768 GEMMs
-    // (YV_GEMM_DBG=1).  Rows >= M / columns >= N are clipped by the tensor map.
+  } else if (warp >= 4 && DIRECT != EPI_LSU) {
+    // ===================== epilogue, TMA-store form: TMEM -> registers -> smem -> TMA =====================
+    // tcgen05.ld hands every thread one accumulator ROW.  Bias (a broadcast load per chunk), GELU and the 16-bit
+    // conversion happen on that layout; the thread drops its 32 columns (64 B) into the warp's staging block in
+    // the 64-byte-swizzle pattern (conflict-free 16-byte accesses) and one lane hands the 32 x 32 block to the TMA
+    // unit (cp.async.bulk.tensor store).  No LSU global accesses at all: LSU stores spend 8 line slots per
+    // instruction on 32-byte row pieces, and they are what bounds the K = 768 GEMMs (YV_GEMM_DBG=1).  Rows >= M /
+    // columns >= N are clipped by the tensor map.
+    // EPI_TMA_RES: the residual stream's two 32 x 32 boxes of this warp are requested by TMA (same swizzle, so
+    // every thread finds its own row's 64 B exactly where it will write the sum) right after the previous tile's
+    // stores have read the block, i.e. while the MMAs of THIS tile still run; sum = acc + bias + residual is
+    // written over the residual in shared memory and stored as fp16.  out may alias residual (x += ...): each
+    // box is loaded before it is stored by the same warp and no other warp touches it.
     const int ew = warp - 4;
     const int q = warp & 3;
     const int cg = ew >> 2;
-    static_assert(!DIRECT || EPI_COLS == 64, "TMA-store epilogue: two 32-column halves per warp");
-    uint8_t *stg = epi_smem + ew * 2048;
+    static_assert(DIRECT == EPI_LSU || EPI_COLS == 64, "TMA-store epilogue: two 32-column halves per warp");
+    constexpr bool RES = DIRECT == EPI_TMA_RES;
+    uint8_t *stg = epi_smem + ew * epi_warp_bytes(DIRECT);
     const uint32_t sw = (uint32_t)(lane >> 1) & 3u;
-    uint32_t it = 0;
+    uint32_t it = 0, rit = 0;
     for (int tile = pair; tile < num_tiles; tile += npairs, ++it) {
       const uint32_t as = it & 1u, aph = (it >> 1) & 1u;
       const int m0 = (tile / n_tiles) * PM + (int)rank * BM, n0 = (tile % n_tiles) * BN;
       const int row0 = m0 + q * 32;
       const int col0 = n0 + cg * EPI_COLS;
+      const bool box0 = row0 < M && col0 < N, box1 = row0 < M && col0 + 32 < N;      // warp-uniform
+      if (RES && box0) {
+        if (lane == 0) {
+          bulk_wait_read0();                       // the previous tile's stores have read both staging boxes
+          mbar_arrive_expect_tx(&rbar[ew], box1 ? 4096u : 2048u);
+          tma_load_2d(stg, &tmR, &rbar[ew], col0, row0);
+          if (box1) tma_load_2d(stg + 2048, &tmR, &rbar[ew], col0 + 32, row0);
+        }
+        __syncwarp();
+      }
       mbar_wait(&tfull[as], aph);
       tc_fence_after();
       const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + cg * EPI_COLS;
@@ -216,30 +260,48 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
                              __uint_as_float(rr[2]) + b4[j].z, __uint_as_float(rr[3]) + b4[j].w);
           if (GELU) gelu4(v[j]);
         }
-        if ((ch & 1) == 0) {                       // the previous store of this warp has read the block
+        uint8_t *blk = stg + (RES ? (ch >> 1) * 2048 : 0);
+        if (RES) {
+          if (ch == 0 && box0) mbar_wait(&rbar[ew], rit & 1u);      // residual boxes are in shared memory
+        } else if ((ch & 1) == 0) {                // the previous store of this warp has read the block
           if (lane == 0) bulk_wait_read0();
           __syncwarp();
         }
 #pragma unroll
         for (int j = 0; j < 2; ++j) {
-          __nv_bfloat162 h0 = __floats2bfloat162_rn(v[2 * j].x, v[2 * j].y), h1 = __floats2bfloat162_rn(v[2 * j].z, v[2 * j].w);
-          __nv_bfloat162 h2 = __floats2bfloat162_rn(v[2 * j + 1].x, v[2 * j + 1].y), h3 = __floats2bfloat162_rn(v[2 * j + 1].z, v[2 * j + 1].w);
-          uint4 u;
-          u.x = *reinterpret_cast<unsigned *>(&h0); u.y = *reinterpret_cast<unsigned *>(&h1);
-          u.z = *reinterpret_cast<unsigned *>(&h2); u.w = *reinterpret_cast<unsigned *>(&h3);
           const uint32_t c16 = (uint32_t)((ch & 1) * 2 + j);             // 16-byte piece of the 64-byte row
-          *reinterpret_cast<uint4 *>(stg + lane * 64 + ((c16 ^ sw) << 4)) = u;
+          uint4 *slot = reinterpret_cast<uint4 *>(blk + lane * 64 + ((c16 ^ sw) << 4));
+          uint4 u;
+          if (RES) {
+            const uint4 x = *slot;
+            const float2 x0 = __half22float2(*reinterpret_cast<const __half2 *>(&x.x));
+            const float2 x1 = __half22float2(*reinterpret_cast<const __half2 *>(&x.y));
+            const float2 x2 = __half22float2(*reinterpret_cast<const __half2 *>(&x.z));
+            const float2 x3 = __half22float2(*reinterpret_cast<const __half2 *>(&x.w));
+            u.x = pack_h2(v[2 * j].x + x0.x, v[2 * j].y + x0.y);
+            u.y = pack_h2(v[2 * j].z + x1.x, v[2 * j].w + x1.y);
+            u.z = pack_h2(v[2 * j + 1].x + x2.x, v[2 * j + 1].y + x2.y);
+            u.w = pack_h2(v[2 * j + 1].z + x3.x, v[2 * j + 1].w + x3.y);
+          } else {
+            u.x = pack_b2(v[2 * j].x, v[2 * j].y);
+            u.y = pack_b2(v[2 * j].z, v[2 * j].w);
+            u.z = pack_b2(v[2 * j + 1].x, v[2 * j + 1].y);
+            u.w = pack_b2(v[2 * j + 1].z, v[2 * j + 1].w);
+          }
+          *slot = u;
         }
         if (ch & 1) {
           fence_proxy_async_smem();
           __syncwarp();
-          if (lane == 0 && ep.dbg != 1 && col0 + (ch >> 1) * 32 < N && row0 < M) {
-            tma_store_2d(&tmD, stg, col0 + (ch >> 1) * 32, row0);
+          if (lane == 0 && ep.dbg != 1 && ((ch >> 1) ? box1 : box0)) {
+            tma_store_2d(&tmD, blk, col0 + (ch >> 1) * 32, row0);
             bulk_commit();
           }
         }
       }
+      if (RES && box0) ++rit;
       if (ep.dbg == 2) {                           // (measurement mode: nothing was read)
+        if (RES && box0) mbar_wait(&rbar[ew], (rit - 1) & 1u);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) {
@@ -250,7 +312,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     if (lane == 0) bulk_wait0();
   } else if (warp >= 4) {
-    // ===================== epilogue: TMEM -> registers -> smem transpose -> global =====================
+    // ===================== epilogue, LSU form: TMEM -> registers -> smem transpose -> global =====================
     // tcgen05.ld hands every thread one accumulator ROW (32 lanes x 16 columns per load).  Storing
     // that directly would make each warp instruction touch 32 rows; instead the 32 x 16 fp32 block
     // goes through a per-warp XOR-swizzled smem buffer (conflict-free both ways) and comes back with
@@ -291,50 +353,6 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
         obase[i] = (size_t)drow * N + colw;
       }
-      // folded LayerNorm: per-row (mu, rstd) from the producer's (sum, sum of squares); per-column sums
-      float ln_mu[4], ln_rstd[4];
-      float4 s4[MODE == EPI_LNFOLD ? NCH : 1];
-      if (MODE == EPI_LNFOLD) {
-        const float invd = 1.0f / (float)ep.ln_dim;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int row = m0 + q * 32 + i * 8 + trow;
-          float2 st = make_float2(0.f, 0.f);
-          if (rok[i]) {                            // fixed-order sum of the producer's per-column-block partials
-            const float2 *sp = reinterpret_cast<const float2 *>(ep.row_stats) + (size_t)row * ep.ln_slots;
-            float2 t[16];                          // all loads in flight at once (ln_slots <= 16)
-#pragma unroll
-            for (int j = 0; j < 16; ++j) t[j] = j < ep.ln_slots ? __ldg(sp + j) : make_float2(0.f, 0.f);
-#pragma unroll
-            for (int j = 0; j < 16; ++j) { st.x += t[j].x; st.y += t[j].y; }
-          }
-          ln_mu[i] = st.x * invd;
-          ln_rstd[i] = rsqrtf(fmaxf(st.y * invd - ln_mu[i] * ln_mu[i], 0.f) + ep.ln_eps);
-        }
-#pragma unroll
-        for (int ch = 0; ch < NCH; ++ch) {
-          s4[ch] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (colw + ch * 16 < N) s4[ch] = __ldg(reinterpret_cast<const float4 *>(ep.col_s + colw + ch * 16));
-        }
-      }
-      float rs_sum[4] = {0.f, 0.f, 0.f, 0.f}, rs_sq[4] = {0.f, 0.f, 0.f, 0.f};   // MODE 3 row statistics
-      float4 xres[4];                              // MODE 3: residual-stream values of the current chunk
-      if (MODE == EPI_RESID) {
-        // pull this tile's part of the fp32 residual stream towards L2 while the MMAs of the tile run (one
-        // 128-byte line = 2 chunks of a row; the lane with tseg == 0 speaks for its row group) ...
-        if (tseg == 0) {
-#pragma unroll
-          for (int i = 0; i < 4; ++i)
-            if (rok[i])
-#pragma unroll
-              for (int ch = 0; ch < NCH; ch += 2)
-                if (colw + ch * 16 < N) asm volatile("prefetch.global.L2 [%0];" ::"l"(ep.x32 + obase[i] + ch * 16));
-        }
-        // ... and load chunk 0 before waiting for the accumulator
-#pragma unroll
-        for (int i = 0; i < 4; ++i)
-          xres[i] = (rok[i] && colw < N) ? *reinterpret_cast<const float4 *>(ep.x32 + obase[i]) : make_float4(0.f, 0.f, 0.f, 0.f);
-      }
       mbar_wait(&tfull[as], aph);
       tc_fence_after();
       const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + cg * EPI_COLS;
@@ -354,45 +372,22 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
         if (ch + 1 < NCH) tmem_ld_32x16(tbase + (ch + 1) * 16, r);
         __syncwarp();
-        float4 xnext[4];                           // MODE 3: next chunk's residual values, loaded one chunk ahead
-        if (MODE == EPI_RESID) {
-#pragma unroll
-          for (int i = 0; i < 4; ++i)
-            xnext[i] = (ch + 1 < NCH && rok[i] && colw + (ch + 1) * 16 < N)
-                           ? *reinterpret_cast<const float4 *>(ep.x32 + obase[i] + (ch + 1) * 16)
-                           : make_float4(0.f, 0.f, 0.f, 0.f);
-        }
         if (colw + ch * 16 < N) {
 #pragma unroll
           for (int i = 0; i < 4; ++i) {
             const int rr = i * 8 + trow;
             float4 v = *reinterpret_cast<const float4 *>(stg + rr * 16 + ((tseg ^ ((rr >> 1) & 3)) << 2));
             if (!rok[i]) continue;
-            if (MODE == EPI_LNFOLD) {
-              const float nm = -ln_mu[i], rs = ln_rstd[i];
-              v.x = fmaf(rs, fmaf(nm, s4[ch].x, v.x), bias4[ch].x);
-              v.y = fmaf(rs, fmaf(nm, s4[ch].y, v.y), bias4[ch].y);
-              v.z = fmaf(rs, fmaf(nm, s4[ch].z, v.z), bias4[ch].z);
-              v.w = fmaf(rs, fmaf(nm, s4[ch].w, v.w), bias4[ch].w);
-            } else {
-              v.x += bias4[ch].x; v.y += bias4[ch].y; v.z += bias4[ch].z; v.w += bias4[ch].w;
-            }
+            v.x += bias4[ch].x; v.y += bias4[ch].y; v.z += bias4[ch].z; v.w += bias4[ch].w;
             if (GELU) gelu4(v);
             const size_t o = obase[i] + ch * 16;
-            if (MODE == EPI_RESID) {
-              const float4 x = xres[i];
-              v.x += x.x; v.y += x.y; v.z += x.z; v.w += x.w;
-              *reinterpret_cast<float4 *>(ep.x32 + o) = v;
-              rs_sum[i] += (v.x + v.y) + (v.z + v.w);
-              rs_sq[i] += (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
-            }
             if (MODE == EPI_EXTRA) {
               if (pos_row[i]) {
                 const float4 p = __ldg(reinterpret_cast<const float4 *>(pos_row[i] + colw + ch * 16));
                 v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w;
               }
               if (ep.residual) {
-                if (ep.res_f32) {
+                if (ep.res_type == T_F32) {
                   const float4 f = *reinterpret_cast<const float4 *>((const float *)ep.residual + o);
                   v.x += f.x; v.y += f.y; v.z += f.z; v.w += f.w;
                 } else {
@@ -404,35 +399,16 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
               }
             }
             if (ep.dbg == 1 && v.x != 12345.678f) continue;      // keeps the arithmetic alive, drops the stores
-            if (OUT_F32) {
+            if (OUT == T_F32) {
               *reinterpret_cast<float4 *>((float *)ep.out + o) = v;
+            } else if (OUT == T_F16) {
+              *reinterpret_cast<uint2 *>((__half *)ep.out + o) = make_uint2(pack_h2(v.x, v.y), pack_h2(v.z, v.w));
             } else {
-              __nv_bfloat162 h0 = __floats2bfloat162_rn(v.x, v.y), h1 = __floats2bfloat162_rn(v.z, v.w);
-              uint2 u;
-              u.x = *reinterpret_cast<unsigned *>(&h0);
-              u.y = *reinterpret_cast<unsigned *>(&h1);
-              *reinterpret_cast<uint2 *>((__nv_bfloat16 *)ep.out + o) = u;
+              *reinterpret_cast<uint2 *>((__nv_bfloat16 *)ep.out + o) = make_uint2(pack_b2(v.x, v.y), pack_b2(v.z, v.w));
             }
           }
         }
-        if (MODE == EPI_RESID) {
-#pragma unroll
-          for (int i = 0; i < 4; ++i) xres[i] = xnext[i];
-        }
         __syncwarp();
-      }
-      if (MODE == EPI_RESID) {
-        // the 4 lanes of a row group (tseg) hold partial sums of the same rows: reduce, one atomic per row
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          float a = rs_sum[i], b = rs_sq[i];
-          a += __shfl_xor_sync(0xffffffffu, a, 1); b += __shfl_xor_sync(0xffffffffu, b, 1);
-          a += __shfl_xor_sync(0xffffffffu, a, 2); b += __shfl_xor_sync(0xffffffffu, b, 2);
-          if (tseg == 0 && rok[i]) {               // one slot per EPI_COLS-column block: deterministic, no atomics
-            const int slot = n0 / EPI_COLS + cg;
-            reinterpret_cast<float2 *>(ep.stats_out)[(size_t)(m0 + q * 32 + i * 8 + trow) * (N / EPI_COLS) + slot] = make_float2(a, b);
-          }
-        }
       }
       tc_fence_before();
       __syncwarp();
@@ -458,6 +434,7 @@ PFN_encodeTiled g_encode = nullptr;
 std::once_flag g_once;
 int g_init_status = YV_OK;
 
+// process-wide: the driver entry point of cuTensorMapEncodeTiled
 void init_once() {
   void *fn = nullptr;
   cudaDriverEntryPointQueryResult qres;
@@ -468,38 +445,40 @@ void init_once() {
     return;
   }
   g_encode = (PFN_encodeTiled)fn;
-#define YV_SET(G, F, X, W)                                                                                    \
-  if (e == cudaSuccess)                                                                                     \
-    e = cudaFuncSetAttribute(gemm_bf16_kernel<G, F, X, W>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes(W));
-  e = cudaSuccess;
-  YV_SET(false, false, 0, 8) YV_SET(false, true, 0, 8) YV_SET(true, false, 0, 8) YV_SET(true, true, 0, 8)
-  YV_SET(false, false, 0, 16) YV_SET(false, true, 0, 16) YV_SET(true, false, 0, 16) YV_SET(true, true, 0, 16)
-#define YV_SETD(G, F)                                                                                         \
-  if (e == cudaSuccess)                                                                                     \
-    e = cudaFuncSetAttribute(gemm_bf16_kernel<G, F, 0, 16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes(16));
-  YV_SETD(false, false) YV_SETD(true, false)
-#undef YV_SETD
-  YV_SET(false, false, 1, 8) YV_SET(false, true, 1, 8) YV_SET(true, false, 1, 8) YV_SET(true, true, 1, 8)
-  YV_SET(false, false, 2, 16) YV_SET(true, false, 2, 16) YV_SET(false, false, 3, 16)
-#undef YV_SET
-  if (e != cudaSuccess) {
-    g_init_status = yv_cuda_fail(e, "cudaFuncSetAttribute(gemm smem)", __FILE__, __LINE__);
-  }
 }
 
-// row-major bf16 [rows, cols]; box = box_rows x 64 columns, 128-byte swizzle, zero OOB fill
-// (operands: box_cols = 64, 128-byte swizzle; TMA-store epilogue: 32 x 32 box, 64-byte swizzle)
+// per device (cudaFuncSetAttribute applies to the current device only): dynamic shared memory of every instance
+#define YV_GEMM_INSTANCES(X)                                                                                       \
+  X(false, T_BF16, 0, 8, EPI_LSU) X(false, T_F32, 0, 8, EPI_LSU) X(true, T_BF16, 0, 8, EPI_LSU) X(true, T_F32, 0, 8, EPI_LSU)     \
+  X(false, T_BF16, 0, 16, EPI_LSU) X(false, T_F32, 0, 16, EPI_LSU) X(true, T_BF16, 0, 16, EPI_LSU) X(true, T_F32, 0, 16, EPI_LSU) \
+  X(false, T_F16, 0, 16, EPI_LSU)                                                                                  \
+  X(false, T_BF16, 0, 16, EPI_TMA) X(true, T_BF16, 0, 16, EPI_TMA) X(false, T_F16, 0, 16, EPI_TMA_RES)             \
+  X(false, T_BF16, 1, 8, EPI_LSU) X(false, T_F32, 1, 8, EPI_LSU) X(true, T_BF16, 1, 8, EPI_LSU) X(true, T_F32, 1, 8, EPI_LSU)     \
+  X(false, T_F16, 1, 8, EPI_LSU)
+int init_device() {
+  cudaError_t e = cudaSuccess;
+#define YV_SET(G, O, X, W, D)                                                                                      \
+  if (e == cudaSuccess)                                                                                          \
+    e = cudaFuncSetAttribute(gemm_bf16_kernel<G, O, X, W, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes(W, D));
+  YV_GEMM_INSTANCES(YV_SET)
+#undef YV_SET
+  if (e != cudaSuccess) return yv_cuda_fail(e, "cudaFuncSetAttribute(gemm smem)", __FILE__, __LINE__);
+  return YV_OK;
+}
+
+// row-major 16-bit [rows, cols]; box = box_rows x box_cols, zero OOB fill
+// (operands: 64 columns, 128-byte swizzle; TMA epilogues: 32 x 32 box, 64-byte swizzle)
 int make_tmap(CUtensorMap *m, const void *ptr, uint64_t rows, uint64_t cols, uint32_t box_rows, uint32_t box_cols = BK,
-              CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B) {
+              CUtensorMapSwizzle swz = CU_TENSOR_MAP_SWIZZLE_128B, CUtensorMapDataType dt = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16) {
   cuuint64_t dims[2] = {cols, rows};
   cuuint64_t strides[1] = {cols * 2};
   cuuint32_t box[2] = {box_cols, box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = g_encode(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void *>(ptr), dims, strides, box, estr,
+  CUresult r = g_encode(m, dt, 2, const_cast<void *>(ptr), dims, strides, box, estr,
                         CU_TENSOR_MAP_INTERLEAVE_NONE, swz, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                         CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
-    yv_set_error("cuTensorMapEncodeTiled failed (%d) for [%llu x %llu] bf16 at %p", (int)r, (unsigned long long)rows,
+    yv_set_error("cuTensorMapEncodeTiled failed (%d) for [%llu x %llu] 16-bit at %p", (int)r, (unsigned long long)rows,
                  (unsigned long long)cols, ptr);
     return YV_ECUDA;
   }
@@ -523,10 +502,13 @@ int yv_gemm_launch(const void *A, const void *W, int M, int N, int K, const Gemm
                  ((uintptr_t)ep.residual % 16) == 0,
              "yv_gemm: operands must be 16-byte aligned");
   YV_REQUIRE(ep.group_rows == 0 || ep.pos, "yv_gemm: group_rows needs a position table");
+  YV_REQUIRE(ep.out_type >= T_BF16 && ep.out_type <= T_F16 && ep.res_type >= T_BF16 && ep.res_type <= T_F16, "yv_gemm: bad element type");
   std::call_once(g_once, init_once);
   if (g_init_status != YV_OK) return g_init_status;
+  int rc = yv_device_once(YV_INIT_GEMM, init_device);
+  if (rc) return rc;
   CUtensorMap tmA, tmB;
-  int rc = make_tmap(&tmA, A, (uint64_t)M, (uint64_t)K, BM);
+  rc = make_tmap(&tmA, A, (uint64_t)M, (uint64_t)K, BM);
   if (rc) return rc;
   rc = make_tmap(&tmB, W, (uint64_t)N, (uint64_t)K, BNH);
   if (rc) return rc;
@@ -536,56 +518,55 @@ int yv_gemm_launch(const void *A, const void *W, int M, int N, int K, const Gemm
   YvProf prof(YV_K_GEMM, s, 2.0 * M * (double)N * K);
   static const int dbg = []() { const char *e = getenv("YV_GEMM_DBG"); return e ? atoi(e) : 0; }();
   const_cast<GemmEpilogue &>(ep).dbg = dbg;
-  const bool extra = ep.group_rows > 0 || ep.residual != nullptr;
-  const bool lnfold = ep.row_stats != nullptr, resid = ep.x32 != nullptr;
-  YV_REQUIRE(!(lnfold && (extra || resid || ep.out_f32)) && !(resid && (extra || ep.gelu || ep.out_f32)),
-             "yv_gemm: unsupported epilogue combination");
-  YV_REQUIRE(!lnfold || (ep.col_s && ep.ln_dim > 0), "yv_gemm: folded LayerNorm needs col_s and ln_dim");
-  YV_REQUIRE(!lnfold || (ep.ln_slots >= 1 && ep.ln_slots <= 16), "yv_gemm: folded LayerNorm needs 1 <= ln_slots <= 16");
-  YV_REQUIRE(!resid || (ep.stats_out && N % 128 == 0), "yv_gemm: fused residual needs stats_out and N %% 128 == 0");
+  // Which epilogue: the fused fp16 residual form (x16 = x16 + A W^T + b, TMA in and out), the bf16 TMA-store
+  // form, or the LSU form (fp32 outputs, the patch-embed row map, bf16 / fp32 residuals of the generic C-ABI call).
+  const bool tma_res = ep.residual && ep.res_type == T_F16 && ep.out_type == T_F16 && !ep.gelu && ep.group_rows == 0;
+  const bool extra = !tma_res && (ep.group_rows > 0 || ep.residual != nullptr);
+  YV_REQUIRE(tma_res || !ep.residual || ep.res_type != T_F16, "yv_gemm: an fp16 residual needs an fp16 output and no GELU");
+  YV_REQUIRE(ep.out_type != T_F16 || !ep.gelu, "yv_gemm: fp16 output with GELU is not instantiated");
   // epilogue warps of the plain mode: 16 (measured +1.2 % on the whole step against 8; fc1 179 -> 168 us);
-  // YV_GEMM_EPI_WARPS=8 selects the 8-warp form, YV_GEMM_TMA_STORE=0 turns the TMA-store epilogue of bf16 outputs off (A/B timing).  The patch-embed mode keeps 8 (it spills at 96 registers), the statistics modes need 16.
+  // YV_GEMM_EPI_WARPS=8 selects the 8-warp form, YV_GEMM_TMA_STORE=0 turns the TMA-store epilogue of bf16 outputs off (A/B timing).  The patch-embed mode keeps 8 (it spills at 96 registers).
   static const int force = []() { const char *e = getenv("YV_GEMM_EPI_WARPS"); return e ? atoi(e) : 0; }();
-  const bool w16 = force != 8;
+  const bool w16 = force != 8 || ep.out_type == T_F16;
   static const bool direct = []() { const char *e = getenv("YV_GEMM_TMA_STORE"); return !(e && e[0] == '0'); }();
-  const bool tma_out = direct && !extra && !lnfold && !resid && !ep.out_f32;
-  CUtensorMap tmD = tmA;                       // placeholder unless the TMA-store epilogue runs
+  const bool tma_out = direct && !extra && !tma_res && ep.out_type == T_BF16;
+  CUtensorMap tmD = tmA, tmR = tmA;            // placeholders unless a TMA epilogue runs
   if (tma_out && (rc = make_tmap(&tmD, ep.out, (uint64_t)M, (uint64_t)N, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
-#define YV_GO(G, F, X, W) gemm_bf16_kernel<G, F, X, W><<<grid, gemm_threads(W), smem_bytes(W), s>>>(tmA, tmB, tmD, ep, M, N, K)
-#define YV_GO0(G, F)                                                                                                    \
-  do {                                                                                                                  \
-    if (tma_out) gemm_bf16_kernel<G, false, 0, 16, true><<<grid, gemm_threads(16), smem_bytes(16), s>>>(tmA, tmB, tmD, ep, M, N, K); \
-    else if (w16) YV_GO(G, F, 0, 16);                                                                                   \
-    else YV_GO(G, F, 0, 8);                                                                                             \
-  } while (0)
-  if (lnfold) {
-    if (ep.gelu) YV_GO(true, false, 2, 16); else YV_GO(false, false, 2, 16);
-  } else if (resid) {
-    YV_GO(false, false, 3, 16);
-  } else if (ep.gelu) {
-    if (ep.out_f32) { if (extra) YV_GO(true, true, 1, 8); else YV_GO0(true, true); }
-    else { if (extra) YV_GO(true, false, 1, 8); else YV_GO0(true, false); }
-  } else {
-    if (ep.out_f32) { if (extra) YV_GO(false, true, 1, 8); else YV_GO0(false, true); }
-    else { if (extra) YV_GO(false, false, 1, 8); else YV_GO0(false, false); }
+  if (tma_res) {
+    if ((rc = make_tmap(&tmD, ep.out, (uint64_t)M, (uint64_t)N, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_DATA_TYPE_FLOAT16))) return rc;
+    if ((rc = make_tmap(&tmR, ep.residual, (uint64_t)M, (uint64_t)N, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_DATA_TYPE_FLOAT16))) return rc;
   }
-#undef YV_GO0
+#define YV_GO(G, O, X, W, D) gemm_bf16_kernel<G, O, X, W, D><<<grid, gemm_threads(W), smem_bytes(W, D), s>>>(tmA, tmB, tmD, tmR, ep, M, N, K)
+  if (tma_res) {
+    YV_GO(false, T_F16, 0, 16, EPI_TMA_RES);
+  } else if (tma_out) {
+    if (ep.gelu) YV_GO(true, T_BF16, 0, 16, EPI_TMA); else YV_GO(false, T_BF16, 0, 16, EPI_TMA);
+  } else if (ep.out_type == T_F16) {
+    if (extra) YV_GO(false, T_F16, 1, 8, EPI_LSU); else YV_GO(false, T_F16, 0, 16, EPI_LSU);
+  } else if (ep.gelu) {
+    if (ep.out_type == T_F32) { if (extra) YV_GO(true, T_F32, 1, 8, EPI_LSU); else if (w16) YV_GO(true, T_F32, 0, 16, EPI_LSU); else YV_GO(true, T_F32, 0, 8, EPI_LSU); }
+    else { if (extra) YV_GO(true, T_BF16, 1, 8, EPI_LSU); else if (w16) YV_GO(true, T_BF16, 0, 16, EPI_LSU); else YV_GO(true, T_BF16, 0, 8, EPI_LSU); }
+  } else {
+    if (ep.out_type == T_F32) { if (extra) YV_GO(false, T_F32, 1, 8, EPI_LSU); else if (w16) YV_GO(false, T_F32, 0, 16, EPI_LSU); else YV_GO(false, T_F32, 0, 8, EPI_LSU); }
+    else { if (extra) YV_GO(false, T_BF16, 1, 8, EPI_LSU); else if (w16) YV_GO(false, T_BF16, 0, 16, EPI_LSU); else YV_GO(false, T_BF16, 0, 8, EPI_LSU); }
+  }
 #undef YV_GO
   YV_LAUNCH_CHECK();
   return YV_OK;
 }
 
 YV_EXPORT int yv_gemm_bf16(const void *A, const void *W, const float *bias, const void *residual, void *D, int M,
-                           int N, int K, int epi, int out_f32, yv_stream_t stream) {
+                           int N, int K, int epi, int out_type, yv_stream_t stream) {
   YV_REQUIRE(epi == YV_EPI_NONE || epi == YV_EPI_GELU, "yv_gemm_bf16: unknown epilogue %d", epi);
+  YV_REQUIRE(out_type >= 0 && out_type <= 2, "yv_gemm_bf16: out_type %d (0 bf16, 1 f32, 2 f16)", out_type);
   GemmEpilogue ep;
   ep.out = D;
   ep.bias = bias;
   ep.residual = residual;
-  ep.res_f32 = false;
+  ep.res_type = out_type == T_F16 ? T_F16 : T_BF16;     // an fp16 output takes an fp16 residual (may alias D)
   ep.pos = nullptr;
   ep.group_rows = 0;
   ep.gelu = (epi == YV_EPI_GELU);
-  ep.out_f32 = out_f32 != 0;
+  ep.out_type = out_type;
   return yv_gemm_launch(A, W, M, N, K, ep, (cudaStream_t)stream);
 }

@@ -4,33 +4,16 @@
 #include <cuda_bf16.h>
 #include <cuda.h>
 
-// width of one row-statistics slot of the fused residual / folded LayerNorm modes (= the column group of one
-// epilogue warp)
-constexpr int GEMM_STAT_COLS = 64;
-
 struct GemmEpilogue {
-  void *out;                        // [rows, N] bf16 or f32 (row remapped when group_rows > 0)
+  void *out;                        // [rows, N] bf16 / f32 / f16 (row remapped when group_rows > 0)
   const float *bias;                // [N] or null
-  const void *residual;             // [rows, N] bf16 (or f32 when res_f32) or null; indexed by the OUTPUT
-                                    // row; may alias out (each element is read then written by one thread)
+  const void *residual;             // [rows, N] of res_type or null; indexed by the OUTPUT row; may alias out (each
+                                    // element is read, then written, by one thread / one warp's TMA box)
   const float *pos;                 // patch-embed: [group_rows + 1, N] f32 position table (bias folded in)
   int group_rows;                   // patch-embed: patches per crop (196); 0 = identity row map
   bool gelu;
-  bool out_f32;
-  bool res_f32;
-  // LayerNorm folded into the GEMM (mode 2): A holds the RAW bf16 residual stream x, W = g (.) W_orig,
-  // D = rstd_m * (acc - mu_m * col_s[n]) + bias[n]  with  bias = b . W_orig^T + bias_orig,  col_s[n] = sum_k W[n,k],
-  // (mu_m, rstd_m) from row_stats[m][0..ln_slots) = partial (sum_k x, sum_k x^2) over ln_dim features.
-  const float *row_stats = nullptr;
-  const float *col_s = nullptr;
-  int ln_dim = 0;
-  int ln_slots = 0;
-  float ln_eps = 0.f;
-  // Residual update fused into the producer GEMM (mode 3): x32[m, n] += acc + bias (fp32, in place),
-  // out = bf16(x32) and stats_out[m][n / GEMM_STAT_COLS] = (sum, sum of squares) of the new entries of that column
-  // block (one slot per block: deterministic, nothing to zero).  null = off.
-  float *x32 = nullptr;
-  float *stats_out = nullptr;
+  int out_type;                     // 0 bf16, 1 f32, 2 f16
+  int res_type;                     // 0 bf16, 1 f32 (LSU epilogue), 2 f16 (fused TMA residual: needs out_type 2, no GELU)
   int dbg = 0;                      // measurement only (YV_GEMM_DBG): 1 = no global stores, 2 = no epilogue work
 };
 

@@ -3,15 +3,19 @@
 //
 // Reference: utils/utils.py:59-87 (Network_Wrapper, build_model); the backbone arithmetic is
 // timm's vit_base_patch{16,8}_224 (third-party, unpinned, restated from its published
-// architecture: pre-norm blocks, LayerNorm eps 1e-6, erf-GELU, class token, learned position
+// architecture: pre-norm blocks, LayerNorm eps 1e-6, GELU (evaluated in its tanh form, see gemm_sm100.cu), class token, learned position
 // embedding, final norm, class-token pooling, linear head).
 //
-// Data layout in HBM (per chunk of Cc crops, M = Cc * T token rows):
-//   x32  [M, dim]   f32   residual stream (kept fp32 so 24 residual adds do not accumulate bf16 rounding)
+// Data layout in HBM (per pass of Cc crops, M = Cc * T token rows):
+//   x    [M, dim]   f16   residual stream.  fp16, not bf16: 11 significant bits, so the 24 residual adds of the
+//                         stack stay below the bf16 rounding of the GEMM operands (saturating conversion, no inf);
+//                         proj / fc2 update it IN PLACE in their epilogue (x += y W^T + b, TMA in and out)
 //   y    [M, dim]   bf16  LayerNorm output / attention output (GEMM A operands)
-//   d    [M, dim]   bf16  proj / fc2 output (+bias): the residual delta the next LayerNorm adds to x32
 //   qkv  [M, 3 dim] bf16  timm packing (q | k | v, head-major)
 //   h    [M, mlp]   bf16  GELU(fc1)
+// = 18 B per stream element per pass (2.8 KB... per token: 13.8 KB), LayerNorm moves 4 B per element.
+// YV_VIT_STREAM=f32 selects the round-1 layout instead (A/B and high-precision mode): x32 [M, dim] f32 stream,
+// proj / fc2 write bf16 deltas d / d2 which the NEXT LayerNorm folds into x32 (22 B per element per block).
 // Weights are packed once to bf16 [out, in] (K-major = the UMMA B operand as stored by torch).
 #include "common.cuh"
 
@@ -86,35 +90,43 @@ void add_param(yv_vit *m, const std::string &name, size_t numel, bool bf16, bool
 }
 
 struct VitWs {
-  float *x32;
-  __nv_bfloat16 *y, *d, *d2, *qkv, *h, *cls_ln;
+  void *x;                      // residual stream: f16 [M, dim] (default) or f32
+  __nv_bfloat16 *y, *d, *d2, *qkv, *h, *cls_ln;      // d / d2: fp32-stream mode only
   float *hidden;
-  float *stats[2];      // folded-LayerNorm pipeline: per-row partial (sum, sum of squares), dim / GEMM_STAT_COLS slots
   size_t total;
 };
+
+// residual stream precision (read once per process)
+bool vit_stream_f32() {
+  static const bool f32 = []() { const char *e = getenv("YV_VIT_STREAM"); return e && (e[0] == 'f' || e[0] == 'F') && e[1] == '3'; }();
+  return f32;
+}
 
 VitWs vit_ws(const yv_vit *m, void *base, int chunk) {
   const yv_vit_config &c = m->cfg;
   const size_t M = (size_t)chunk * m->T;
+  const bool f32 = vit_stream_f32();
   size_t o = 0;
   char *b = (char *)base;
   VitWs w;
-  w.x32 = (float *)(b + o);            o = yv_align_up(o + M * c.dim * 4, 1024);
+  w.x = (void *)(b + o);               o = yv_align_up(o + M * c.dim * (f32 ? 4 : 2), 1024);
   w.y = (__nv_bfloat16 *)(b + o);      o = yv_align_up(o + M * c.dim * 2, 1024);
-  w.d = (__nv_bfloat16 *)(b + o);      o = yv_align_up(o + M * c.dim * 2, 1024);
-  w.d2 = (__nv_bfloat16 *)(b + o);     o = yv_align_up(o + M * c.dim * 2, 1024);
+  w.d = w.d2 = nullptr;
+  if (f32) {
+    w.d = (__nv_bfloat16 *)(b + o);    o = yv_align_up(o + M * c.dim * 2, 1024);
+    w.d2 = (__nv_bfloat16 *)(b + o);   o = yv_align_up(o + M * c.dim * 2, 1024);
+  }
   w.qkv = (__nv_bfloat16 *)(b + o);    o = yv_align_up(o + M * 3 * c.dim * 2, 1024);
   w.h = (__nv_bfloat16 *)(b + o);      o = yv_align_up(o + M * c.mlp * 2, 1024);
   w.cls_ln = (__nv_bfloat16 *)(b + o); o = yv_align_up(o + (size_t)chunk * c.dim * 2, 1024);
   w.hidden = (float *)(b + o);         o = yv_align_up(o + (size_t)chunk * c.head_out * 4, 1024);
-  for (int i = 0; i < 2; ++i) { w.stats[i] = (float *)(b + o); o = yv_align_up(o + M * (c.dim / GEMM_STAT_COLS) * 8, 1024); }
   w.total = o;
   return w;
 }
 
-// Largest number of crops per pass of the block stack (3.03 MB of workspace per crop for ViT-B/16: 6.2 GB at
-// 2048).  One pass over 1072 crops instead of 4 x 256 + 48 measured +1.5 % on the whole step (450 -> 90 launches,
-// no 48-crop remainder pass); passes are balanced when n exceeds the limit.  YV_VIT_CHUNK overrides (timing).
+// Largest number of crops per pass of the block stack (2.7 MB of workspace per crop for ViT-B/16).  One pass over
+// 1072 crops instead of 4 x 256 + 48 measured +1.5 % on the whole step (450 -> 90 launches, no 48-crop remainder
+// pass); passes are balanced when n exceeds the limit.  YV_VIT_CHUNK overrides (timing).
 int vit_default_chunk() {
   static const int c = []() { const char *e = getenv("YV_VIT_CHUNK"); int v = e ? atoi(e) : 0; return v > 0 ? v : 2048; }();
   return c;
@@ -134,21 +146,6 @@ int finalize(yv_vit *m, cudaStream_t s) {
                                                    m->F("model.patch_embed.proj.bias"), m->wf + m->pos_table_off,
                                                    m->T, m->cfg.dim);
   YV_LAUNCH_CHECK();
-  // LayerNorm folded into the following Linear (qkv after norm1, fc1 after norm2): g (.) W, column sums, bias
-  for (int i = 0; i < m->cfg.depth; ++i) {
-    const std::string p = "model.blocks." + std::to_string(i) + ".";
-    const int D = m->cfg.dim;
-    int rc = yv_fold_ln_launch(m->B(p + "attn.qkv.weight"), m->F(p + "attn.qkv.bias"), m->F(p + "norm1.weight"),
-                               m->F(p + "norm1.bias"), 3 * D, D, m->wb + m->params.at(p + "attn.qkv.wfold").off,
-                               m->wf + m->params.at(p + "attn.qkv.colsum").off,
-                               m->wf + m->params.at(p + "attn.qkv.cfold").off, s);
-    if (rc) return rc;
-    rc = yv_fold_ln_launch(m->B(p + "mlp.fc1.weight"), m->F(p + "mlp.fc1.bias"), m->F(p + "norm2.weight"),
-                           m->F(p + "norm2.bias"), m->cfg.mlp, D, m->wb + m->params.at(p + "mlp.fc1.wfold").off,
-                           m->wf + m->params.at(p + "mlp.fc1.colsum").off,
-                           m->wf + m->params.at(p + "mlp.fc1.cfold").off, s);
-    if (rc) return rc;
-  }
   m->finalized = true;
   return YV_OK;
 }
@@ -186,12 +183,6 @@ YV_EXPORT int yv_vit_create(const yv_vit_config *cfg, yv_vit_t **out) {
     add_param(m, p + "mlp.fc1.bias", c.mlp, false);
     add_param(m, p + "mlp.fc2.weight", D * c.mlp, true);
     add_param(m, p + "mlp.fc2.bias", D, false);
-    add_param(m, p + "attn.qkv.wfold", 3 * D * D, true, true);
-    add_param(m, p + "attn.qkv.colsum", 3 * D, false, true);
-    add_param(m, p + "attn.qkv.cfold", 3 * D, false, true);
-    add_param(m, p + "mlp.fc1.wfold", (size_t)c.mlp * D, true, true);
-    add_param(m, p + "mlp.fc1.colsum", c.mlp, false, true);
-    add_param(m, p + "mlp.fc1.cfold", c.mlp, false, true);
   }
   add_param(m, "model.norm.weight", D, false);
   add_param(m, "model.norm.bias", D, false);
@@ -277,73 +268,61 @@ YV_EXPORT int yv_vit_forward(yv_vit_t *m, const void *patches_bf16, int n, float
   const int T = m->T, D = c.dim, NP = T - 1;
   const float *pos_table = m->wf + m->pos_table_off;
 
-  // YV_VIT_FUSED_LN=1 selects the EXPERIMENTAL folded-LayerNorm pipeline (no LayerNorm kernels inside the
-  // blocks).  Measured perf-neutral on B200 so far (48.7 ms/step both ways on the same box: the 8.8 ms of
-  // LayerNorm kernels reappear as slower K = 768 GEMM epilogues) and about 2x the logit error of the default
-  // (the tensor cores see the raw bf16 residual stream), so the stand-alone kernels stay the default.
-  static const bool fused_ln = []() { const char *e = getenv("YV_VIT_FUSED_LN"); return e && e[0] == '1'; }();
+  const bool f32 = vit_stream_f32();
+  const int XT = f32 ? 1 : 2;                            // yv_ln_launch element type of the stream
   for (int c0 = 0; c0 < n; c0 += chunk) {
     const int cc = (n - c0) < chunk ? (n - c0) : chunk;
     const int M = cc * T;
     const __nv_bfloat16 *patches = (const __nv_bfloat16 *)patches_bf16 + (size_t)c0 * NP * m->pdim;
     GemmEpilogue ep;
-    // patch embedding: [cc*NP, pdim] x [D, pdim]^T -> token rows (+ position, + bias), f32 residual stream
-    ep = GemmEpilogue{w.x32, nullptr, nullptr, pos_table, NP, false, true, false};
+    // patch embedding: [cc*NP, pdim] x [D, pdim]^T -> token rows (+ position, + bias) of the residual stream
+    ep = GemmEpilogue{w.x, nullptr, nullptr, pos_table, NP, false, f32 ? 1 : 2, 0};
     if ((rc = yv_gemm_launch(patches, m->B("model.patch_embed.proj.weight"), cc * NP, D, m->pdim, ep, s))) return rc;
-    if ((rc = yv_cls_rows_launch(w.x32, pos_table, cc, T, D, s))) return rc;
-    if (fused_ln) {
-      // Folded-LayerNorm pipeline: no LayerNorm kernels inside the blocks.
-      //   qkv / fc1 read the RAW bf16 residual stream xb and apply LayerNorm in their epilogue
-      //     (rstd * (acc - mu * colsum) + cfold, weights pre-multiplied by gamma);
-      //   proj / fc2 add their output to the fp32 residual stream in their epilogue, store the bf16 copy xb
-      //     and the per-row partial (sum, sum of squares) the next folded LayerNorm needs.
-      // HBM traffic per token per block drops from 49 KB to 43 KB and 24 kernel launches disappear.
-      __nv_bfloat16 *xb = w.d;
-      const int slots = D / GEMM_STAT_COLS;
-      if ((rc = yv_row_stats_launch(w.x32, xb, w.stats[0], slots, M, D, s))) return rc;
+    if ((rc = yv_cls_rows_launch(w.x, !f32, pos_table, cc, T, D, s))) return rc;
+    if (!f32) {
+      // fp16 residual stream, updated in place by the proj / fc2 epilogues (residual boxes in and sums out by TMA):
+      // per block and stream element LayerNorm moves 2 x (2 B in + 2 B out) and the two updates 2 x (2 + 2) B.
       for (int i = 0; i < c.depth; ++i) {
         const std::string p = "model.blocks." + std::to_string(i) + ".";
-        ep = GemmEpilogue{w.qkv, m->F(p + "attn.qkv.cfold"), nullptr, nullptr, 0, false, false, false};
-        ep.row_stats = w.stats[0]; ep.col_s = m->F(p + "attn.qkv.colsum"); ep.ln_dim = D; ep.ln_slots = slots; ep.ln_eps = c.eps;
-        if ((rc = yv_gemm_launch(xb, m->B(p + "attn.qkv.wfold"), M, 3 * D, D, ep, s))) return rc;
+        if ((rc = yv_ln_launch(w.x, XT, D, nullptr, 0, false, m->F(p + "norm1.weight"), m->F(p + "norm1.bias"), w.y, M, D, c.eps, s))) return rc;
+        ep = GemmEpilogue{w.qkv, m->F(p + "attn.qkv.bias"), nullptr, nullptr, 0, false, 0, 0};
+        if ((rc = yv_gemm_launch(w.y, m->B(p + "attn.qkv.weight"), M, 3 * D, D, ep, s))) return rc;
         if ((rc = yv_attention_launch(w.qkv, w.y, cc, T, c.heads, D / c.heads, s))) return rc;
-        ep = GemmEpilogue{xb, m->F(p + "attn.proj.bias"), nullptr, nullptr, 0, false, false, false};
-        ep.x32 = w.x32; ep.stats_out = w.stats[1];
+        ep = GemmEpilogue{w.x, m->F(p + "attn.proj.bias"), w.x, nullptr, 0, false, 2, 2};
         if ((rc = yv_gemm_launch(w.y, m->B(p + "attn.proj.weight"), M, D, D, ep, s))) return rc;
-        ep = GemmEpilogue{w.h, m->F(p + "mlp.fc1.cfold"), nullptr, nullptr, 0, true, false, false};
-        ep.row_stats = w.stats[1]; ep.col_s = m->F(p + "mlp.fc1.colsum"); ep.ln_dim = D; ep.ln_slots = slots; ep.ln_eps = c.eps;
-        if ((rc = yv_gemm_launch(xb, m->B(p + "mlp.fc1.wfold"), M, c.mlp, D, ep, s))) return rc;
-        ep = GemmEpilogue{xb, m->F(p + "mlp.fc2.bias"), nullptr, nullptr, 0, false, false, false};
-        ep.x32 = w.x32; ep.stats_out = w.stats[0];
+        if ((rc = yv_ln_launch(w.x, XT, D, nullptr, 0, false, m->F(p + "norm2.weight"), m->F(p + "norm2.bias"), w.y, M, D, c.eps, s))) return rc;
+        ep = GemmEpilogue{w.h, m->F(p + "mlp.fc1.bias"), nullptr, nullptr, 0, true, 0, 0};
+        if ((rc = yv_gemm_launch(w.y, m->B(p + "mlp.fc1.weight"), M, c.mlp, D, ep, s))) return rc;
+        ep = GemmEpilogue{w.x, m->F(p + "mlp.fc2.bias"), w.x, nullptr, 0, false, 2, 2};
         if ((rc = yv_gemm_launch(w.h, m->B(p + "mlp.fc2.weight"), M, D, c.mlp, ep, s))) return rc;
       }
-      // final norm on the class-token rows only (x32 is up to date), then the heads
-      if ((rc = yv_ln_launch(w.x32, true, (size_t)T * D, nullptr, 0, false, m->F("model.norm.weight"), m->F("model.norm.bias"), w.cls_ln, cc, D, c.eps, s))) return rc;
+      // final norm on the class-token rows only, then the heads
+      if ((rc = yv_ln_launch(w.x, XT, (size_t)T * D, nullptr, 0, false, m->F("model.norm.weight"), m->F("model.norm.bias"), w.cls_ln, cc, D, c.eps, s))) return rc;
     } else {
-      // Residual adds are fused into the LayerNorms, so proj / fc2 store plain bf16 deltas (no global loads on
-      // the GEMM epilogue's critical path).  The fp32 stream is rewritten ONCE per block: norm2 normalises
-      // x32 + d_attn on the fly without writing it back, and the next norm1 folds (x32 + d_attn) + d_mlp in and
-      // writes x32 -- the same fp32 sums in the same order as two separate updates, 1.5 KB less traffic per token.
+      // fp32 residual stream (round-1 layout): the residual adds are fused into the LayerNorms, so proj / fc2 store
+      // plain bf16 deltas.  The fp32 stream is rewritten ONCE per block: norm2 normalises x32 + d_attn on the fly
+      // without writing it back, and the next norm1 folds (x32 + d_attn) + d_mlp in and writes x32 -- the same fp32
+      // sums in the same order as two separate updates.
       bool have = false;                                 // deltas of the previous block pending?
       for (int i = 0; i < c.depth; ++i) {
         const std::string p = "model.blocks." + std::to_string(i) + ".";
-        if ((rc = yv_ln2_launch(w.x32, true, D, have ? w.d : nullptr, have ? w.d2 : nullptr, D, true, m->F(p + "norm1.weight"), m->F(p + "norm1.bias"), w.y, M, D, c.eps, s))) return rc;
-        ep = GemmEpilogue{w.qkv, m->F(p + "attn.qkv.bias"), nullptr, nullptr, 0, false, false, false};
+        if ((rc = yv_ln2_launch(w.x, XT, D, have ? w.d : nullptr, have ? w.d2 : nullptr, D, true, m->F(p + "norm1.weight"), m->F(p + "norm1.bias"), w.y, M, D, c.eps, s))) return rc;
+        ep = GemmEpilogue{w.qkv, m->F(p + "attn.qkv.bias"), nullptr, nullptr, 0, false, 0, 0};
         if ((rc = yv_gemm_launch(w.y, m->B(p + "attn.qkv.weight"), M, 3 * D, D, ep, s))) return rc;
         if ((rc = yv_attention_launch(w.qkv, w.y, cc, T, c.heads, D / c.heads, s))) return rc;
-        ep = GemmEpilogue{w.d, m->F(p + "attn.proj.bias"), nullptr, nullptr, 0, false, false, false};
+        ep = GemmEpilogue{w.d, m->F(p + "attn.proj.bias"), nullptr, nullptr, 0, false, 0, 0};
         if ((rc = yv_gemm_launch(w.y, m->B(p + "attn.proj.weight"), M, D, D, ep, s))) return rc;
-        if ((rc = yv_ln_launch(w.x32, true, D, w.d, D, false, m->F(p + "norm2.weight"), m->F(p + "norm2.bias"), w.y, M, D, c.eps, s))) return rc;
-        ep = GemmEpilogue{w.h, m->F(p + "mlp.fc1.bias"), nullptr, nullptr, 0, true, false, false};
+        if ((rc = yv_ln_launch(w.x, XT, D, w.d, D, false, m->F(p + "norm2.weight"), m->F(p + "norm2.bias"), w.y, M, D, c.eps, s))) return rc;
+        ep = GemmEpilogue{w.h, m->F(p + "mlp.fc1.bias"), nullptr, nullptr, 0, true, 0, 0};
         if ((rc = yv_gemm_launch(w.y, m->B(p + "mlp.fc1.weight"), M, c.mlp, D, ep, s))) return rc;
-        ep = GemmEpilogue{w.d2, m->F(p + "mlp.fc2.bias"), nullptr, nullptr, 0, false, false, false};
+        ep = GemmEpilogue{w.d2, m->F(p + "mlp.fc2.bias"), nullptr, nullptr, 0, false, 0, 0};
         if ((rc = yv_gemm_launch(w.h, m->B(p + "mlp.fc2.weight"), M, D, c.mlp, ep, s))) return rc;
         have = true;
       }
       // final norm on the class-token rows only (+ both deltas of the last block), 1000-way head, wrapper MLP + argmax
-      if ((rc = yv_ln2_launch(w.x32, true, (size_t)T * D, w.d, w.d2, (size_t)T * D, false, m->F("model.norm.weight"), m->F("model.norm.bias"), w.cls_ln, cc, D, c.eps, s))) return rc;
+      if ((rc = yv_ln2_launch(w.x, XT, (size_t)T * D, w.d, w.d2, (size_t)T * D, false, m->F("model.norm.weight"), m->F("model.norm.bias"), w.cls_ln, cc, D, c.eps, s))) return rc;
     }
-    ep = GemmEpilogue{w.hidden, m->F("model.head.bias"), nullptr, nullptr, 0, false, true, false};
+    ep = GemmEpilogue{w.hidden, m->F("model.head.bias"), nullptr, nullptr, 0, false, 1, 0};
     if ((rc = yv_gemm_launch(w.cls_ln, m->B("model.head.weight"), cc, c.head_out, D, ep, s))) return rc;
     if ((rc = yv_wrapper_head_launch(w.hidden, c.head_out, m->F("fc.1.weight"), m->F("fc.1.bias"), m->F("fc.3.weight"),
                                      m->F("fc.3.bias"), cc, c.head_out, c.hidden, c.num_classes,

@@ -5,6 +5,7 @@
 //       ldmatrix-fed, online softmax in registers)
 //   K8  class-token rows, and the Network_Wrapper head (ReLU -> 1000x128 -> ReLU -> 128x5) + argmax
 #include <cstdlib>
+#include <cuda_fp16.h>
 #include "common.cuh"
 #include "vit_ops.cuh"
 
@@ -17,7 +18,9 @@ constexpr int LN_MAXCH = 4;    // dim <= 1024 (chunks of 256 = 32 lanes x 8 elem
 // CS: streaming cache operators on the operands nobody re-reads soon (the fp32 stream and the consumed deltas:
 // ld.global.cs / st.global.cs = evict-first), so that y -- the A operand of the GEMM launched next -- is what
 // stays in the 126 MB L2.
-template <bool XF32, bool CS = false>
+// XT: element type of x -- 0 bf16, 1 f32 (the fp32 residual stream, with the pending deltas), 2 f16 (the fp16
+// residual stream: 2 B in + 2 B out per element, nothing else)
+template <int XT, bool CS = false>
 __global__ void __launch_bounds__(LN_WARPS * 32)
 layernorm_kernel(const void *xv, size_t in_stride, const __nv_bfloat16 *__restrict__ delta,
                  const __nv_bfloat16 *__restrict__ delta2, size_t delta_stride, int writeback, const float *__restrict__ gamma, const float *__restrict__ beta,
@@ -37,11 +40,20 @@ layernorm_kernel(const void *xv, size_t in_stride, const __nv_bfloat16 *__restri
   for (int c = 0; c < LN_MAXCH; ++c) {
     if (c < nch) {
       const int e = c * 256 + lane * 8;
-      if (XF32) {
+      if (XT == 1) {
         const float4 *p = reinterpret_cast<const float4 *>((const float *)xv + (size_t)row * in_stride + e);
         const float4 a = CS ? __ldcs(p) : p[0], b = CS ? __ldcs(p + 1) : p[1];
         v[c][0] = a.x; v[c][1] = a.y; v[c][2] = a.z; v[c][3] = a.w;
         v[c][4] = b.x; v[c][5] = b.y; v[c][6] = b.z; v[c][7] = b.w;
+      } else if (XT == 2) {
+        const uint4 u = *reinterpret_cast<const uint4 *>((const __half *)xv + (size_t)row * in_stride + e);
+        const __half2 *h = reinterpret_cast<const __half2 *>(&u);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const float2 f = __half22float2(h[k]);
+          v[c][2 * k] = f.x;
+          v[c][2 * k + 1] = f.y;
+        }
       } else {
         const uint4 u = *reinterpret_cast<const uint4 *>((const __nv_bfloat16 *)xv + (size_t)row * in_stride + e);
         const __nv_bfloat162 *h = reinterpret_cast<const __nv_bfloat162 *>(&u);
@@ -73,7 +85,7 @@ layernorm_kernel(const void *xv, size_t in_stride, const __nv_bfloat16 *__restri
             v[c][2 * k + 1] += f.y;
           }
         }
-        if (XF32 && writeback) {
+        if (XT == 1 && writeback) {
           float4 *p = reinterpret_cast<float4 *>((float *)const_cast<void *>(xv) + (size_t)row * in_stride + e);
           if (CS) {
             __stcs(p, make_float4(v[c][0], v[c][1], v[c][2], v[c][3]));
@@ -129,11 +141,12 @@ layernorm_kernel(const void *xv, size_t in_stride, const __nv_bfloat16 *__restri
 }
 
 // ------------------------------------------------------------------------------------ cls rows
-__global__ void cls_rows_kernel(float *__restrict__ x32, const float *__restrict__ cls_pos0, int n, int T, int dim) {
+template <typename XT>
+__global__ void cls_rows_kernel(XT *__restrict__ x, const float *__restrict__ cls_pos0, int n, int T, int dim) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= n * dim) return;
   const int c = i / dim, e = i % dim;
-  x32[(size_t)c * T * dim + e] = cls_pos0[e];
+  x[(size_t)c * T * dim + e] = (XT)cls_pos0[e];
 }
 
 // ------------------------------------------------------------------------------------ wrapper head
@@ -226,20 +239,23 @@ wrapper_head_kernel(const float *__restrict__ hidden, int ld, const float *__res
 
 }  // namespace
 
-int yv_ln_launch(const void *x, bool x_f32, size_t in_stride, const __nv_bfloat16 *delta, size_t delta_stride,
+int yv_ln_launch(const void *x, int x_type, size_t in_stride, const __nv_bfloat16 *delta, size_t delta_stride,
                  bool writeback, const float *gamma, const float *beta, __nv_bfloat16 *y, int rows, int dim, float eps,
                  cudaStream_t s) {
-  return yv_ln2_launch(x, x_f32, in_stride, delta, nullptr, delta_stride, writeback, gamma, beta, y, rows, dim, eps, s);
+  return yv_ln2_launch(x, x_type, in_stride, delta, nullptr, delta_stride, writeback, gamma, beta, y, rows, dim, eps, s);
 }
 
-int yv_ln2_launch(const void *x, bool x_f32, size_t in_stride, const __nv_bfloat16 *delta, const __nv_bfloat16 *delta2,
+int yv_ln2_launch(const void *x, int x_type, size_t in_stride, const __nv_bfloat16 *delta, const __nv_bfloat16 *delta2,
                   size_t delta_stride,
                  bool writeback, const float *gamma, const float *beta, __nv_bfloat16 *y, int rows, int dim, float eps,
                  cudaStream_t s) {
   YV_REQUIRE(rows >= 1 && dim >= 256 && dim % 256 == 0 && dim <= 256 * LN_MAXCH, "layernorm: dim=%d must be a multiple of 256, <= %d", dim, 256 * LN_MAXCH);
   YV_REQUIRE(x && gamma && beta && y, "layernorm: null pointer");
+  YV_REQUIRE(x_type >= 0 && x_type <= 2, "layernorm: x_type %d (0 bf16, 1 f32, 2 f16)", x_type);
   YV_REQUIRE(in_stride % 8 == 0, "layernorm: row stride must be a multiple of 8 elements");
   YV_REQUIRE(!delta2 || delta, "layernorm: delta2 needs delta");
+  YV_REQUIRE(!delta || x_type == 1, "layernorm: deltas belong to the fp32 residual stream");
+  const bool x_f32 = x_type == 1;
   YvProf prof(YV_K_LN, s, (double)rows * dim * ((x_f32 ? 6.0 : 4.0) + (delta ? 2.0 : 0.0) + (delta2 ? 2.0 : 0.0) + (delta && writeback ? 4.0 : 0.0)));
   static const bool cs = [] { const char *e = getenv("YV_LN_STREAM"); return e && e[0] == '1'; }();   // A/B switches
   static const int rev = [] { const char *e = getenv("YV_LN_REVERSE"); return (e && e[0] == '1') ? 1 : 0; }();
@@ -248,96 +264,19 @@ int yv_ln2_launch(const void *x, bool x_f32, size_t in_stride, const __nv_bfloat
   static const int persist = [] { const char *e = getenv("YV_LN_PERSIST"); return e ? atoi(e) : 4; }();   // CTAs per SM
   int grid = (rows + LN_WARPS - 1) / LN_WARPS;
   if (persist > 0 && grid > yv_num_sms() * persist) grid = yv_num_sms() * persist;
-  if (x_f32 && cs) layernorm_kernel<true, true><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, delta, delta2, delta_stride, writeback ? 1 : 0, gamma, beta, y, rows, dim, eps, rev);
-  else if (x_f32) layernorm_kernel<true><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, delta, delta2, delta_stride, writeback ? 1 : 0, gamma, beta, y, rows, dim, eps, rev);
-  else layernorm_kernel<false><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, delta, delta2, delta_stride, 0, gamma, beta, y, rows, dim, eps, rev);
+  if (x_f32 && cs) layernorm_kernel<1, true><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, delta, delta2, delta_stride, writeback ? 1 : 0, gamma, beta, y, rows, dim, eps, rev);
+  else if (x_f32) layernorm_kernel<1><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, delta, delta2, delta_stride, writeback ? 1 : 0, gamma, beta, y, rows, dim, eps, rev);
+  else if (x_type == 2) layernorm_kernel<2><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, nullptr, nullptr, 0, 0, gamma, beta, y, rows, dim, eps, rev);
+  else layernorm_kernel<0><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, nullptr, nullptr, 0, 0, gamma, beta, y, rows, dim, eps, rev);
   YV_LAUNCH_CHECK();
   return YV_OK;
 }
 
-namespace {
-
-// xb = bf16(x32) and the one-pass row statistics (sum, sum of squares) in slot 0 of stats[row][slots]
-// (the other slots are zeroed): the first LayerNorm of a chunk in the folded-LayerNorm pipeline.
-__global__ void __launch_bounds__(LN_WARPS * 32)
-row_stats_kernel(const float *__restrict__ x32, __nv_bfloat16 *__restrict__ xb, float2 *__restrict__ stats, int slots,
-                 int rows, int dim) {
-  const int lane = threadIdx.x & 31;
-  const int row = blockIdx.x * LN_WARPS + (threadIdx.x >> 5);
-  if (row >= rows) return;
-  float sum = 0.f, sq = 0.f;
-  for (int e = lane * 8; e < dim; e += 256) {
-    const float4 *p = reinterpret_cast<const float4 *>(x32 + (size_t)row * dim + e);
-    const float4 a = p[0], b = p[1];
-    sum += ((a.x + a.y) + (a.z + a.w)) + ((b.x + b.y) + (b.z + b.w));
-    sq += ((a.x * a.x + a.y * a.y) + (a.z * a.z + a.w * a.w)) + ((b.x * b.x + b.y * b.y) + (b.z * b.z + b.w * b.w));
-    __nv_bfloat162 h[4] = {__floats2bfloat162_rn(a.x, a.y), __floats2bfloat162_rn(a.z, a.w),
-                           __floats2bfloat162_rn(b.x, b.y), __floats2bfloat162_rn(b.z, b.w)};
-    *reinterpret_cast<uint4 *>(xb + (size_t)row * dim + e) = *reinterpret_cast<const uint4 *>(h);
-  }
-#pragma unroll
-  for (int d = 16; d > 0; d >>= 1) {
-    sum += __shfl_xor_sync(0xffffffffu, sum, d);
-    sq += __shfl_xor_sync(0xffffffffu, sq, d);
-  }
-  if (lane < slots) stats[(size_t)row * slots + lane] = lane == 0 ? make_float2(sum, sq) : make_float2(0.f, 0.f);
-}
-
-// Folds a LayerNorm's affine part into the following Linear (one block per output feature n):
-//   wf[n, k] = bf16(g[k] * w[n, k]),  colsum[n] = sum_k wf[n, k],  cf[n] = bias[n] + sum_k beta[k] * w[n, k]
-// so that Linear(LN(x)) = rstd * (x . wf^T - mu * colsum) + cf.
-__global__ void __launch_bounds__(256)
-fold_ln_kernel(const __nv_bfloat16 *__restrict__ w, const float *__restrict__ bias, const float *__restrict__ g,
-               const float *__restrict__ beta, int K, __nv_bfloat16 *__restrict__ wf, float *__restrict__ colsum,
-               float *__restrict__ cf) {
-  const int n = blockIdx.x;
-  float s = 0.f, c = 0.f;
-  for (int k = threadIdx.x; k < K; k += 256) {
-    const float wv = __bfloat162float(w[(size_t)n * K + k]);
-    const __nv_bfloat16 f = __float2bfloat16_rn(g[k] * wv);
-    wf[(size_t)n * K + k] = f;
-    s += __bfloat162float(f);
-    c += beta[k] * wv;
-  }
-  __shared__ float sh[2][8];
-#pragma unroll
-  for (int d = 16; d > 0; d >>= 1) {
-    s += __shfl_xor_sync(0xffffffffu, s, d);
-    c += __shfl_xor_sync(0xffffffffu, c, d);
-  }
-  if ((threadIdx.x & 31) == 0) { sh[0][threadIdx.x >> 5] = s; sh[1][threadIdx.x >> 5] = c; }
-  __syncthreads();
-  if (threadIdx.x == 0) {
-    float ts = 0.f, tc = 0.f;
-    for (int i = 0; i < 8; ++i) { ts += sh[0][i]; tc += sh[1][i]; }
-    colsum[n] = ts;
-    cf[n] = bias[n] + tc;
-  }
-}
-
-}  // namespace
-
-int yv_row_stats_launch(const float *x32, __nv_bfloat16 *xb, float *stats, int slots, int rows, int dim, cudaStream_t s) {
-  YV_REQUIRE(dim % 8 == 0 && slots >= 1 && slots <= 32, "row_stats: dim=%d slots=%d unsupported", dim, slots);
-  const int grid = (rows + LN_WARPS - 1) / LN_WARPS;
-  YvProf prof(YV_K_LN, s, (double)rows * dim * 6.0);
-  row_stats_kernel<<<grid, LN_WARPS * 32, 0, s>>>(x32, xb, reinterpret_cast<float2 *>(stats), slots, rows, dim);
-  YV_LAUNCH_CHECK();
-  return YV_OK;
-}
-
-int yv_fold_ln_launch(const __nv_bfloat16 *w, const float *bias, const float *g, const float *beta, int N, int K,
-                      __nv_bfloat16 *wf, float *colsum, float *cf, cudaStream_t s) {
-  YvProf prof(YV_K_MISC, s, 0.0);
-  fold_ln_kernel<<<N, 256, 0, s>>>(w, bias, g, beta, K, wf, colsum, cf);
-  YV_LAUNCH_CHECK();
-  return YV_OK;
-}
-
-int yv_cls_rows_launch(float *x32, const float *cls_pos0, int n, int T, int dim, cudaStream_t s) {
+int yv_cls_rows_launch(void *x, bool x_f16, const float *cls_pos0, int n, int T, int dim, cudaStream_t s) {
   const int total = n * dim;
   YvProf prof(YV_K_MISC, s, 0.0);
-  cls_rows_kernel<<<(total + 255) / 256, 256, 0, s>>>(x32, cls_pos0, n, T, dim);
+  if (x_f16) cls_rows_kernel<__half><<<(total + 255) / 256, 256, 0, s>>>((__half *)x, cls_pos0, n, T, dim);
+  else cls_rows_kernel<float><<<(total + 255) / 256, 256, 0, s>>>((float *)x, cls_pos0, n, T, dim);
   YV_LAUNCH_CHECK();
   return YV_OK;
 }
@@ -359,5 +298,5 @@ int yv_wrapper_head_launch(const float *hidden, int ld_hidden, const float *w1, 
 
 YV_EXPORT int yv_layernorm_bf16(const void *x, const float *gamma, const float *beta, void *y, int rows, int dim,
                                 float eps, yv_stream_t stream) {
-  return yv_ln_launch(x, false, (size_t)dim, nullptr, 0, false, gamma, beta, (__nv_bfloat16 *)y, rows, dim, eps, (cudaStream_t)stream);
+  return yv_ln_launch(x, 0, (size_t)dim, nullptr, 0, false, gamma, beta, (__nv_bfloat16 *)y, rows, dim, eps, (cudaStream_t)stream);
 }

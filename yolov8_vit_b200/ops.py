@@ -215,16 +215,26 @@ def crop_resize(images: torch.Tensor, crop_box: torch.Tensor, crop_img: torch.Te
 
 
 # ------------------------------------------------------------------------- a5 building blocks
-def gemm_bf16(a: torch.Tensor, w: torch.Tensor, bias=None, residual=None, gelu: bool = False, out_f32: bool = False):
-    """a [M,K] bf16, w [N,K] bf16 -> a @ w.T (+bias) (GELU) (+residual bf16)."""
+def gemm_bf16(a: torch.Tensor, w: torch.Tensor, bias=None, residual=None, gelu: bool = False, out_f32: bool = False,
+              out: torch.Tensor | None = None):
+    """a [M,K] bf16, w [N,K] bf16 -> a @ w.T (+bias) (GELU) (+residual).  Output bf16, or f32 (``out_f32``), or --
+    when ``out`` is an f16 tensor -- f16 with an f16 ``residual`` that may be ``out`` itself (the ViT's in-place
+    residual-stream update, TMA in both directions)."""
     require_device(a)
     assert a.dtype == torch.bfloat16 and w.dtype == torch.bfloat16
     a, w = a.contiguous(), w.contiguous()
     M, K = a.shape
     N = w.shape[0]
-    d = torch.empty(M, N, dtype=torch.float32 if out_f32 else torch.bfloat16, device=a.device)
+    if out is not None:
+        assert out.dtype == torch.float16 and out.is_contiguous() and out.shape == (M, N)
+        assert residual is None or (residual.dtype == torch.float16 and residual.is_contiguous())
+        d, out_type = out, 2
+    else:
+        assert residual is None or residual.dtype == torch.bfloat16
+        d = torch.empty(M, N, dtype=torch.float32 if out_f32 else torch.bfloat16, device=a.device)
+        out_type = 1 if out_f32 else 0
     check(load().yv_gemm_bf16(ptr(a), ptr(w), ptr(bias), ptr(residual), ptr(d), M, N, K, 1 if gelu else 0,
-                              1 if out_f32 else 0, stream_ptr(a.device)), "yv_gemm_bf16")
+                              out_type, stream_ptr(a.device)), "yv_gemm_bf16")
     return d
 
 

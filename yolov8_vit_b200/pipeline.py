@@ -10,6 +10,9 @@ app.py:61), batched over images.  Every stage is a C-ABI call into libyv8vit.so.
 """
 from __future__ import annotations
 
+import dataclasses
+import threading
+from contextlib import contextmanager
 from dataclasses import dataclass, field
 
 import torch
@@ -48,23 +51,39 @@ class HotPathResult:
     cand: tuple | None = None
 
 
+@contextmanager
+def _nvtx(name: str):
+    """NVTX range per stage (visible in nsys / ncu --nvtx; a no-op otherwise)."""
+    torch.cuda.nvtx.range_push(name)
+    try:
+        yield
+    finally:
+        torch.cuda.nvtx.range_pop()
+
+
 class HotPath:
-    """Stateless apart from the (optional) classifier; safe to call from several threads as long
-    as each uses its own CUDA stream (the reference shares module-global models across Flask
-    request threads, app.py:24-37)."""
+    """Stateless apart from the (optional) classifier.  The resident entry points (``__call__``, ``detect``,
+    ``classify``, ``from_candidates``) may be called from several threads that share one instance and one
+    model, as the reference's Flask request threads share ``model_list`` (app.py:24-37), PROVIDED each thread
+    works on its own CUDA stream: the 4-byte pinned read-back buffer is per thread and the ViT activation
+    workspace is per stream (``ViTModel._workspace``); two threads on the SAME stream are ordered by the
+    stream.  The host-buffer entry points (``submit_host`` / ``run_host``) own staging slots and are not
+    re-entrant: one HotPath per serving thread."""
 
     def __init__(self, model: ViTModel | None = None, cfg: HotPathConfig = HotPathConfig()):
         self.model = model
         self.cfg = cfg
         self.extra_models = ()         # further classifiers of the reference's model_list (logits are summed)
-        self._pin = None
+        self._tls = threading.local()  # per-thread pinned crop-count buffer
 
     def detect(self, head: torch.Tensor):
         """K1..K3: candidates and keep lists (device tensors, no sync)."""
         c = self.cfg
-        cand = ops.decode_filter(head, c.conf, c.ratio, c.dwdh, cap=c.cand_cap)
+        with _nvtx("yv8vit.decode_filter"):
+            cand = ops.decode_filter(head, c.conf, c.ratio, c.dwdh, cap=c.cand_cap)
         boxes, scores, labels, anchors, counts = cand
-        keep, keep_counts = ops.nms_batched(boxes, scores, counts, c.iou, max_keep=c.max_det)
+        with _nvtx("yv8vit.custom_nms"):
+            keep, keep_counts = ops.nms_batched(boxes, scores, counts, c.iou, max_keep=c.max_det)
         return cand, keep, keep_counts
 
     def __call__(self, head: torch.Tensor, images: torch.Tensor, keep_intermediates: bool = False,
@@ -95,20 +114,25 @@ class HotPath:
         c = self.cfg
         B, H, W, _ = images.shape
         boxes, scores, labels, anchors, _ = cand
-        cl = ops.build_crops(boxes, scores, labels, anchors, keep, keep_counts, c.max_det, W, H, c.alpha,
-                             c.dilate_mode)
+        with _nvtx("yv8vit.build_crops"):
+            cl = ops.build_crops(boxes, scores, labels, anchors, keep, keep_counts, c.max_det, W, H, c.alpha,
+                                 c.dilate_mode)
         logits = top1 = None
         n = 0
         if self.model is not None:
-            # The crop count sizes the ViT launch: one 4-byte read-back (the only host sync of the path).
-            if self._pin is None:
-                self._pin = torch.empty(1, dtype=torch.int32).pin_memory()
-            self._pin.copy_(cl.n_crops, non_blocking=True)
+            # The crop count sizes the ViT launches (GEMM grids, TMA maps): one 4-byte read-back, the only host
+            # sync of the path (~20 us of a 40 ms step; the GPU has the whole ViT queued again right after it).
+            pin = getattr(self._tls, "pin", None)
+            if pin is None:
+                pin = self._tls.pin = torch.empty(1, dtype=torch.int32).pin_memory()
+            pin.copy_(cl.n_crops, non_blocking=True)
             torch.cuda.current_stream(images.device).synchronize()
-            n = min(int(self._pin.item()), cl.crop_box.shape[0])
-            patches = ops.crop_resize(images, cl.crop_box, cl.crop_img, n, c.interp, c.out_size,
-                                      self.model.cfg.patch, "patch")
-            logits, top1 = self.model.forward_patches(patches, n)
+            n = min(int(pin.item()), cl.crop_box.shape[0])
+            with _nvtx("yv8vit.crop_resize"):
+                patches = ops.crop_resize(images, cl.crop_box, cl.crop_img, n, c.interp, c.out_size,
+                                          self.model.cfg.patch, "patch")
+            with _nvtx("yv8vit.vit_forward"):
+                logits, top1 = self.model.forward_patches(patches, n)
             for m in getattr(self, "extra_models", ()):
                 logits = logits + m.forward_patches(patches, n)[0]
             if getattr(self, "extra_models", ()) and n:
@@ -282,14 +306,20 @@ class PendingHost:
         self._res = HotPathResult(records=rec, det_count=torch.cat([cl.det_count for cl in cls]), n_crops=total,
                                   logits=st["logits"][:total].clone() if total else None,
                                   top1=st["top1"][:total].clone() if total else None)
+        # The crop lists were allocated on the FRONT stream and are read here on the caller's stream (crop_resize,
+        # and pack_results after the whole ViT): tell the caching allocator, or their blocks would go back to the
+        # front-stream pool as soon as the last reference drops and the next submit_host -- which only waits for
+        # the OTHER slot's `free` event -- would overwrite them while this batch's pack_results is still queued.
+        for cl in cls:
+            for f in dataclasses.fields(cl):
+                getattr(cl, f.name).record_stream(main)
         if st["free"] is None:
             st["free"] = torch.cuda.Event()
         st["free"].record(main)                # the slot's staging buffers may be overwritten after this point
         self._done = torch.cuda.Event()
         self._done.record(main)
         hp._last_done = self._done
-        self.cls = None
-        self._launched = True
+        self._launched = True                  # (self.cls stays referenced until result() has seen the batch finish)
         return self
 
     def result(self) -> HotPathResult:
@@ -298,6 +328,7 @@ class PendingHost:
         if self._done is not None:
             self._done.synchronize()
             self._done = None
+            self.cls = None
         return self._res
 
 

@@ -97,3 +97,54 @@ def make_raw_head(B: int, nc: int = 80, levels=LEVELS_640, n_obj: int = 8, seed:
         val = (torch.randperm(n_obj, generator=g).to(torch.float32) + 0.5) * (4.0 / n_obj)
         raw[b, 64 + cls, idx] = val
     return raw
+
+
+def make_vit_weights(cfg=None, seed: int = 20240410, fc_gain: float = 8.0):
+    """Seeded synthetic ``Network_Wrapper.state_dict()`` (keys ``model.*`` in
+    timm naming + ``fc.1.*``/``fc.3.*``, utils/utils.py:59-69).  trunc-normal
+    0.02 like timm's init; ``fc`` scaled by ``fc_gain`` so top-1 margins are
+    well above bf16 noise (no trained weights exist in the tree).  Values are
+    rounded to bf16-representable fp32 so oracle and GPU see identical weights."""
+    if cfg is None:
+        from .vit import ViTConfig
+        cfg = ViTConfig()
+    g = torch.Generator().manual_seed(seed)
+    D, P = cfg.dim, cfg.patch
+
+    def tn(*shape, std=0.02):
+        t = torch.empty(*shape)
+        torch.nn.init.trunc_normal_(t, std=std, a=-2 * std, b=2 * std, generator=g)
+        return t.to(torch.bfloat16).to(torch.float32)
+
+    def small(*shape, std=0.02):
+        return (torch.randn(*shape, generator=g) * std).to(torch.bfloat16).to(torch.float32)
+
+    sd = {
+        "model.cls_token": tn(1, 1, D),
+        "model.pos_embed": tn(1, cfg.tokens, D),
+        "model.patch_embed.proj.weight": tn(D, 3, P, P),
+        "model.patch_embed.proj.bias": small(D),
+    }
+    for i in range(cfg.depth):
+        p = f"model.blocks.{i}."
+        sd[p + "norm1.weight"] = (1.0 + small(D, std=0.1)).to(torch.bfloat16).to(torch.float32)
+        sd[p + "norm1.bias"] = small(D)
+        sd[p + "attn.qkv.weight"] = tn(3 * D, D, std=0.04)
+        sd[p + "attn.qkv.bias"] = small(3 * D)
+        sd[p + "attn.proj.weight"] = tn(D, D)
+        sd[p + "attn.proj.bias"] = small(D)
+        sd[p + "norm2.weight"] = (1.0 + small(D, std=0.1)).to(torch.bfloat16).to(torch.float32)
+        sd[p + "norm2.bias"] = small(D)
+        sd[p + "mlp.fc1.weight"] = tn(cfg.mlp, D)
+        sd[p + "mlp.fc1.bias"] = small(cfg.mlp)
+        sd[p + "mlp.fc2.weight"] = tn(D, cfg.mlp)
+        sd[p + "mlp.fc2.bias"] = small(D)
+    sd["model.norm.weight"] = (1.0 + small(D, std=0.1)).to(torch.bfloat16).to(torch.float32)
+    sd["model.norm.bias"] = small(D)
+    sd["model.head.weight"] = tn(cfg.head_out, D, std=0.04)
+    sd["model.head.bias"] = small(cfg.head_out, std=0.2)
+    sd["fc.1.weight"] = tn(cfg.hidden, cfg.head_out, std=0.02 * fc_gain)
+    sd["fc.1.bias"] = small(cfg.hidden, std=0.1)
+    sd["fc.3.weight"] = tn(cfg.num_classes, cfg.hidden, std=0.02 * fc_gain)
+    sd["fc.3.bias"] = small(cfg.num_classes, std=0.1)
+    return sd

@@ -57,7 +57,7 @@ class ViTModel:
         with torch.cuda.device(self.device):
             check(load().yv_vit_create(ctypes.byref(c), ctypes.byref(h)), "yv_vit_create")
         self._h = h
-        self._ws = None
+        self._ws = {}           # activation workspace per CUDA stream (threads on different streams never share one)
 
     def __del__(self):
         h = getattr(self, "_h", None)
@@ -86,10 +86,15 @@ class ViTModel:
         return self
 
     def _workspace(self, n: int) -> torch.Tensor:
+        """Workspace of the CURRENT stream: forwards on different streams (one per serving thread) run
+        concurrently on separate buffers; on one stream they are ordered.  A buffer that is outgrown is
+        released to the allocator of the stream it was allocated (and only ever used) on."""
         nb = load().yv_vit_workspace_bytes(self._h, n)          # sized for min(n, the library's chunk)
-        if self._ws is None or self._ws.numel() < nb:
-            self._ws = torch.empty(nb, dtype=torch.uint8, device=self.device)
-        return self._ws
+        key = torch.cuda.current_stream(self.device).cuda_stream
+        ws = self._ws.get(key)
+        if ws is None or ws.numel() < nb:
+            ws = self._ws[key] = torch.empty(nb, dtype=torch.uint8, device=self.device)
+        return ws
 
     def forward_patches(self, patches: torch.Tensor, n: int, return_hidden: bool = False,
                         out_logits: torch.Tensor | None = None, out_top1: torch.Tensor | None = None):
