@@ -209,19 +209,35 @@ def verify(oracle_results, r):
     keep, kc = r.keep.cpu(), r.keep_counts.cpu()
     det_count, rec = r.crops.det_count.cpu(), r.records.cpu()
     det_box, det_cb = r.crops.det_box.cpu().numpy(), r.crops.det_crop_box.cpu().numpy()
-    n_img = n_crop = 0
+    det_crop, logits = r.crops.det_crop.cpu(), r.logits.cpu().numpy()
+    n_img = n_crop = n_tie = 0
+    worst = 0.0
+    scale = max(float(np.abs(ref["logits"]).max()) for ref in oracle_results if "logits" in ref)
     for b, ref in enumerate(oracle_results):
         n = int(det_count[b])
         if keep[b, :int(kc[b])].tolist()[:n] != ref["keep"].tolist():
             return {"ok": False, "why": f"keep list of image {b} differs"}
         if not (np.array_equal(det_box[b, :n], ref["box"]) and np.array_equal(det_cb[b, :n], ref["crop_box"])):
             return {"ok": False, "why": f"boxes of image {b} differ"}
-        if "cls" in ref and rec[b, :n, 4].int().tolist() != ref["cls"].tolist():
-            return {"ok": False, "why": f"top-1 of image {b} differs"}
+        if "cls" in ref:
+            # logits within 1e-2 of the oracle's largest logit; top-1 identical unless the oracle's own two largest
+            # logits are closer than twice that tolerance (a near-tie may flip inside the tolerance: counted, not failed)
+            ok = ref["valid"]                            # detections whose dilated crop is non-empty (all, in this workload)
+            got = logits[det_crop[b, :n].numpy()[ok]]
+            worst = max(worst, float(np.abs(got - ref["logits"]).max()) / scale)
+            if worst > 1e-2:
+                return {"ok": False, "why": f"logits of image {b} off by {worst:.3g} of max|ref|"}
+            top2 = np.sort(ref["logits"], axis=1)[:, -2:]
+            clear = (top2[:, 1] - top2[:, 0]) > 2e-2 * scale
+            cls = rec[b, :n, 4].int().numpy()[ok]
+            if (cls[clear] != ref["cls"][clear]).any():
+                return {"ok": False, "why": f"top-1 of image {b} differs"}
+            n_tie += int((~clear).sum())
         n_img += 1
         n_crop += n
-    return {"ok": True, "images": n_img, "crops": n_crop,
-            "what": "keep lists + rounded / dilated boxes bit-exact and ViT top-1 identical vs the CPU oracle"}
+    return {"ok": True, "images": n_img, "crops": n_crop, "logit_err_rel_max": worst, "near_tie_crops_excluded_from_top1": n_tie,
+            "what": "keep lists + rounded / dilated boxes bit-exact, ViT logits within 1e-2 of max|ref| and top-1 "
+                    "identical (where the oracle's top-2 margin exceeds 2e-2 of max|ref|) vs the CPU oracle"}
 
 
 def run_reference(args):

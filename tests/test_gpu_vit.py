@@ -27,14 +27,56 @@ def test_layernorm():
     assert float((got - ref).abs().max()) <= 2 ** -7 * float(ref.abs().max())
 
 
-@pytest.mark.parametrize("n,T", [(3, 197), (2, 64), (2, 5), (1, 256), (2, 785), (1, 300)])
+def _attention_ref(qkv, heads, dh):
+    n, T, _ = qkv.shape
+    q, k, v = qkv.float().reshape(n, T, 3, heads, dh).permute(2, 0, 3, 1, 4)
+    return (torch.softmax(q @ k.transpose(-1, -2) * dh ** -0.5, -1) @ v).transpose(1, 2).reshape(n, T, heads * dh)
+
+
+# T covers every shape of the key-block / query-tile decomposition: one block (<= 128 keys), two blocks (197 = 112 +
+# 96, 256 = 128 + 128, 129 = 80 + 64), many blocks with a short last one (785 = 6 x 128 + 32, 300, 400), one / two /
+# seven query tiles, an odd tile count (the second slot of the last pair does not exist), T = 1
+@pytest.mark.parametrize("n,T", [(3, 197), (2, 64), (2, 5), (1, 256), (2, 785), (1, 300), (2, 1), (3, 16), (2, 17),
+                                 (2, 128), (2, 129), (1, 400), (13, 197)])
 def test_attention(n, T):
     heads, dh = 12, 64
-    qkv = (torch.randn(n, T, 3 * heads * dh) * 0.7).to(torch.bfloat16)
-    q, k, v = qkv.float().reshape(n, T, 3, heads, dh).permute(2, 0, 3, 1, 4)
-    ref = (torch.softmax(q @ k.transpose(-1, -2) * dh ** -0.5, -1) @ v).transpose(1, 2).reshape(n, T, heads * dh)
+    qkv = (torch.randn(n, T, 3 * heads * dh, generator=torch.Generator().manual_seed(T)) * 0.7).to(torch.bfloat16)
+    ref = _attention_ref(qkv, heads, dh)
     got = ops.attention_bf16(qkv.to(DEV), heads).cpu().float()
+    assert bool(torch.isfinite(got).all())
     assert float((got - ref).abs().max()) <= 2e-2 * float(ref.abs().max())
+
+
+@pytest.mark.parametrize("T", [197, 785])
+def test_attention_online_softmax_rescale(T):
+    """Scores whose running maximum jumps by far more than the 2^8 rescale threshold from one key block to the next
+    (a few keys with a 30x larger norm placed in LATER blocks), peaked rows, and large-magnitude logits: the O
+    accumulator in tensor memory is rescaled in place and the result still matches the fp32 softmax."""
+    heads, dh = 12, 64
+    g = torch.Generator().manual_seed(7 + T)
+    qkv = (torch.randn(2, T, 3 * heads * dh, generator=g) * 0.5)
+    D = heads * dh
+    hot = [T - 1, T - 40, 130] if T < 300 else [T - 1, 300, 520, 700, 130]
+    for t in hot:
+        qkv[:, t, D:2 * D] *= 30.0                  # keys with a huge norm: the block they sit in raises the row maximum
+    qkv[1, :, :D] *= 6.0                            # large logits on every row of the second sample
+    qkv = qkv.to(torch.bfloat16)
+    ref = _attention_ref(qkv, heads, dh)
+    got = ops.attention_bf16(qkv.to(DEV), heads).cpu().float()
+    assert bool(torch.isfinite(got).all())
+    assert float((got - ref).abs().max()) <= 2e-2 * float(ref.abs().max())
+
+
+def test_attention_many_items_persistent_phases():
+    """More work items than SMs x 4, so every CTA wraps its Q / K-V rings, the three rotating score buffers and
+    both O accumulators several times; deterministic across launches."""
+    heads, dh, n, T = 12, 64, 60, 197
+    qkv = (torch.randn(n, T, 3 * heads * dh, generator=torch.Generator().manual_seed(3)) * 0.7).to(torch.bfloat16)
+    ref = _attention_ref(qkv, heads, dh)
+    a = ops.attention_bf16(qkv.to(DEV), heads)
+    b = ops.attention_bf16(qkv.to(DEV), heads)
+    assert torch.equal(a, b)
+    assert float((a.cpu().float() - ref).abs().max()) <= 2e-2 * float(ref.abs().max())
 
 
 def test_vit_tiny_golden(golden):
@@ -154,12 +196,13 @@ def test_run_host_no_detections(full_model):
     assert r.n_crops == 0 and float(r.records[..., 7].sum()) == 0.0
 
 
-def test_vit_b8_reference_literal_model():
+@pytest.mark.parametrize("depth", [2, 12])
+def test_vit_b8_reference_literal_model(depth):
     """Row f4: the reference-literal vit_base_patch8_224 shape (785 tokens, utils/class_config.py:21) runs end to
-    end (patch-8 crop layout, K = 192 patch-embed GEMM, long-sequence attention); 2 blocks vs the oracle."""
-    cfg = O.ViTConfig(patch=8, depth=2)
+    end (patch-8 crop layout, K = 192 patch-embed GEMM, 7-key-block flash attention) at its full depth of 12."""
+    cfg = O.ViTConfig(patch=8, depth=depth)
     sd = O.make_vit_weights(cfg, seed=9)
-    m = ViTModel(ViTConfig(patch=8, depth=2), DEV).load_state_dict(sd)
+    m = ViTModel(ViTConfig(patch=8, depth=depth), DEV).load_state_dict(sd)
     x = torch.randn(3, 3, 224, 224, generator=torch.Generator().manual_seed(3)).clamp_(-1, 1)
     ref = O.vit_forward(sd, x, cfg)
     got = m(x.to(DEV)).cpu()

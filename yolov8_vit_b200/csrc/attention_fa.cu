@@ -1,0 +1,431 @@
+// attention_fa.cu -- K7: softmax(Q K^T / sqrt(dh)) V for ANY sequence length on tcgen05 / TMEM, fed by TMA.
+//
+// timm Attention.forward (vit_base_patch{16,8}_224; reached by the reference through utils/utils.py:71-72):
+// qkv [n, T, 3, heads, 64] -> per head softmax(q k^T * 64^-0.5) v.  One kernel serves ViT-B/16 (T = 197: two key
+// blocks of 112 + 96) and the reference-literal ViT-B/8 (T = 785: six key blocks of 128 + one of 32).
+//
+// Flash-style, single read of the scores.  What bounds a softmax on this machine is the MUFU pipe: 16 ex2 per clock
+// per SM (measured, tools/ubench_tmem.cu), i.e. 1664 clocks for the 26 624 exponentials of a 128 x 208 tile, against
+// ~530 clocks to read its fp32 scores twice from tensor memory (tcgen05.ld.32x32b.x16: 400 B/clock/SM with 16
+// warps, 210 with 4; the .x32 shape only reaches 115) and ~830 clocks of tensor pipe.  The round-1 kernel ran at
+// 3.7 k clocks per tile because all 16 softmax warps worked on ONE tile in lock step (max pass, barrier, exp
+// pass: the MUFU pipe idles during the first half and nothing hides the dependent chain).  Here TWO query tiles are
+// in flight per SM, each owned by its own group of 8 warps, so one tile's MUFU-bound exp pass overlaps the other's
+// load / max / exchange / store; every score is read from tensor memory once and held in registers between the
+// max and the exp (<= 64 per thread: the keys are cut into blocks of <= 128 and two threads share a row), with an
+// online softmax across the blocks -- which is also what makes the kernel independent of the sequence length.
+//
+// One persistent CTA per SM, 20 warps.  A work item is a (crop, head, PAIR of 128-row query tiles): the pair shares
+// every K / V block (loaded once).  Slot s in {0, 1} = query tile 2 pair + s, owned by softmax group s.
+//   warp 0      TMA producer: Q tiles (2-stage ring over items), K / V blocks (4-stage ring)
+//   warp 1      MMA issuer.  Score MMAs run up to THREE block-entries ahead of the softmax: tensor memory holds
+//               three 128-column score buffers that rotate over the entries (item, block, slot) in issue order,
+//               plus one 64-column O accumulator per slot = 512 columns.  S(e + 3) is issued right after P V(e).
+//   warps 4-11  softmax group 0, warps 12-19 group 1: 4 TMEM lane quarters x 2 key halves.  Per block a thread
+//               loads its <= 64 scores (tcgen05.ld x16), takes the maximum (FMNMX3), exchanges it with the thread
+//               that holds the other half of the row (shared memory + a 64-thread named barrier), exponentiates
+//               (FFMA2 + MUFU.EX2), accumulates the row sum and writes P as packed bf16 back INTO the score buffer
+//               (the A operand of the P V MMA comes from tensor memory; P never touches shared memory).
+//               Online softmax: the running maximum is only raised when a block exceeds it by more than 2^8
+//               (P then stays <= 256, exact in bf16 / fp32); raising it rescales O in tensor memory
+//               (tcgen05.ld / st, decided per warp, rare after the first block).  After the last block the group
+//               drains O, scales by 1 / sum and stores bf16.
+// Warps whose 32 query rows are all past T (the tail tile) only pass the barriers on.
+#include "common.cuh"
+#include "gemm_sm100.cuh"
+#include "sm100_ptx.cuh"
+#include "vit_ops.cuh"
+
+using namespace sm100;
+
+namespace {
+
+constexpr int FA_DH = 64;
+constexpr int FA_THREADS = 20 * 32;
+constexpr int FA_TILE_BYTES = 128 * FA_DH * 2;      // one 128-row operand tile: 16 KB
+constexpr int FA_Q_STAGES = 2;
+constexpr int FA_KV_STAGES = 4;
+constexpr int FA_SBUF = 3;                          // rotating score buffers
+constexpr int FA_SCOLS = 128;                       // TMEM columns per score buffer
+constexpr int FA_OCOL = FA_SBUF * FA_SCOLS;         // O accumulators: [384, 448) and [448, 512)
+constexpr float FA_RESCALE_THR = 8.0f;              // log2 units
+
+struct FaShared {
+  uint64_t q_full[FA_Q_STAGES], q_empty[FA_Q_STAGES];
+  uint64_t kv_full[FA_KV_STAGES], kv_empty[FA_KV_STAGES];
+  uint64_t s_full[FA_SBUF], p_full[FA_SBUF];
+  uint64_t o_done[2], o_free[2];
+  uint32_t tmem_slot, pad;
+  float xmax[2][2][2][128];          // [group][block parity][key half][row]
+  float xsum[2][2][128];             // [group][key half][row]
+};
+constexpr int FA_SMEM = (FA_Q_STAGES * 2 + FA_KV_STAGES * 2) * FA_TILE_BYTES + (int)sizeof(FaShared) + 1024;
+
+// MN-major B operand (V: keys x 64, 128-byte swizzled rows of dh): 8-key groups are 1024 B apart
+__device__ __forceinline__ uint64_t fa_desc_mn_sw128(uint32_t smem_addr) {
+  const uint32_t lo = ((smem_addr >> 4) & 0x3FFFu) | ((1024u >> 4) << 16);
+  const uint32_t hi = (1024u >> 4) | (1u << 14) | (2u << 29);
+  return ((uint64_t)hi << 32) | lo;
+}
+// kind::f16, D=f32, A=bf16 K-major (or from TMEM), B=bf16 MN-major
+__host__ __device__ constexpr uint32_t fa_idesc_bmn(int M, int N) { return umma_idesc_bf16(M, N) | (1u << 16); }
+
+__device__ __forceinline__ float fa_ex2(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float fa_max3(float a, float b, float c) {
+  float y;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(y) : "f"(a), "f"(b), "f"(c));
+  return y;
+}
+__device__ __forceinline__ uint32_t fa_pack_bf16x2(float lo, float hi) {
+  __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t *>(&h);
+}
+__device__ __forceinline__ void fa_tmem_ld_32x8(uint32_t taddr, uint32_t (&r)[8]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
+               : "r"(taddr)
+               : "memory");
+}
+
+struct FaShape {
+  int T, heads;
+  int nkb;            // key blocks
+  int blk0, blk_last; // keys of the first nkb - 1 blocks / of the last block (multiples of 16, <= 128)
+  int nq, npair;      // 128-row query tiles per (crop, head); pairs of them
+};
+
+__global__ void __launch_bounds__(FA_THREADS, 1)
+attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV0,
+                    const __grid_constant__ CUtensorMap tmKV1, __nv_bfloat16 *__restrict__ out, int n_items,
+                    const FaShape sh, float scale_log2e) {
+  extern __shared__ __align__(1024) uint8_t fa_raw[];
+  uint8_t *smem = fa_raw;
+  if ((smem_u32(smem) & 1023u) != 0u) __trap();                  // 128B-swizzled tiles need 1024-byte alignment
+  uint8_t *sQ = smem;                                            // [stage][slot] 16 KB
+  uint8_t *sKV = smem + FA_Q_STAGES * 2 * FA_TILE_BYTES;         // [stage] K 16 KB | V 16 KB
+  FaShared *bar = reinterpret_cast<FaShared *>(sKV + FA_KV_STAGES * 2 * FA_TILE_BYTES);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int T = sh.T, NKB = sh.nkb, D = sh.heads * FA_DH;
+  const int my_items = (n_items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&tmQ);
+    prefetch_tmap(&tmKV0);
+    prefetch_tmap(&tmKV1);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < FA_Q_STAGES; ++i) { mbar_init(&bar->q_full[i], 1); mbar_init(&bar->q_empty[i], 1); }
+    for (int i = 0; i < FA_KV_STAGES; ++i) { mbar_init(&bar->kv_full[i], 1); mbar_init(&bar->kv_empty[i], 1); }
+    for (int i = 0; i < FA_SBUF; ++i) { mbar_init(&bar->s_full[i], 1); mbar_init(&bar->p_full[i], 8); }   // 8 warps of a group
+    for (int i = 0; i < 2; ++i) { mbar_init(&bar->o_done[i], 1); mbar_init(&bar->o_free[i], 8); }
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(&bar->tmem_slot, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = bar->tmem_slot;
+
+  // item -> (crop, head, first query tile); slot 1 of the last pair of an odd tile count does not exist
+  auto item_of = [&](int i, int &crop, int &head, int &tile0) {
+    const int item = (int)blockIdx.x + i * (int)gridDim.x;
+    const int ch = item / sh.npair, pair = item - ch * sh.npair;
+    crop = ch / sh.heads;
+    head = ch - crop * sh.heads;
+    tile0 = 2 * pair;
+  };
+  auto keys_of = [&](int j) { return j == NKB - 1 ? sh.blk_last : sh.blk0; };
+
+  // Register re-allocation by warpgroup: the control warps give registers back, the softmax warps (64 scores held
+  // between the max and the exp) take them: 128 x 40 + 512 x 112 = 62 464 <= the 61 440 the CTA was launched with + 4 096 freed.
+  if (warp < 4) {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (elect_one()) {
+      for (int i = 0; i < my_items; ++i) {
+        int crop, head, tile0;
+        item_of(i, crop, head, tile0);
+        const int row0 = crop * T;
+        const int qs = i & 1;
+        const bool two = tile0 + 1 < sh.nq;
+        mbar_wait(&bar->q_empty[qs], (((uint32_t)i >> 1) & 1u) ^ 1u);          // S MMAs of item i - 2 retired
+        mbar_arrive_expect_tx(&bar->q_full[qs], (two ? 2u : 1u) * FA_TILE_BYTES);
+        tma_load_2d(sQ + (qs * 2 + 0) * FA_TILE_BYTES, &tmQ, &bar->q_full[qs], head * FA_DH, row0 + tile0 * 128);
+        if (two) tma_load_2d(sQ + (qs * 2 + 1) * FA_TILE_BYTES, &tmQ, &bar->q_full[qs], head * FA_DH, row0 + (tile0 + 1) * 128);
+        for (int j = 0; j < NKB; ++j) {
+          const uint32_t g = (uint32_t)(i * NKB + j);
+          const int st = (int)(g % FA_KV_STAGES);
+          mbar_wait(&bar->kv_empty[st], ((g / FA_KV_STAGES) & 1u) ^ 1u);       // P V MMAs of the stage's last user retired
+          const CUtensorMap *tm = (j == NKB - 1) ? &tmKV1 : &tmKV0;
+          mbar_arrive_expect_tx(&bar->kv_full[st], 2u * (uint32_t)keys_of(j) * FA_DH * 2u);
+          uint8_t *sK = sKV + st * 2 * FA_TILE_BYTES;
+          tma_load_2d(sK, tm, &bar->kv_full[st], D + head * FA_DH, row0 + j * sh.blk0);
+          tma_load_2d(sK + FA_TILE_BYTES, tm, &bar->kv_full[st], 2 * D + head * FA_DH, row0 + j * sh.blk0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer =====================
+    // Entries e = (item i, block j, slot s) in the order ((i * NKB + j) * 2 + s); entry e uses score buffer e % 3.
+    // Entries of a slot that does not exist are passed through (empty commits) so that every barrier sees one
+    // completion per entry and the phase of entry e is (e / 3) & 1 for both sides.
+    if (elect_one()) {
+      const int E = my_items * NKB * 2;
+      uint32_t tiles_done[2] = {0u, 0u};
+      auto issue_s = [&](int e) {
+        const int s = e & 1, t = e >> 1, i = t / NKB, j = t - i * NKB;
+        int crop, head, tile0;
+        item_of(i, crop, head, tile0);
+        const bool exists = tile0 + s < sh.nq;
+        const uint32_t g = (uint32_t)(i * NKB + j);
+        const int st = (int)(g % FA_KV_STAGES);
+        if (exists) {
+          if (j == 0) mbar_wait(&bar->q_full[i & 1], ((uint32_t)i >> 1) & 1u);
+          mbar_wait(&bar->kv_full[st], (g / FA_KV_STAGES) & 1u);
+          tc_fence_after();
+          const uint32_t idesc = umma_idesc_bf16(128, keys_of(j));
+          const uint64_t dq = umma_desc_k_sw128(smem_u32(sQ + ((i & 1) * 2 + s) * FA_TILE_BYTES));
+          const uint64_t dk = umma_desc_k_sw128(smem_u32(sKV + st * 2 * FA_TILE_BYTES));
+          const uint32_t d = tmem_base + (uint32_t)(e % FA_SBUF) * FA_SCOLS;
+#pragma unroll
+          for (int k = 0; k < FA_DH / 16; ++k)
+            umma_bf16(d, dq + (uint64_t)(k * 2), dk + (uint64_t)(k * 2), idesc, (uint32_t)(k != 0));
+        }
+        umma_commit(&bar->s_full[e % FA_SBUF]);
+        if (j == NKB - 1 && s == 1) umma_commit(&bar->q_empty[i & 1]);         // every S MMA of the item is issued
+      };
+      auto issue_pv = [&](int e) {
+        const int s = e & 1, t = e >> 1, i = t / NKB, j = t - i * NKB;
+        int crop, head, tile0;
+        item_of(i, crop, head, tile0);
+        const bool exists = tile0 + s < sh.nq;
+        const uint32_t g = (uint32_t)(i * NKB + j);
+        const int st = (int)(g % FA_KV_STAGES);
+        mbar_wait(&bar->p_full[e % FA_SBUF], ((uint32_t)e / FA_SBUF) & 1u);
+        if (exists) {
+          if (j == 0) {                                                        // O of the slot's previous tile drained
+            mbar_wait(&bar->o_free[s], (tiles_done[s] & 1u) ^ 1u);
+            ++tiles_done[s];
+          }
+          tc_fence_after();
+          const uint32_t idesc = fa_idesc_bmn(128, FA_DH);
+          uint64_t dv = fa_desc_mn_sw128(smem_u32(sKV + st * 2 * FA_TILE_BYTES + FA_TILE_BYTES));
+          uint32_t pc = tmem_base + (uint32_t)(e % FA_SBUF) * FA_SCOLS;
+          const uint32_t o = tmem_base + FA_OCOL + (uint32_t)s * FA_DH;
+          const int nch = keys_of(j) >> 4;
+          for (int k = 0; k < nch; ++k, pc += 8, dv += 128)                    // +16 keys = +2048 B = +128 in (addr >> 4)
+            umma_bf16_ts(o, pc, dv, idesc, (uint32_t)((j | k) != 0));
+          umma_commit(&bar->o_done[s]);
+        }
+        if (s == 1) umma_commit(&bar->kv_empty[st]);                           // both slots have consumed the block
+      };
+      for (int e = 0; e < E && e < FA_SBUF; ++e) issue_s(e);
+      for (int e = 0; e < E; ++e) {
+        issue_pv(e);
+        if (e + FA_SBUF < E) issue_s(e + FA_SBUF);                             // its buffer is free: P V(e) is in order before it
+      }
+    }
+  }
+  } else {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 112;");
+    // ===================== softmax groups =====================
+    const int g = (warp - 4) >> 3;                   // group = slot
+    const int h = ((warp - 4) >> 2) & 1;             // key half of the block
+    const int q = warp & 3;                          // TMEM lane quarter (rows 32 q .. 32 q + 31 of the tile)
+    const int trow = q * 32 + lane;
+    const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
+    const uint32_t o_addr = lane_addr + FA_OCOL + (uint32_t)g * FA_DH + (uint32_t)h * 32;
+    const uint64_t sc2 = pk2(scale_log2e, scale_log2e);
+    const int bar_id = 1 + g * 4 + q;                // 64-thread named barrier of the two warps that share these rows
+    uint32_t nblk = 0;                               // blocks of existing tiles this slot has seen (o_done phases, xmax parity)
+    uint32_t ntile = 0;                              // existing tiles this slot has seen (o_free phases)
+    for (int i = 0; i < my_items; ++i) {
+      int crop, head, tile0;
+      item_of(i, crop, head, tile0);
+      const int tile = tile0 + g;
+      const bool exists = tile < sh.nq;
+      const bool live = exists && tile * 128 + q * 32 < T;                     // warp-uniform: some row of this warp is a token
+      float m_used = 0.f, l = 0.f;
+      for (int j = 0; j < NKB; ++j) {
+        const int e = (i * NKB + j) * 2 + g;
+        const uint32_t sbuf = lane_addr + (uint32_t)(e % FA_SBUF) * FA_SCOLS;
+        mbar_wait(&bar->s_full[e % FA_SBUF], ((uint32_t)e / FA_SBUF) & 1u);
+        if (!live) {
+          __syncwarp();
+          if (lane == 0) mbar_arrive(&bar->p_full[e % FA_SBUF]);
+          if (exists) ++nblk;
+          continue;
+        }
+        tc_fence_after();
+        const int nch = keys_of(j) >> 4;                                       // 16-key chunks of the block
+        const int c0 = h ? (nch + 1) >> 1 : 0, c1 = h ? nch : (nch + 1) >> 1;  // this thread's chunks (<= 4)
+        const int key0 = j * sh.blk0 + 16 * c0;
+        // ---- one read of the scores
+        uint32_t r[4][16];
+#pragma unroll
+        for (int c = 0; c < 4; ++c)
+          if (c0 + c < c1) tmem_ld_32x16(sbuf + 16 * (c0 + c), r[c]);
+        tmem_ld_wait();
+        float mx = -INFINITY;
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          if (c0 + c < c1) {
+            if (key0 + 16 * c + 16 > T) {                                      // keys >= T are padding: -inf
+#pragma unroll
+              for (int k = 0; k < 16; ++k)
+                if (key0 + 16 * c + k >= T) r[c][k] = 0xff800000u;
+            }
+#pragma unroll
+            for (int k = 0; k < 16; k += 2) mx = fa_max3(mx, __uint_as_float(r[c][k]), __uint_as_float(r[c][k + 1]));
+          }
+        }
+        // ---- row maximum of the block: exchange with the thread holding the other key half
+        float *xm = &bar->xmax[g][nblk & 1u][h][trow];
+        *xm = mx;
+        asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
+        mx = fmaxf(mx, bar->xmax[g][nblk & 1u][h ^ 1][trow]);
+        // ---- online softmax: raise the running maximum only when the block exceeds it by more than 2^THR
+        if (j == 0) {
+          m_used = mx;
+        } else {
+          mbar_wait(&bar->o_done[g], (nblk - 1u) & 1u);                        // P V of the previous block has retired
+          const bool need = (mx - m_used) * scale_log2e > FA_RESCALE_THR;
+          if (__any_sync(0xffffffffu, need)) {
+            float f = 1.f;
+            if (need) {
+              f = fa_ex2((m_used - mx) * scale_log2e);
+              m_used = mx;
+              l *= f;
+            }
+            tc_fence_after();
+#pragma unroll 1
+            for (int part = 0; part < 4; ++part) {                             // 8 columns at a time: 64 scores are live
+              uint32_t o[8];
+              fa_tmem_ld_32x8(o_addr + 8 * part, o);
+              tmem_ld_wait();
+#pragma unroll
+              for (int k = 0; k < 8; ++k) o[k] = __float_as_uint(__uint_as_float(o[k]) * f);
+              tmem_st_32x8(o_addr + 8 * part, o);
+            }
+          }
+        }
+        // ---- p = exp2((s - m) * scale); row sum; P -> tensor memory as packed bf16 (chunk k at column 8 k)
+        const float mneg = -m_used * scale_log2e;
+        const uint64_t mn2 = pk2(mneg, mneg);
+        uint64_t sum2 = pk2(0.f, 0.f);
+#pragma unroll
+        for (int c = 0; c < 4; ++c) {
+          if (c0 + c < c1) {
+            uint32_t w[8];
+#pragma unroll
+            for (int k = 0; k < 16; k += 2) {
+              float x0, x1;
+              unpk2(fma2(pk2(__uint_as_float(r[c][k]), __uint_as_float(r[c][k + 1])), sc2, mn2), x0, x1);
+              const float p0 = fa_ex2(x0), p1 = fa_ex2(x1);
+              sum2 = add2(sum2, pk2(p0, p1));
+              w[k >> 1] = fa_pack_bf16x2(p0, p1);
+            }
+            tmem_st_32x8(sbuf + 8 * (c0 + c), w);
+          }
+        }
+        {
+          float s0, s1;
+          unpk2(sum2, s0, s1);
+          l += s0 + s1;
+        }
+        tmem_st_wait();
+        tc_fence_before();                           // P (and a rescaled O) are in tensor memory before the MMA reads them
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bar->p_full[e % FA_SBUF]);
+        ++nblk;
+      }
+      if (!exists) continue;
+      ++ntile;
+      if (!live) {
+        // Nothing to drain, but this warp's arrival must land in THIS tile's phase of o_free: a warp that only
+        // passes barriers on runs ahead of the warps that are still draining the slot's previous tile, so it waits
+        // until that tile's phase has completed (the MMA warp is waiting for the same phase before its first P V).
+        if (ntile > 1u) mbar_wait(&bar->o_free[g], (ntile - 2u) & 1u);
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&bar->o_free[g]);
+        continue;
+      }
+      // ---- O / row sum -> bf16 -> global (this thread: 32 of the 64 head-dim columns of its row)
+      bar->xsum[g][h][trow] = l;
+      asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
+      const float inv = 1.0f / (l + bar->xsum[g][h ^ 1][trow]);
+      mbar_wait(&bar->o_done[g], (nblk - 1u) & 1u);
+      tc_fence_after();
+      uint32_t o[32];                                // two x16 loads: the x32 shape runs at a quarter of the x16 rate
+      tmem_ld_32x16(o_addr, *reinterpret_cast<uint32_t(*)[16]>(&o[0]));
+      tmem_ld_32x16(o_addr + 16, *reinterpret_cast<uint32_t(*)[16]>(&o[16]));
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&bar->o_free[g]);   // the accumulator may be overwritten by the slot's next tile
+      const int tok = tile * 128 + trow;
+      if (tok < T) {
+        uint4 *dst = reinterpret_cast<uint4 *>(out + ((size_t)crop * T + tok) * D + (size_t)head * FA_DH + h * 32);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          uint4 u;
+          u.x = fa_pack_bf16x2(__uint_as_float(o[8 * k + 0]) * inv, __uint_as_float(o[8 * k + 1]) * inv);
+          u.y = fa_pack_bf16x2(__uint_as_float(o[8 * k + 2]) * inv, __uint_as_float(o[8 * k + 3]) * inv);
+          u.z = fa_pack_bf16x2(__uint_as_float(o[8 * k + 4]) * inv, __uint_as_float(o[8 * k + 5]) * inv);
+          u.w = fa_pack_bf16x2(__uint_as_float(o[8 * k + 6]) * inv, __uint_as_float(o[8 * k + 7]) * inv);
+          dst[k] = u;
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) tmem_dealloc(tmem_base, 512);
+}
+
+}  // namespace
+
+int yv_attention_fa_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, int T, int heads, int dh,
+                           cudaStream_t s) {
+  YV_REQUIRE(dh == FA_DH, "attention: head dim %d unsupported (need %d)", dh, FA_DH);
+  YV_REQUIRE(n >= 1 && heads >= 1 && T >= 1, "attention: bad shape");
+  YV_REQUIRE(((uintptr_t)qkv % 16) == 0 && ((uintptr_t)out % 16) == 0, "attention: operands must be 16-byte aligned");
+  FaShape sh;
+  sh.T = T;
+  sh.heads = heads;
+  const int t16 = (T + 15) & ~15, nch = t16 >> 4;
+  if (t16 <= 128) { sh.nkb = 1; sh.blk0 = sh.blk_last = t16; }
+  else if (t16 <= 256) { sh.nkb = 2; sh.blk0 = 16 * ((nch + 1) >> 1); sh.blk_last = t16 - sh.blk0; }
+  else { sh.nkb = (t16 + 127) / 128; sh.blk0 = 128; sh.blk_last = t16 - (sh.nkb - 1) * 128; }
+  sh.nq = (T + 127) >> 7;
+  sh.npair = (sh.nq + 1) >> 1;
+  const long long items = (long long)n * heads * sh.npair;
+  YV_REQUIRE(items * (long long)sh.nkb * 2 < (1ll << 30), "attention: too many work items");
+  const int D = heads * FA_DH;
+  const float scale_log2e = (1.0f / sqrtf((float)dh)) * 1.4426950408889634f;
+  CUtensorMap tmQ, tmKV0, tmKV1;
+  int rc = yv_tmap_bf16_2d(&tmQ, qkv, (uint64_t)n * T, (uint64_t)3 * D, 128u);
+  if (rc) return rc;
+  if ((rc = yv_tmap_bf16_2d(&tmKV0, qkv, (uint64_t)n * T, (uint64_t)3 * D, (uint32_t)sh.blk0))) return rc;
+  if ((rc = yv_tmap_bf16_2d(&tmKV1, qkv, (uint64_t)n * T, (uint64_t)3 * D, (uint32_t)sh.blk_last))) return rc;
+  rc = yv_device_once(YV_INIT_ATTN_FA, []() -> int {
+    YV_CUDA(cudaFuncSetAttribute(attention_fa_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FA_SMEM));
+    return YV_OK;
+  });
+  if (rc) return rc;
+  YvProf prof(YV_K_ATTN, s, 4.0 * n * heads * (double)T * T * dh);
+  const int grid = items < yv_num_sms() ? (int)items : yv_num_sms();
+  attention_fa_kernel<<<grid, FA_THREADS, FA_SMEM, s>>>(tmQ, tmKV0, tmKV1, out, (int)items, sh, scale_log2e);
+  YV_LAUNCH_CHECK();
+  return YV_OK;
+}

@@ -19,6 +19,7 @@
 //            transpose), into TMEM columns [192, 256);
 //   output   O * (1 / sum) -> bf16 -> global.
 // The fp32 scores never leave the SM; HBM traffic is qkv in, out out.
+#include <cstdlib>
 #include "common.cuh"
 #include "gemm_sm100.cuh"
 #include "sm100_ptx.cuh"
@@ -627,6 +628,10 @@ int yv_attention_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, int
                         cudaStream_t s) {
   YV_REQUIRE(dh == AT_DH, "attention: head dim %d unsupported (need %d)", dh, AT_DH);
   YV_REQUIRE(n >= 1 && heads >= 1 && T >= 1, "attention: bad shape");
+  // YV_ATTN=legacy selects the round-1 kernels (A/B timing): attention_pipe / attention_tc for T <= 256 and the
+  // mma.sync multi-block kernel above that; the default is the flash-style tcgen05 kernel of attention_fa.cu
+  static const bool legacy = []() { const char *e = getenv("YV_ATTN"); return e && e[0] == 'l'; }();
+  if (!legacy) return yv_attention_fa_launch(qkv, out, n, T, heads, dh, s);
   if (T > 256) return yv_attention_long_launch(qkv, out, n, T, heads, dh, s);   // ViT-B/8: mma.sync multi-block path
   YV_REQUIRE(((uintptr_t)qkv % 16) == 0 && ((uintptr_t)out % 16) == 0, "attention: operands must be 16-byte aligned");
   const int NK = (T + 15) & ~15, NG = (T + 127) >> 7;

@@ -15,7 +15,15 @@
 //          the N^2/2 of a full bitmask.
 // IoU arithmetic = torchvision.ops.box_iou in fp32, no FMA contraction, IEEE division;
 // survivors need iou < thr (strict), NaN is suppressed.  Integer outputs, bit-exact.
+//
+// Large candidate lists (the 30 000-box stress case, BASELINE.json configs[4]): a CLUSTER of NMS_CLUSTER CTAs per
+// image.  The O(survivors x kept) part -- applying the kept heads of a pass to the rest of the list -- is split
+// over the CTAs of the cluster (contiguous slices of the list, so the order is preserved); every CTA resolves the
+// 64 heads redundantly (4096 IoUs, the same deterministic arithmetic, so nothing has to be broadcast), the CTAs
+// exchange their survivor counts through distributed shared memory and write their compacted slices at the
+// resulting offsets of the ONE global list.  Two cluster barriers per pass.
 #include "common.cuh"
+#include <cstdlib>
 
 namespace {
 
@@ -24,6 +32,27 @@ constexpr int NMS_W = NMS_T / 32;
 constexpr int NMS_MAX_N = 65536;
 constexpr int NMS_HEAD = 64;
 constexpr int NMS_MAX_ITERS = (NMS_MAX_N / NMS_W + 31) / 32;   // ballot words per warp per pass
+constexpr int NMS_CLUSTER = 4;          // CTAs per image for long lists (32 images x 4 = 128 of 148 SMs in cfg5)
+constexpr int NMS_CLUSTER_MIN_N = 4096; // shorter lists stay on one CTA (two cluster barriers per pass would dominate)
+
+__device__ __forceinline__ unsigned cluster_rank() {
+  unsigned r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+// release / acquire at cluster scope: global and shared writes before it are visible to the cluster after it
+__device__ __forceinline__ void cluster_barrier() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// store into the same shared-memory variable of CTA `cta` of the cluster
+__device__ __forceinline__ void st_cluster_s32(int *p, unsigned cta, int v) {
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "st.shared::cluster.s32 [ra], %2;\n\t}"
+      ::"r"((unsigned)__cvta_generic_to_shared(p)), "r"(cta), "r"(v)
+      : "memory");
+}
 
 __device__ __forceinline__ float max_t(float a, float b) {   // torch.max: NaN propagates
   return (a != a) ? a : ((b != b) ? b : (a > b ? a : b));
@@ -62,11 +91,14 @@ struct NmsWs {
   float4 *lbox[2];
 };
 
+// CL = CTAs per image (1, or NMS_CLUSTER launched as a thread-block cluster)
+template <int CL>
 __global__ void __launch_bounds__(NMS_T)
-nms_kernel(const float4 *__restrict__ boxes, const float *__restrict__ scores,
+nms_kernel(const float4 *boxes, const float *scores,
            const int32_t *__restrict__ counts, int stride, int n_all, float thr, int max_keep,
-           int32_t *__restrict__ keep, int32_t *__restrict__ keep_counts, NmsWs ws, int rule) {
-  const int b = blockIdx.x;
+           int32_t *keep, int32_t *__restrict__ keep_counts, NmsWs ws, int rule) {
+  const int b = blockIdx.x / CL;
+  const int rank = CL > 1 ? (int)cluster_rank() : 0;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   int n = counts ? counts[b] : n_all;
   n = n < 0 ? 0 : (n > stride ? stride : n);
@@ -90,13 +122,15 @@ nms_kernel(const float4 *__restrict__ boxes, const float *__restrict__ scores,
   __shared__ int s_k;
   __shared__ unsigned s_ballot[NMS_W][NMS_MAX_ITERS];
   __shared__ int s_wcnt[NMS_W];
+  __shared__ int s_ccnt[CL];            // survivors of every CTA of the cluster in this pass (written by its owner)
 
-  if (n == 0) {
-    if (tid == 0) keep_counts[b] = 0;
+  if (n == 0) {                         // (uniform over the cluster: no barrier is skipped by a part of it)
+    if (tid == 0 && rank == 0) keep_counts[b] = 0;
     return;
   }
 
-  // ------------------------------------------------------------------ phase 1: sort
+  // ------------------------------------------------------------------ phase 1: sort (CTA 0 of the cluster)
+  if (rank == 0) {
   for (int i = tid; i < n; i += NMS_T) {
     key[0][i] = score_key_desc(scores[i]);
     idx[0][i] = i;
@@ -181,7 +215,9 @@ nms_kernel(const float4 *__restrict__ boxes, const float *__restrict__ scores,
     lidx[0][i] = id;
     lbox[0][i] = boxes[id];
   }
+  }  // rank == 0
   __syncthreads();
+  if (CL > 1) cluster_barrier();        // the list is in global memory for every CTA of the cluster
 
   // ------------------------------------------------------------------ phase 2: greedy sweep
   const int kmax = (max_keep > 0 && max_keep < n) ? max_keep : n;
@@ -227,7 +263,7 @@ nms_kernel(const float4 *__restrict__ boxes, const float *__restrict__ scores,
       for (int h = lane; h < hb; h += 32) {
         if (kept & (1ull << h)) {
           const int slot = __popcll(kept & ((1ull << h) - 1ull));
-          keep[nkeep + slot] = s_hidx[h];
+          if (rank == 0) keep[nkeep + slot] = s_hidx[h];
           const float4 p = s_hbox[h];
           s_kbox[slot] = p;
           s_karea[slot] = area_of(p);
@@ -241,9 +277,12 @@ nms_kernel(const float4 *__restrict__ boxes, const float *__restrict__ scores,
     const int rem = m - hb;
     if (rem == 0 || nkeep >= kmax) break;
 
-    // apply the k kept heads to the rest of the list and compact the survivors
-    const int seg = ((rem + NMS_W - 1) / NMS_W + 31) & ~31;
-    const int w_beg = hb + min(rem, warp * seg), w_end = hb + min(rem, (warp + 1) * seg);
+    // apply the k kept heads to the rest of the list and compact the survivors: this CTA's slice of the rest,
+    // cut into one contiguous segment per warp
+    const int cseg = CL > 1 ? (((rem + CL - 1) / CL + 31) & ~31) : rem;
+    const int c_beg = min(rem, rank * cseg), c_len = min(rem, (rank + 1) * cseg) - c_beg;
+    const int seg = ((c_len + NMS_W - 1) / NMS_W + 31) & ~31;
+    const int w_beg = hb + c_beg + min(c_len, warp * seg), w_end = hb + c_beg + min(c_len, (warp + 1) * seg);
     int wcnt = 0, it = 0;
     for (int i0 = w_beg; i0 < w_end; i0 += 32, ++it) {
       const int i = i0 + lane;
@@ -266,6 +305,19 @@ nms_kernel(const float4 *__restrict__ boxes, const float *__restrict__ scores,
       if (w < warp) off += t;
       m_new += t;
     }
+    if (CL > 1) {                       // cluster-wide offsets: every CTA publishes its count to all of them
+      if (tid < CL) st_cluster_s32(&s_ccnt[rank], (unsigned)tid, m_new);
+      cluster_barrier();
+      int coff = 0, tot = 0;
+#pragma unroll
+      for (int c = 0; c < CL; ++c) {
+        const int t = s_ccnt[c];
+        if (c < rank) coff += t;
+        tot += t;
+      }
+      off += coff;
+      m_new = tot;
+    }
     int32_t *lo = lidx[lc ^ 1];
     float4 *bo = lbox[lc ^ 1];
     it = 0;
@@ -279,10 +331,11 @@ nms_kernel(const float4 *__restrict__ boxes, const float *__restrict__ scores,
       off += __popc(bal);
     }
     __syncthreads();
+    if (CL > 1) cluster_barrier();      // the new list is complete (and s_ccnt may be rewritten)
     lc ^= 1;
     m = m_new;
   }
-  if (tid == 0) keep_counts[b] = nkeep;
+  if (tid == 0 && rank == 0) keep_counts[b] = nkeep;
 }
 
 struct NmsLayout {
@@ -330,8 +383,27 @@ YV_EXPORT int yv_nms_batched_rule(const float *boxes, const float *scores, const
     W.lbox[i] = (float4 *)(w + L.o_lbox[i]);
   }
   YvProf prof(YV_K_NMS, (cudaStream_t)stream, counts ? 0.0 : (double)B * n_all * 20.0);
-  nms_kernel<<<B, NMS_T, 0, (cudaStream_t)stream>>>((const float4 *)boxes, scores, counts, stride, n_all,
-                                                    iou_thr, max_keep, keep, keep_counts, W, rule);
+  // long lists: a cluster of NMS_CLUSTER CTAs per image (YV_NMS_CLUSTER=0 / 1 forces one CTA / the cluster, A/B timing)
+  static const int force = []() { const char *e = getenv("YV_NMS_CLUSTER"); return e ? atoi(e) : -1; }();
+  // (with per-image `counts` the list lengths live on the device -- the detector path, hundreds of candidates per
+  // image -- and one CTA per image is right; the cluster is for callers that state a long n_all)
+  const bool cluster = force >= 0 ? force != 0 : (!counts && n_all >= NMS_CLUSTER_MIN_N);
+  if (cluster) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)B * NMS_CLUSTER);
+    cfg.blockDim = dim3(NMS_T);
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = NMS_CLUSTER; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    YV_CUDA(cudaLaunchKernelEx(&cfg, nms_kernel<NMS_CLUSTER>, (const float4 *)boxes, scores, counts, stride, n_all,
+                               iou_thr, max_keep, keep, keep_counts, W, rule));
+  } else {
+    nms_kernel<1><<<B, NMS_T, 0, (cudaStream_t)stream>>>((const float4 *)boxes, scores, counts, stride, n_all,
+                                                         iou_thr, max_keep, keep, keep_counts, W, rule);
+  }
   YV_LAUNCH_CHECK();
   return YV_OK;
 }

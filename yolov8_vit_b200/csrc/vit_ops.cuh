@@ -26,6 +26,9 @@ int yv_attention_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, int
                         cudaStream_t s);
 int yv_attention_long_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, int T, int heads, int dh,
                              cudaStream_t s);
+// attention_fa.cu: flash-style tcgen05 kernel for any T (single read of the scores, two query tiles in flight)
+int yv_attention_fa_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, int T, int heads, int dh,
+                           cudaStream_t s);
 
 // x[c*T, :] = cls + pos[0]  (the class-token row of every crop); x is the residual stream, f32 or f16
 int yv_cls_rows_launch(void *x, bool x_f16, const float *cls_pos0, int n, int T, int dim, cudaStream_t s);
