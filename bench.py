@@ -290,8 +290,27 @@ def event_timed(fn, reps, flush=None):
     return ts[len(ts) // 2]
 
 
+def kernel_ms(fn, kind, reps=5, flush=None):
+    """Mean device time of the library's own launches of kernel class `kind` inside `fn` (every launch bracketed by
+    CUDA events on its stream, yv_prof_*): the kernel alone, without the host-side gaps an event pair around a
+    ~50 us Python call also contains."""
+    import torch
+    from yolov8_vit_b200 import _lib
+    fn()
+    _lib.prof_enable(True)
+    for _ in range(reps):
+        if flush is not None:
+            flush.zero_()
+        fn()
+    torch.cuda.synchronize()
+    p = _lib.prof_read()[kind]
+    _lib.prof_enable(False)
+    return p["ms"] / max(p["launches"], 1)
+
+
 def run_extras(dev, model, hbm):
-    """cfg2 / cfg5 / cfg3 of BASELINE.json as short event-timed passes on one GPU (L2 flushed between reps)."""
+    """cfg2 / cfg5 / cfg3 of BASELINE.json as short event-timed passes on one GPU (L2 flushed between reps).
+    `ms` = CUDA events around the public op (includes host-side launch gaps), `kernel_ms` = the kernel itself."""
     import torch
     from yolov8_vit_b200 import ops, synth
     out = {}
@@ -300,10 +319,13 @@ def run_extras(dev, model, hbm):
     head = synth.make_head(64, 80, 8400, n_obj=32, n_jit=24, seed=synth.SEED0 + 2).to(dev)
     ms = event_timed(lambda: ops.decode_filter(head, 0.35), 10, flush)
     cand = ops.decode_filter(head, 0.35)
-    out["cfg2_decode"] = {"ms": ms, "gbs": head.numel() * 4 / ms / 1e6, "hbm_frac": head.numel() * 4 / ms / 1e6 / hbm,
-                          "shape": [64, 84, 8400]}
+    kms = kernel_ms(lambda: ops.decode_filter(head, 0.35), "decode_filter", 5, flush)
+    out["cfg2_decode"] = {"ms": ms, "kernel_ms": kms, "gbs": head.numel() * 4 / kms / 1e6,
+                          "hbm_frac": head.numel() * 4 / kms / 1e6 / hbm, "shape": [64, 84, 8400]}
     ms = event_timed(lambda: ops.nms_batched(cand[0], cand[1], cand[4], 0.45), 10, flush)
-    out["cfg2_nms"] = {"us_per_img": ms * 1e3 / 64, "ms": ms, "mean_candidates": float(cand[4].float().mean()), "iou": 0.45}
+    kms = kernel_ms(lambda: ops.nms_batched(cand[0], cand[1], cand[4], 0.45), "nms", 5, flush)
+    out["cfg2_nms"] = {"us_per_img": kms * 1e3 / 64, "kernel_ms": kms, "ms": ms,
+                       "mean_candidates": float(cand[4].float().mean()), "iou": 0.45}
     del head, cand
     # cfg5: NMS stress, 32 images x 30 000 dense-overlap boxes, threshold sweep
     boxes, scores = synth.make_nms_stress(32, 30000, seed=synth.SEED0 + 5)

@@ -12,7 +12,7 @@ for f in tests/test_gpu_vit.py tests/test_gpu_shapes.py tests/test_gpu_ref.py te
   echo "rc=$?" >> gpurun_out/r2b_pytest.log
 done
 grep -E "^===|passed|failed|rc=|Error|error|assert" gpurun_out/r2b_pytest.log | head -60
-for v in "fa 3" "legacy 3" "fa 0" "fa 2" "fa 4"; do set -- $v
+for v in "fa 2" "legacy 2" "legacy 0" "legacy 1"; do set -- $v
   YV_ATTN=$1 YV_LN_F16_CTAS=$2 timeout 600 python bench.py --steps 10 --warmup 3 --no-extras --no-cpu-baseline > gpurun_out/r2b_bench_$1_ln$2.json 2> gpurun_out/r2b_bench_$1_ln$2.err
   echo "bench attn=$1 ln_ctas=$2 rc=$?"; python - <<PY
 import json

@@ -49,6 +49,7 @@ constexpr int FA_SBUF = 3;                          // rotating score buffers
 constexpr int FA_SCOLS = 128;                       // TMEM columns per score buffer
 constexpr int FA_OCOL = FA_SBUF * FA_SCOLS;         // O accumulators: [384, 448) and [448, 512)
 constexpr float FA_RESCALE_THR = 8.0f;              // log2 units
+constexpr int FA_REGS_CTRL = 32, FA_REGS_SOFTMAX = 112;   // setmaxnreg targets (the kernel is compiled for 96 = 65536 / 640)
 
 struct FaShared {
   uint64_t q_full[FA_Q_STAGES], q_empty[FA_Q_STAGES];
@@ -145,9 +146,12 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   auto keys_of = [&](int j) { return j == NKB - 1 ? sh.blk_last : sh.blk0; };
 
   // Register re-allocation by warpgroup: the control warps give registers back, the softmax warps (64 scores held
-  // between the max and the exp) take them: 128 x 40 + 512 x 112 = 62 464 <= the 61 440 the CTA was launched with + 4 096 freed.
+  // between the max and the exp) take them.  setmaxnreg.inc can only draw on what the CTA's OWN warps released
+  // (USETMAXREG.TRY_ALLOC.CTAPOOL spins otherwise -- a first version with 40 / 112 hung there): the CTA starts with
+  // 640 x 96 registers, 128 x (96 - 32) = 8192 are released and 512 x (112 - 96) = 8192 are taken.
+  static_assert(128 * (96 - FA_REGS_CTRL) >= 512 * (FA_REGS_SOFTMAX - 96), "setmaxnreg: the control warps must release what the softmax warps take");
   if (warp < 4) {
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 40;");
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(FA_REGS_CTRL));
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (elect_one()) {
@@ -236,7 +240,7 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     }
   }
   } else {
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 112;");
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(FA_REGS_SOFTMAX));
     // ===================== softmax groups =====================
     const int g = (warp - 4) >> 3;                   // group = slot
     const int h = ((warp - 4) >> 2) & 1;             // key half of the block

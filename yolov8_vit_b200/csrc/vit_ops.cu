@@ -141,42 +141,40 @@ layernorm_kernel(const void *xv, size_t in_stride, const __nv_bfloat16 *__restri
 }
 
 // fp16 residual stream -> bf16 normalised rows, 4 B of traffic per element.  With so few bytes per row (1.5 KB at
-// dim 768) one row per warp leaves too little in flight to cover the HBM latency (measured 3.2 TB/s); here a warp
-// owns LN_R rows per iteration and issues all their loads before the first reduction.
-constexpr int LN_R = 2;
+// dim 768) one row per warp leaves too little in flight to cover the HBM latency (measured 3.2 TB/s with 48 KB per
+// SM, 3.6 TB/s with 72 KB); here a warp owns LN_R rows per iteration, issues all their loads before the first
+// reduction and keeps them as RAW fp16 in registers (3 x 16 B per row and lane), converting on the fly in each of the
+// three passes (sum, centred sum of squares, normalise), so that 2 CTAs x 8 warps x 6 rows = 144 KB are in flight per SM
+// (128 registers; capping the kernel at 80 registers for a third CTA spills).
+constexpr int ln_rows_per_warp(int nch) { return nch <= 3 ? 6 : 4; }
 template <int NCH>                                  // dim = 256 * NCH (compile-time: the row lives in registers)
-__global__ void __launch_bounds__(LN_WARPS * 32, NCH <= 3 ? 3 : 2)
+__global__ void __launch_bounds__(LN_WARPS * 32, 2)
 layernorm_f16_kernel(const __half *__restrict__ x, size_t in_stride, const float *__restrict__ gamma,
                      const float *__restrict__ beta, __nv_bfloat16 *__restrict__ y, int rows, float eps) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  constexpr int nch = NCH, dim = 256 * NCH, LN_MAXCH = NCH;
+  constexpr int dim = 256 * NCH, LN_R = ln_rows_per_warp(NCH);
   const int ngrp = (rows + LN_WARPS * LN_R - 1) / (LN_WARPS * LN_R);          // groups of LN_WARPS * LN_R rows
   for (int gi = blockIdx.x; gi < ngrp; gi += gridDim.x) {
     const int row0 = (gi * LN_WARPS + warp) * LN_R;
-    uint4 raw[LN_R][LN_MAXCH];
+    uint4 raw[LN_R][NCH];
 #pragma unroll
     for (int r = 0; r < LN_R; ++r)
 #pragma unroll
-      for (int c = 0; c < LN_MAXCH; ++c)
-        if (c < nch && row0 + r < rows)
-          raw[r][c] = *reinterpret_cast<const uint4 *>(x + (size_t)(row0 + r) * in_stride + c * 256 + lane * 8);
+      for (int c = 0; c < NCH; ++c)
+        if (row0 + r < rows)
+          raw[r][c] = __ldcs(reinterpret_cast<const uint4 *>(x + (size_t)(row0 + r) * in_stride + c * 256 + lane * 8));
 #pragma unroll
     for (int r = 0; r < LN_R; ++r) {
       const int row = row0 + r;
       if (row >= rows) continue;                                               // warp-uniform
-      float v[LN_MAXCH][8];
       float sum = 0.f;
 #pragma unroll
-      for (int c = 0; c < LN_MAXCH; ++c) {
-        if (c < nch) {
-          const __half2 *h = reinterpret_cast<const __half2 *>(&raw[r][c]);
+      for (int c = 0; c < NCH; ++c) {
+        const __half2 *h = reinterpret_cast<const __half2 *>(&raw[r][c]);
 #pragma unroll
-          for (int k = 0; k < 4; ++k) {
-            const float2 f = __half22float2(h[k]);
-            v[c][2 * k] = f.x;
-            v[c][2 * k + 1] = f.y;
-            sum += f.x + f.y;
-          }
+        for (int k = 0; k < 4; ++k) {
+          const float2 f = __half22float2(h[k]);
+          sum += f.x + f.y;
         }
       }
 #pragma unroll
@@ -184,28 +182,34 @@ layernorm_f16_kernel(const __half *__restrict__ x, size_t in_stride, const float
       const float mean = sum / (float)dim;
       float sq = 0.f;
 #pragma unroll
-      for (int c = 0; c < LN_MAXCH; ++c)
-        if (c < nch)
+      for (int c = 0; c < NCH; ++c) {
+        const __half2 *h = reinterpret_cast<const __half2 *>(&raw[r][c]);
 #pragma unroll
-          for (int k = 0; k < 8; ++k) { const float d = v[c][k] - mean; sq += d * d; }
+        for (int k = 0; k < 4; ++k) {
+          const float2 f = __half22float2(h[k]);
+          const float d0 = f.x - mean, d1 = f.y - mean;
+          sq += d0 * d0 + d1 * d1;
+        }
+      }
 #pragma unroll
       for (int d = 16; d > 0; d >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, d);
       const float rstd = rsqrtf(sq / (float)dim + eps);
 #pragma unroll
-      for (int c = 0; c < LN_MAXCH; ++c) {
-        if (c < nch) {
-          const int e = c * 256 + lane * 8;
-          const float4 g0 = __ldg(reinterpret_cast<const float4 *>(gamma + e)), g1 = __ldg(reinterpret_cast<const float4 *>(gamma + e + 4));
-          const float4 b0 = __ldg(reinterpret_cast<const float4 *>(beta + e)), b1 = __ldg(reinterpret_cast<const float4 *>(beta + e + 4));
-          const float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-          const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-          __nv_bfloat162 hh[4];
+      for (int c = 0; c < NCH; ++c) {
+        const int e = c * 256 + lane * 8;
+        const float4 g0 = __ldg(reinterpret_cast<const float4 *>(gamma + e)), g1 = __ldg(reinterpret_cast<const float4 *>(gamma + e + 4));
+        const float4 b0 = __ldg(reinterpret_cast<const float4 *>(beta + e)), b1 = __ldg(reinterpret_cast<const float4 *>(beta + e + 4));
+        const float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+        const float bb[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+        const __half2 *h = reinterpret_cast<const __half2 *>(&raw[r][c]);
+        __nv_bfloat162 hh[4];
 #pragma unroll
-          for (int k = 0; k < 4; ++k)
-            hh[k] = __floats2bfloat162_rn((v[c][2 * k] - mean) * rstd * g[2 * k] + bb[2 * k],
-                                          (v[c][2 * k + 1] - mean) * rstd * g[2 * k + 1] + bb[2 * k + 1]);
-          *reinterpret_cast<uint4 *>(y + (size_t)row * dim + e) = *reinterpret_cast<const uint4 *>(hh);
+        for (int k = 0; k < 4; ++k) {
+          const float2 f = __half22float2(h[k]);
+          hh[k] = __floats2bfloat162_rn((f.x - mean) * rstd * g[2 * k] + bb[2 * k],
+                                        (f.y - mean) * rstd * g[2 * k + 1] + bb[2 * k + 1]);
         }
+        *reinterpret_cast<uint4 *>(y + (size_t)row * dim + e) = *reinterpret_cast<const uint4 *>(hh);
       }
     }
   }
@@ -338,8 +342,9 @@ int yv_ln2_launch(const void *x, int x_type, size_t in_stride, const __nv_bfloat
   if (x_f32 && cs) layernorm_kernel<1, true><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, delta, delta2, delta_stride, writeback ? 1 : 0, gamma, beta, y, rows, dim, eps, rev);
   else if (x_f32) layernorm_kernel<1><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, delta, delta2, delta_stride, writeback ? 1 : 0, gamma, beta, y, rows, dim, eps, rev);
   else if (x_type == 2) {
-    static const int f16_ctas = [] { const char *e = getenv("YV_LN_F16_CTAS"); return e ? atoi(e) : 3; }();    // per SM (75 registers)
-    int g16 = (rows + LN_WARPS * LN_R - 1) / (LN_WARPS * LN_R);
+    static const int f16_ctas = [] { const char *e = getenv("YV_LN_F16_CTAS"); return e ? atoi(e) : 2; }();    // per SM (128 registers)
+    const int rpw = ln_rows_per_warp(dim >> 8);
+    int g16 = (rows + LN_WARPS * rpw - 1) / (LN_WARPS * rpw);
     if (f16_ctas > 0 && g16 > yv_num_sms() * f16_ctas) g16 = yv_num_sms() * f16_ctas;
     if (f16_ctas == 0) layernorm_kernel<2><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, nullptr, nullptr, 0, 0, gamma, beta, y, rows, dim, eps, rev);
     else if (dim == 768) layernorm_f16_kernel<3><<<g16, LN_WARPS * 32, 0, s>>>((const __half *)x, in_stride, gamma, beta, y, rows, eps);
