@@ -182,60 +182,80 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     // Entries e = (item i, block j, slot s) in the order ((i * NKB + j) * 2 + s); entry e uses score buffer e % 3.
     // Entries of a slot that does not exist are passed through (empty commits) so that every barrier sees one
     // completion per entry and the phase of entry e is (e / 3) & 1 for both sides.
+    // This ONE thread is on the critical path of both softmax groups (P V(e) and S(e + 3) are issued between the
+    // arrival of P(e) and the moment a group needs its next scores), so its bookkeeping is incremental: two
+    // cursors walk the entry sequence (one for the S stream, three entries ahead, one for the P V stream) with
+    // adds and compares only -- a first version that decoded (i, j, s), the ring stages and the buffer from e with
+    // divisions in every call spent ~4 k clocks per entry and made the kernel slower than the one it replaces.
     if (elect_one()) {
+      struct Cursor {
+        int i, j, s;            // item, key block, slot
+        int buf;                // e % 3
+        uint32_t bph;           // (e / 3) & 1
+        int st;                 // K / V ring stage of (i, j)
+        uint32_t kph;           // its phase
+        bool two;               // the item has a second query tile
+      };
       const int E = my_items * NKB * 2;
+      auto has_two = [&](int i) {
+        if (sh.npair == 1) return sh.nq >= 2;
+        const int item = (int)blockIdx.x + i * (int)gridDim.x;
+        return 2 * (item % sh.npair) + 1 < sh.nq;
+      };
+      auto advance = [&](Cursor &c) {
+        if (++c.buf == FA_SBUF) { c.buf = 0; c.bph ^= 1u; }
+        c.s ^= 1;
+        if (c.s == 0) {
+          if (++c.st == FA_KV_STAGES) { c.st = 0; c.kph ^= 1u; }
+          if (++c.j == NKB) { c.j = 0; ++c.i; c.two = has_two(c.i); }
+        }
+      };
+      const uint32_t q_base = smem_u32(sQ), kv_base = smem_u32(sKV);
+      const uint32_t idesc_o = fa_idesc_bmn(128, FA_DH);
       uint32_t tiles_done[2] = {0u, 0u};
-      auto issue_s = [&](int e) {
-        const int s = e & 1, t = e >> 1, i = t / NKB, j = t - i * NKB;
-        int crop, head, tile0;
-        item_of(i, crop, head, tile0);
-        const bool exists = tile0 + s < sh.nq;
-        const uint32_t g = (uint32_t)(i * NKB + j);
-        const int st = (int)(g % FA_KV_STAGES);
+      auto issue_s = [&](const Cursor &c) {
+        const bool exists = c.s == 0 || c.two;
         if (exists) {
-          if (j == 0) mbar_wait(&bar->q_full[i & 1], ((uint32_t)i >> 1) & 1u);
-          mbar_wait(&bar->kv_full[st], (g / FA_KV_STAGES) & 1u);
+          if (c.j == 0) mbar_wait(&bar->q_full[c.i & 1], ((uint32_t)c.i >> 1) & 1u);
+          mbar_wait(&bar->kv_full[c.st], c.kph);
           tc_fence_after();
-          const uint32_t idesc = umma_idesc_bf16(128, keys_of(j));
-          const uint64_t dq = umma_desc_k_sw128(smem_u32(sQ + ((i & 1) * 2 + s) * FA_TILE_BYTES));
-          const uint64_t dk = umma_desc_k_sw128(smem_u32(sKV + st * 2 * FA_TILE_BYTES));
-          const uint32_t d = tmem_base + (uint32_t)(e % FA_SBUF) * FA_SCOLS;
+          const uint32_t idesc = umma_idesc_bf16(128, keys_of(c.j));
+          const uint64_t dq = umma_desc_k_sw128(q_base + (uint32_t)((c.i & 1) * 2 + c.s) * FA_TILE_BYTES);
+          const uint64_t dk = umma_desc_k_sw128(kv_base + (uint32_t)c.st * 2 * FA_TILE_BYTES);
+          const uint32_t d = tmem_base + (uint32_t)c.buf * FA_SCOLS;
 #pragma unroll
           for (int k = 0; k < FA_DH / 16; ++k)
             umma_bf16(d, dq + (uint64_t)(k * 2), dk + (uint64_t)(k * 2), idesc, (uint32_t)(k != 0));
         }
-        umma_commit(&bar->s_full[e % FA_SBUF]);
-        if (j == NKB - 1 && s == 1) umma_commit(&bar->q_empty[i & 1]);         // every S MMA of the item is issued
+        umma_commit(&bar->s_full[c.buf]);
+        if (c.j == NKB - 1 && c.s == 1) umma_commit(&bar->q_empty[c.i & 1]);   // every S MMA of the item is issued
       };
-      auto issue_pv = [&](int e) {
-        const int s = e & 1, t = e >> 1, i = t / NKB, j = t - i * NKB;
-        int crop, head, tile0;
-        item_of(i, crop, head, tile0);
-        const bool exists = tile0 + s < sh.nq;
-        const uint32_t g = (uint32_t)(i * NKB + j);
-        const int st = (int)(g % FA_KV_STAGES);
-        mbar_wait(&bar->p_full[e % FA_SBUF], ((uint32_t)e / FA_SBUF) & 1u);
+      auto issue_pv = [&](const Cursor &c) {
+        const bool exists = c.s == 0 || c.two;
+        mbar_wait(&bar->p_full[c.buf], c.bph);
         if (exists) {
-          if (j == 0) {                                                        // O of the slot's previous tile drained
-            mbar_wait(&bar->o_free[s], (tiles_done[s] & 1u) ^ 1u);
-            ++tiles_done[s];
+          if (c.j == 0) {                                                      // O of the slot's previous tile drained
+            mbar_wait(&bar->o_free[c.s], (tiles_done[c.s] & 1u) ^ 1u);
+            ++tiles_done[c.s];
           }
           tc_fence_after();
-          const uint32_t idesc = fa_idesc_bmn(128, FA_DH);
-          uint64_t dv = fa_desc_mn_sw128(smem_u32(sKV + st * 2 * FA_TILE_BYTES + FA_TILE_BYTES));
-          uint32_t pc = tmem_base + (uint32_t)(e % FA_SBUF) * FA_SCOLS;
-          const uint32_t o = tmem_base + FA_OCOL + (uint32_t)s * FA_DH;
-          const int nch = keys_of(j) >> 4;
+          uint64_t dv = fa_desc_mn_sw128(kv_base + (uint32_t)c.st * 2 * FA_TILE_BYTES + FA_TILE_BYTES);
+          uint32_t pc = tmem_base + (uint32_t)c.buf * FA_SCOLS;
+          const uint32_t o = tmem_base + FA_OCOL + (uint32_t)c.s * FA_DH;
+          const int nch = keys_of(c.j) >> 4;
           for (int k = 0; k < nch; ++k, pc += 8, dv += 128)                    // +16 keys = +2048 B = +128 in (addr >> 4)
-            umma_bf16_ts(o, pc, dv, idesc, (uint32_t)((j | k) != 0));
-          umma_commit(&bar->o_done[s]);
+            umma_bf16_ts(o, pc, dv, idesc_o, (uint32_t)((c.j | k) != 0));
+          umma_commit(&bar->o_done[c.s]);
         }
-        if (s == 1) umma_commit(&bar->kv_empty[st]);                           // both slots have consumed the block
+        if (c.s == 1) umma_commit(&bar->kv_empty[c.st]);                       // both slots have consumed the block
       };
-      for (int e = 0; e < E && e < FA_SBUF; ++e) issue_s(e);
+      Cursor cs = {0, 0, 0, 0, 0u, 0, 0u, has_two(0)}, cp = cs;
+      int es = 0;                                                              // entries the S stream has issued
+      for (; es < E && es < FA_SBUF; ++es) { issue_s(cs); advance(cs); }
       for (int e = 0; e < E; ++e) {
-        issue_pv(e);
-        if (e + FA_SBUF < E) issue_s(e + FA_SBUF);                             // its buffer is free: P V(e) is in order before it
+        issue_pv(cp);
+        advance(cp);
+        if (es < E) { issue_s(cs); advance(cs); ++es; }                        // its buffer is free: P V(e) is in order before it
       }
     }
   }
