@@ -15,13 +15,13 @@
 // max and the exp (<= 64 per thread: the keys are cut into blocks of <= 128 and two threads share a row), with an
 // online softmax across the blocks -- which is also what makes the kernel independent of the sequence length.
 //
-// One persistent CTA per SM, 20 warps.  A work item is a (crop, head, PAIR of 128-row query tiles): the pair shares
+// One persistent CTA per SM, 18 warps.  A work item is a (crop, head, PAIR of 128-row query tiles): the pair shares
 // every K / V block (loaded once).  Slot s in {0, 1} = query tile 2 pair + s, owned by softmax group s.
 //   warp 0      TMA producer: Q tiles (2-stage ring over items), K / V blocks (4-stage ring)
 //   warp 1      MMA issuer.  Score MMAs run up to THREE block-entries ahead of the softmax: tensor memory holds
 //               three 128-column score buffers that rotate over the entries (item, block, slot) in issue order,
 //               plus one 64-column O accumulator per slot = 512 columns.  S(e + 3) is issued right after P V(e).
-//   warps 4-11  softmax group 0, warps 12-19 group 1: 4 TMEM lane quarters x 2 key halves.  Per block a thread
+//   warps 2-9   softmax group 0, warps 10-17 group 1: 4 TMEM lane quarters x 2 key halves.  Per block a thread
 //               loads its <= 64 scores (tcgen05.ld x16), takes the maximum (FMNMX3), exchanges it with the thread
 //               that holds the other half of the row (shared memory + a 64-thread named barrier), exponentiates
 //               (FFMA2 + MUFU.EX2), accumulates the row sum and writes P as packed bf16 back INTO the score buffer
@@ -41,7 +41,7 @@ using namespace sm100;
 namespace {
 
 constexpr int FA_DH = 64;
-constexpr int FA_THREADS = 20 * 32;
+constexpr int FA_THREADS = 18 * 32;                 // TMA, MMA + 2 groups x 8 softmax warps: 65536 / 576 = 112 registers per thread
 constexpr int FA_TILE_BYTES = 128 * FA_DH * 2;      // one 128-row operand tile: 16 KB
 constexpr int FA_Q_STAGES = 2;
 constexpr int FA_KV_STAGES = 4;
@@ -49,7 +49,6 @@ constexpr int FA_SBUF = 3;                          // rotating score buffers
 constexpr int FA_SCOLS = 128;                       // TMEM columns per score buffer
 constexpr int FA_OCOL = FA_SBUF * FA_SCOLS;         // O accumulators: [384, 448) and [448, 512)
 constexpr float FA_RESCALE_THR = 8.0f;              // log2 units
-constexpr int FA_REGS_CTRL = 32, FA_REGS_SOFTMAX = 112;   // setmaxnreg targets (the kernel is compiled for 96 = 65536 / 640)
 
 struct FaShared {
   uint64_t q_full[FA_Q_STAGES], q_empty[FA_Q_STAGES];
@@ -99,6 +98,41 @@ struct FaShape {
   int nq, npair;      // 128-row query tiles per (crop, head); pairs of them
 };
 
+// Drain of one finished tile by one softmax warp: O (this thread: 32 of the 64 head-dim columns of its row) / row sum
+// -> bf16 -> global, and the warp's arrival on o_free.  Every warp of the group arrives once per tile, in the tile's
+// own phase: a warp that has no rows in the tile runs ahead of the others, so it first waits until the previous
+// tile's phase has completed (the MMA warp is waiting for the same phase before the slot's next first P V).
+__device__ __forceinline__ void fa_drain(FaShared *bar, int g, int lane, bool live, uint32_t ntile, uint32_t phase,
+                                         uint32_t o_addr, float inv, __nv_bfloat16 *dst_row) {
+  if (!live) {
+    if (ntile > 1u) mbar_wait(&bar->o_free[g], (ntile - 2u) & 1u);
+    __syncwarp();
+    if (lane == 0) mbar_arrive(&bar->o_free[g]);
+    return;
+  }
+  mbar_wait(&bar->o_done[g], phase);               // the tile's last P V has retired
+  tc_fence_after();
+  uint32_t o[32];                                  // two x16 loads: the x32 shape runs at a quarter of the x16 rate
+  tmem_ld_32x16(o_addr, *reinterpret_cast<uint32_t(*)[16]>(&o[0]));
+  tmem_ld_32x16(o_addr + 16, *reinterpret_cast<uint32_t(*)[16]>(&o[16]));
+  tmem_ld_wait();
+  tc_fence_before();
+  __syncwarp();
+  if (lane == 0) mbar_arrive(&bar->o_free[g]);     // the accumulator may be overwritten by the slot's next tile
+  if (dst_row) {
+    uint4 *dst = reinterpret_cast<uint4 *>(dst_row);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      uint4 u;
+      u.x = fa_pack_bf16x2(__uint_as_float(o[8 * k + 0]) * inv, __uint_as_float(o[8 * k + 1]) * inv);
+      u.y = fa_pack_bf16x2(__uint_as_float(o[8 * k + 2]) * inv, __uint_as_float(o[8 * k + 3]) * inv);
+      u.z = fa_pack_bf16x2(__uint_as_float(o[8 * k + 4]) * inv, __uint_as_float(o[8 * k + 5]) * inv);
+      u.w = fa_pack_bf16x2(__uint_as_float(o[8 * k + 6]) * inv, __uint_as_float(o[8 * k + 7]) * inv);
+      dst[k] = u;
+    }
+  }
+}
+
 __global__ void __launch_bounds__(FA_THREADS, 1)
 attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV0,
                     const __grid_constant__ CUtensorMap tmKV1, __nv_bfloat16 *__restrict__ out, int n_items,
@@ -119,14 +153,14 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     prefetch_tmap(&tmKV0);
     prefetch_tmap(&tmKV1);
   }
-  if (warp == 1 && lane == 0) {
+  if (warp == 0 && lane == 0) {
     for (int i = 0; i < FA_Q_STAGES; ++i) { mbar_init(&bar->q_full[i], 1); mbar_init(&bar->q_empty[i], 1); }
     for (int i = 0; i < FA_KV_STAGES; ++i) { mbar_init(&bar->kv_full[i], 1); mbar_init(&bar->kv_empty[i], 1); }
     for (int i = 0; i < FA_SBUF; ++i) { mbar_init(&bar->s_full[i], 1); mbar_init(&bar->p_full[i], 8); }   // 8 warps of a group
     for (int i = 0; i < 2; ++i) { mbar_init(&bar->o_done[i], 1); mbar_init(&bar->o_free[i], 8); }
     fence_barrier_init();
   }
-  if (warp == 2) {
+  if (warp == 1) {                                               // (the whole warp; one lane of it issues the MMAs later)
     tmem_alloc(&bar->tmem_slot, 512);
     tmem_relinquish();
   }
@@ -145,13 +179,6 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   };
   auto keys_of = [&](int j) { return j == NKB - 1 ? sh.blk_last : sh.blk0; };
 
-  // Register re-allocation by warpgroup: the control warps give registers back, the softmax warps (64 scores held
-  // between the max and the exp) take them.  setmaxnreg.inc can only draw on what the CTA's OWN warps released
-  // (USETMAXREG.TRY_ALLOC.CTAPOOL spins otherwise -- a first version with 40 / 112 hung there): the CTA starts with
-  // 640 x 96 registers, 128 x (96 - 32) = 8192 are released and 512 x (112 - 96) = 8192 are taken.
-  static_assert(128 * (96 - FA_REGS_CTRL) >= 512 * (FA_REGS_SOFTMAX - 96), "setmaxnreg: the control warps must release what the softmax warps take");
-  if (warp < 4) {
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(FA_REGS_CTRL));
   if (warp == 0) {
     // ===================== TMA producer =====================
     if (elect_one()) {
@@ -242,9 +269,13 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           uint64_t dv = fa_desc_mn_sw128(kv_base + (uint32_t)c.st * 2 * FA_TILE_BYTES + FA_TILE_BYTES);
           uint32_t pc = tmem_base + (uint32_t)c.buf * FA_SCOLS;
           const uint32_t o = tmem_base + FA_OCOL + (uint32_t)c.s * FA_DH;
-          const int nch = keys_of(c.j) >> 4;
-          for (int k = 0; k < nch; ++k, pc += 8, dv += 128)                    // +16 keys = +2048 B = +128 in (addr >> 4)
+          const int nch = keys_of(c.j) >> 4, hc = (nch + 1) >> 1;
+          // P chunk k (16 keys = 8 packed columns) sits at the head of the score columns of the half that wrote it:
+          // column 8 k for the first hc chunks, 16 hc + 8 (k - hc) for the rest
+          for (int k = 0; k < nch; ++k, dv += 128) {                           // +16 keys = +2048 B = +128 in (addr >> 4)
             umma_bf16_ts(o, pc, dv, idesc_o, (uint32_t)((c.j | k) != 0));
+            pc += (k + 1 == hc) ? (uint32_t)(8 * hc + 8) : 8u;
+          }
           umma_commit(&bar->o_done[c.s]);
         }
         if (c.s == 1) umma_commit(&bar->kv_empty[c.st]);                       // both slots have consumed the block
@@ -258,13 +289,12 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         if (es < E) { issue_s(cs); advance(cs); ++es; }                        // its buffer is free: P V(e) is in order before it
       }
     }
-  }
   } else {
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(FA_REGS_SOFTMAX));
     // ===================== softmax groups =====================
-    const int g = (warp - 4) >> 3;                   // group = slot
-    const int h = ((warp - 4) >> 2) & 1;             // key half of the block
-    const int q = warp & 3;                          // TMEM lane quarter (rows 32 q .. 32 q + 31 of the tile)
+    const int g = (warp - 2) >> 3;                   // group = slot
+    const int h = ((warp - 2) >> 2) & 1;             // key half of the block
+    const int q = warp & 3;                          // TMEM lane quarter a warp may access = warp id % 4; the four warps
+                                                     // of a (group, half) are consecutive, so they cover all quarters
     const int trow = q * 32 + lane;
     const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
     const uint32_t o_addr = lane_addr + FA_OCOL + (uint32_t)g * FA_DH + (uint32_t)h * 32;
@@ -272,6 +302,13 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
     const int bar_id = 1 + g * 4 + q;                // 64-thread named barrier of the two warps that share these rows
     uint32_t nblk = 0;                               // blocks of existing tiles this slot has seen (o_done phases, xmax parity)
     uint32_t ntile = 0;                              // existing tiles this slot has seen (o_free phases)
+    // The drain of a finished tile (wait for its last P V, O -> registers -> bf16 -> global) is DEFERRED into the
+    // first block of the slot's next tile: by then the MMA has long retired, so the group never sits out the
+    // MMA-issue + tensor-pipe round trip at the end of a tile.
+    bool pend = false, pend_live = false;            // a tile of this slot waits to be drained / this warp has rows in it
+    float pend_inv = 0.f;
+    uint32_t pend_phase = 0;                         // o_done phase of its last block
+    __nv_bfloat16 *pend_dst = nullptr;               // this thread's output row (null: the row is past T)
     for (int i = 0; i < my_items; ++i) {
       int crop, head, tile0;
       item_of(i, crop, head, tile0);
@@ -283,45 +320,46 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         const int e = (i * NKB + j) * 2 + g;
         const uint32_t sbuf = lane_addr + (uint32_t)(e % FA_SBUF) * FA_SCOLS;
         mbar_wait(&bar->s_full[e % FA_SBUF], ((uint32_t)e / FA_SBUF) & 1u);
-        if (!live) {
-          __syncwarp();
-          if (lane == 0) mbar_arrive(&bar->p_full[e % FA_SBUF]);
-          if (exists) ++nblk;
-          continue;
-        }
+        if (live) {
         tc_fence_after();
         const int nch = keys_of(j) >> 4;                                       // 16-key chunks of the block
         const int c0 = h ? (nch + 1) >> 1 : 0, c1 = h ? nch : (nch + 1) >> 1;  // this thread's chunks (<= 4)
-        const int key0 = j * sh.blk0 + 16 * c0;
-        // ---- one read of the scores
-        uint32_t r[4][16];
-#pragma unroll
-        for (int c = 0; c < 4; ++c)
-          if (c0 + c < c1) tmem_ld_32x16(sbuf + 16 * (c0 + c), r[c]);
-        tmem_ld_wait();
+        const int key0 = j * sh.blk0;
+        const int pbase = 16 * c0;                   // P of this half goes to the head of ITS OWN score columns: the other
+                                                     // half still reads its scores (second pass) while this one stores
+        // ---- pass 1: row maximum over this thread's chunks (tensor memory is read twice: 400 B/clock/SM make the
+        // second read cheaper than the 64 registers -- spills, setmaxnreg -- a single read costs)
         float mx = -INFINITY;
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          if (c0 + c < c1) {
-            if (key0 + 16 * c + 16 > T) {                                      // keys >= T are padding: -inf
+        {
+          uint32_t r[2][16];
+          auto reduce = [&](const uint32_t(&v)[16], int c) {
+            if (key0 + 16 * c + 16 > T) {                                      // keys >= T are padding
 #pragma unroll
               for (int k = 0; k < 16; ++k)
-                if (key0 + 16 * c + k >= T) r[c][k] = 0xff800000u;
-            }
+                if (key0 + 16 * c + k < T) mx = fmaxf(mx, __uint_as_float(v[k]));
+            } else {
 #pragma unroll
-            for (int k = 0; k < 16; k += 2) mx = fa_max3(mx, __uint_as_float(r[c][k]), __uint_as_float(r[c][k + 1]));
+              for (int k = 0; k < 16; k += 2) mx = fa_max3(mx, __uint_as_float(v[k]), __uint_as_float(v[k + 1]));
+            }
+          };
+#pragma unroll 1
+          for (int c = c0; c < c1; c += 2) {         // two chunks per trip, both loads in flight before one wait
+            const bool two = c + 1 < c1;
+            tmem_ld_32x16(sbuf + 16 * c, r[0]);
+            if (two) tmem_ld_32x16(sbuf + 16 * c + 16, r[1]);
+            tmem_ld_wait();
+            reduce(r[0], c);
+            if (two) reduce(r[1], c + 1);
           }
         }
         // ---- row maximum of the block: exchange with the thread holding the other key half
-        float *xm = &bar->xmax[g][nblk & 1u][h][trow];
-        *xm = mx;
+        bar->xmax[g][nblk & 1u][h][trow] = mx;
         asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
         mx = fmaxf(mx, bar->xmax[g][nblk & 1u][h ^ 1][trow]);
         // ---- online softmax: raise the running maximum only when the block exceeds it by more than 2^THR
         if (j == 0) {
           m_used = mx;
         } else {
-          mbar_wait(&bar->o_done[g], (nblk - 1u) & 1u);                        // P V of the previous block has retired
           const bool need = (mx - m_used) * scale_log2e > FA_RESCALE_THR;
           if (__any_sync(0xffffffffu, need)) {
             float f = 1.f;
@@ -330,35 +368,57 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
               m_used = mx;
               l *= f;
             }
+            mbar_wait(&bar->o_done[g], (nblk - 1u) & 1u);                      // P V of the previous block has retired
             tc_fence_after();
-#pragma unroll 1
-            for (int part = 0; part < 4; ++part) {                             // 8 columns at a time: 64 scores are live
-              uint32_t o[8];
-              fa_tmem_ld_32x8(o_addr + 8 * part, o);
+#pragma unroll
+            for (int part = 0; part < 2; ++part) {
+              uint32_t o[16];
+              tmem_ld_32x16(o_addr + 16 * part, o);
               tmem_ld_wait();
 #pragma unroll
-              for (int k = 0; k < 8; ++k) o[k] = __float_as_uint(__uint_as_float(o[k]) * f);
-              tmem_st_32x8(o_addr + 8 * part, o);
+              for (int k = 0; k < 16; ++k) o[k] = __float_as_uint(__uint_as_float(o[k]) * f);
+              tmem_st_32x8(o_addr + 16 * part, *reinterpret_cast<uint32_t(*)[8]>(&o[0]));
+              tmem_st_32x8(o_addr + 16 * part + 8, *reinterpret_cast<uint32_t(*)[8]>(&o[8]));
             }
           }
         }
-        // ---- p = exp2((s - m) * scale); row sum; P -> tensor memory as packed bf16 (chunk k at column 8 k)
+        // ---- pass 2: p = exp2((s - m) * scale); row sum; P -> tensor memory as packed bf16, chunk c0 + i at column
+        // 16 c0 + 8 i: inside this thread's own score columns and never ahead of what it has already loaded.
         const float mneg = -m_used * scale_log2e;
         const uint64_t mn2 = pk2(mneg, mneg);
         uint64_t sum2 = pk2(0.f, 0.f);
-#pragma unroll
-        for (int c = 0; c < 4; ++c) {
-          if (c0 + c < c1) {
-            uint32_t w[8];
+        {
+          uint32_t r[2][16];
+          auto expo = [&](const uint32_t(&v)[16], int c) {
+            float p[16];
 #pragma unroll
             for (int k = 0; k < 16; k += 2) {
               float x0, x1;
-              unpk2(fma2(pk2(__uint_as_float(r[c][k]), __uint_as_float(r[c][k + 1])), sc2, mn2), x0, x1);
-              const float p0 = fa_ex2(x0), p1 = fa_ex2(x1);
-              sum2 = add2(sum2, pk2(p0, p1));
-              w[k >> 1] = fa_pack_bf16x2(p0, p1);
+              unpk2(fma2(pk2(__uint_as_float(v[k]), __uint_as_float(v[k + 1])), sc2, mn2), x0, x1);
+              p[k] = fa_ex2(x0);
+              p[k + 1] = fa_ex2(x1);
             }
-            tmem_st_32x8(sbuf + 8 * (c0 + c), w);
+            if (key0 + 16 * c + 16 > T) {
+#pragma unroll
+              for (int k = 0; k < 16; ++k)
+                if (key0 + 16 * c + k >= T) p[k] = 0.f;
+            }
+            uint32_t w[8];
+#pragma unroll
+            for (int k = 0; k < 16; k += 2) {
+              sum2 = add2(sum2, pk2(p[k], p[k + 1]));
+              w[k >> 1] = fa_pack_bf16x2(p[k], p[k + 1]);
+            }
+            tmem_st_32x8(sbuf + pbase + 8 * (c - c0), w);
+          };
+#pragma unroll 1
+          for (int c = c0; c < c1; c += 2) {
+            const bool two = c + 1 < c1;
+            tmem_ld_32x16(sbuf + 16 * c, r[0]);
+            if (two) tmem_ld_32x16(sbuf + 16 * c + 16, r[1]);
+            tmem_ld_wait();
+            expo(r[0], c);
+            if (two) expo(r[1], c + 1);
           }
         }
         {
@@ -366,55 +426,41 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           unpk2(sum2, s0, s1);
           l += s0 + s1;
         }
-        tmem_st_wait();
-        tc_fence_before();                           // P (and a rescaled O) are in tensor memory before the MMA reads them
+        }  // live
+        // the slot's previous tile is drained here, in the first block of the next one (its last P V retired long
+        // ago), and before this block's arrival: the MMA warp waits for o_free right after p_full
+        if (j == 0 && pend && exists) {
+          fa_drain(bar, g, lane, pend_live, ntile, pend_phase, o_addr, pend_inv, pend_dst);
+          pend = false;
+        }
+        if (live) {
+          tmem_st_wait();
+          tc_fence_before();                         // P (and a rescaled O) are in tensor memory before the MMA reads them
+        }
         __syncwarp();
         if (lane == 0) mbar_arrive(&bar->p_full[e % FA_SBUF]);
-        ++nblk;
+        if (exists) ++nblk;
       }
       if (!exists) continue;
       ++ntile;
-      if (!live) {
-        // Nothing to drain, but this warp's arrival must land in THIS tile's phase of o_free: a warp that only
-        // passes barriers on runs ahead of the warps that are still draining the slot's previous tile, so it waits
-        // until that tile's phase has completed (the MMA warp is waiting for the same phase before its first P V).
-        if (ntile > 1u) mbar_wait(&bar->o_free[g], (ntile - 2u) & 1u);
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&bar->o_free[g]);
-        continue;
-      }
-      // ---- O / row sum -> bf16 -> global (this thread: 32 of the 64 head-dim columns of its row)
-      bar->xsum[g][h][trow] = l;
-      asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
-      const float inv = 1.0f / (l + bar->xsum[g][h ^ 1][trow]);
-      mbar_wait(&bar->o_done[g], (nblk - 1u) & 1u);
-      tc_fence_after();
-      uint32_t o[32];                                // two x16 loads: the x32 shape runs at a quarter of the x16 rate
-      tmem_ld_32x16(o_addr, *reinterpret_cast<uint32_t(*)[16]>(&o[0]));
-      tmem_ld_32x16(o_addr + 16, *reinterpret_cast<uint32_t(*)[16]>(&o[16]));
-      tmem_ld_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&bar->o_free[g]);   // the accumulator may be overwritten by the slot's next tile
-      const int tok = tile * 128 + trow;
-      if (tok < T) {
-        uint4 *dst = reinterpret_cast<uint4 *>(out + ((size_t)crop * T + tok) * D + (size_t)head * FA_DH + h * 32);
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          uint4 u;
-          u.x = fa_pack_bf16x2(__uint_as_float(o[8 * k + 0]) * inv, __uint_as_float(o[8 * k + 1]) * inv);
-          u.y = fa_pack_bf16x2(__uint_as_float(o[8 * k + 2]) * inv, __uint_as_float(o[8 * k + 3]) * inv);
-          u.z = fa_pack_bf16x2(__uint_as_float(o[8 * k + 4]) * inv, __uint_as_float(o[8 * k + 5]) * inv);
-          u.w = fa_pack_bf16x2(__uint_as_float(o[8 * k + 6]) * inv, __uint_as_float(o[8 * k + 7]) * inv);
-          dst[k] = u;
-        }
+      pend = true;
+      pend_live = live;
+      if (live) {
+        // row sum of the tile: exchange the two halves now (cheap), drain later
+        bar->xsum[g][h][trow] = l;
+        asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
+        pend_inv = 1.0f / (l + bar->xsum[g][h ^ 1][trow]);
+        pend_phase = (nblk - 1u) & 1u;
+        const int tok = tile * 128 + trow;
+        pend_dst = tok < T ? out + ((size_t)crop * T + tok) * D + (size_t)head * FA_DH + h * 32 : nullptr;
       }
     }
+    if (pend) fa_drain(bar, g, lane, pend_live, ntile, pend_phase, o_addr, pend_inv, pend_dst);
   }
 
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) tmem_dealloc(tmem_base, 512);
+  if (warp == 1) tmem_dealloc(tmem_base, 512);
 }
 
 }  // namespace
