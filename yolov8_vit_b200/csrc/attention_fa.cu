@@ -4,32 +4,35 @@
 // qkv [n, T, 3, heads, 64] -> per head softmax(q k^T * 64^-0.5) v.  One kernel serves ViT-B/16 (T = 197: two key
 // blocks of 112 + 96) and the reference-literal ViT-B/8 (T = 785: six key blocks of 128 + one of 32).
 //
-// Flash-style, single read of the scores.  What bounds a softmax on this machine is the MUFU pipe: 16 ex2 per clock
-// per SM (measured, tools/ubench_tmem.cu), i.e. 1664 clocks for the 26 624 exponentials of a 128 x 208 tile, against
-// ~530 clocks to read its fp32 scores twice from tensor memory (tcgen05.ld.32x32b.x16: 400 B/clock/SM with 16
-// warps, 210 with 4; the .x32 shape only reaches 115) and ~830 clocks of tensor pipe.  The round-1 kernel ran at
-// 3.7 k clocks per tile because all 16 softmax warps worked on ONE tile in lock step (max pass, barrier, exp
-// pass: the MUFU pipe idles during the first half and nothing hides the dependent chain).  Here TWO query tiles are
-// in flight per SM, each owned by its own group of 8 warps, so one tile's MUFU-bound exp pass overlaps the other's
-// load / max / exchange / store; every score is read from tensor memory once and held in registers between the
-// max and the exp (<= 64 per thread: the keys are cut into blocks of <= 128 and two threads share a row), with an
-// online softmax across the blocks -- which is also what makes the kernel independent of the sequence length.
+// Flash-style: the keys are cut into blocks of <= 128 with an online softmax across the blocks, which makes the
+// kernel independent of the sequence length.  What bounds a softmax on this machine is the MUFU pipe: 16 ex2 per
+// clock per SM (measured, tools/ubench_tmem.cu, profiles/r02_ubench_tmem.md), i.e. 1664 clocks for the 26 624
+// exponentials of a 128 x 208 tile, against ~530 clocks to read its fp32 scores TWICE from tensor memory
+// (tcgen05.ld.32x32b.x16: 400 B/clock/SM; the .x32 shape only reaches 115) and ~830 clocks of tensor pipe.  The
+// round-1 kernel ran at 3.7 k clocks per tile because all 16 softmax warps worked on ONE tile in lock step (max
+// pass, barrier, exp pass: the MUFU pipe idles during the first half and nothing hides the dependent chain).  Here
+// TWO query tiles are in flight per SM, each owned by its own group of 8 warps, so one tile's MUFU-bound exp pass
+// overlaps the other's load / max / exchange / store.  The scores are read twice (max pass, exp pass): holding 64
+// of them per thread between the passes was tried first and cost more (96-register cap at 640 threads: spills,
+// S2R re-reads, setmaxnreg juggling) than the second read.
 //
-// One persistent CTA per SM, 18 warps.  A work item is a (crop, head, PAIR of 128-row query tiles): the pair shares
+// One persistent CTA per SM, 20 warps.  A work item is a (crop, head, PAIR of 128-row query tiles): the pair shares
 // every K / V block (loaded once).  Slot s in {0, 1} = query tile 2 pair + s, owned by softmax group s.
 //   warp 0      TMA producer: Q tiles (2-stage ring over items), K / V blocks (4-stage ring)
-//   warp 1      MMA issuer.  Score MMAs run up to THREE block-entries ahead of the softmax: tensor memory holds
-//               three 128-column score buffers that rotate over the entries (item, block, slot) in issue order,
-//               plus one 64-column O accumulator per slot = 512 columns.  S(e + 3) is issued right after P V(e).
-//   warps 2-9   softmax group 0, warps 10-17 group 1: 4 TMEM lane quarters x 2 key halves.  Per block a thread
-//               loads its <= 64 scores (tcgen05.ld x16), takes the maximum (FMNMX3), exchanges it with the thread
-//               that holds the other half of the row (shared memory + a 64-thread named barrier), exponentiates
-//               (FFMA2 + MUFU.EX2), accumulates the row sum and writes P as packed bf16 back INTO the score buffer
-//               (the A operand of the P V MMA comes from tensor memory; P never touches shared memory).
+//   warp 1      score-MMA issuer: S = Q K^T of entry e = (item, block, slot) into score buffer e % 3.  Tensor memory
+//               holds three 128-column score buffers that rotate over the entries in issue order, plus one 64-column
+//               O accumulator per slot = 512 columns, so S runs up to three entries ahead of the softmax.
+//   warps 2, 3  P V issuers, one per slot: O_s (+)= P V once the group has written P (A operand from tensor memory).
+//   warps 4-11  softmax group 0, warps 12-19 group 1: 4 TMEM lane quarters x 2 key halves.  Per block a thread
+//               takes the maximum of its <= 64 scores (tcgen05.ld x16, FMNMX3), exchanges it with the thread that
+//               holds the other half of the row (shared memory + a 64-thread named barrier), reads the scores
+//               again, exponentiates (FFMA2 + MUFU.EX2), accumulates the row sum and writes P as packed bf16 back
+//               INTO the head of its own score columns (P never touches shared memory).
 //               Online softmax: the running maximum is only raised when a block exceeds it by more than 2^8
 //               (P then stays <= 256, exact in bf16 / fp32); raising it rescales O in tensor memory
-//               (tcgen05.ld / st, decided per warp, rare after the first block).  After the last block the group
-//               drains O, scales by 1 / sum and stores bf16.
+//               (tcgen05.ld / st, decided per warp, rare after the first block).  A finished tile is drained
+//               (O / row sum -> bf16 -> global) inside the first block of the slot's NEXT tile, when its last
+//               P V has long retired.
 // Warps whose 32 query rows are all past T (the tail tile) only pass the barriers on.
 #include "common.cuh"
 #include "gemm_sm100.cuh"
@@ -41,7 +44,7 @@ using namespace sm100;
 namespace {
 
 constexpr int FA_DH = 64;
-constexpr int FA_THREADS = 18 * 32;                 // TMA, MMA + 2 groups x 8 softmax warps: 65536 / 576 = 112 registers per thread
+constexpr int FA_THREADS = 20 * 32;                 // TMA, S issuer, 2 P V issuers + 2 groups x 8 softmax warps
 constexpr int FA_TILE_BYTES = 128 * FA_DH * 2;      // one 128-row operand tile: 16 KB
 constexpr int FA_Q_STAGES = 2;
 constexpr int FA_KV_STAGES = 4;
@@ -53,7 +56,7 @@ constexpr float FA_RESCALE_THR = 8.0f;              // log2 units
 struct FaShared {
   uint64_t q_full[FA_Q_STAGES], q_empty[FA_Q_STAGES];
   uint64_t kv_full[FA_KV_STAGES], kv_empty[FA_KV_STAGES];
-  uint64_t s_full[FA_SBUF], p_full[FA_SBUF];
+  uint64_t s_full[FA_SBUF], p_full[FA_SBUF], pv_done[FA_SBUF];
   uint64_t o_done[2], o_free[2];
   uint32_t tmem_slot, pad;
   float xmax[2][2][2][128];          // [group][block parity][key half][row]
@@ -155,8 +158,8 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   }
   if (warp == 0 && lane == 0) {
     for (int i = 0; i < FA_Q_STAGES; ++i) { mbar_init(&bar->q_full[i], 1); mbar_init(&bar->q_empty[i], 1); }
-    for (int i = 0; i < FA_KV_STAGES; ++i) { mbar_init(&bar->kv_full[i], 1); mbar_init(&bar->kv_empty[i], 1); }
-    for (int i = 0; i < FA_SBUF; ++i) { mbar_init(&bar->s_full[i], 1); mbar_init(&bar->p_full[i], 8); }   // 8 warps of a group
+    for (int i = 0; i < FA_KV_STAGES; ++i) { mbar_init(&bar->kv_full[i], 1); mbar_init(&bar->kv_empty[i], 2); }   // both P V issuers
+    for (int i = 0; i < FA_SBUF; ++i) { mbar_init(&bar->s_full[i], 1); mbar_init(&bar->p_full[i], 8); mbar_init(&bar->pv_done[i], 1); }   // p_full: 8 warps of a group
     for (int i = 0; i < 2; ++i) { mbar_init(&bar->o_done[i], 1); mbar_init(&bar->o_free[i], 8); }
     fence_barrier_init();
   }
@@ -205,94 +208,92 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    // Entries e = (item i, block j, slot s) in the order ((i * NKB + j) * 2 + s); entry e uses score buffer e % 3.
-    // Entries of a slot that does not exist are passed through (empty commits) so that every barrier sees one
-    // completion per entry and the phase of entry e is (e / 3) & 1 for both sides.
-    // This ONE thread is on the critical path of both softmax groups (P V(e) and S(e + 3) are issued between the
-    // arrival of P(e) and the moment a group needs its next scores), so its bookkeeping is incremental: two
-    // cursors walk the entry sequence (one for the S stream, three entries ahead, one for the P V stream) with
-    // adds and compares only -- a first version that decoded (i, j, s), the ring stages and the buffer from e with
-    // divisions in every call spent ~4 k clocks per entry and made the kernel slower than the one it replaces.
+    // ===================== score-MMA issuer =====================
+    // Entries e = (item i, block j, slot s) in the order ((i * NKB + j) * 2 + s); entry e uses score buffer e % 3, so
+    // S runs up to three entries ahead of the softmax.  Entries of a slot that does not exist are passed through
+    // (empty commits) so that every barrier sees one completion per entry and the phase of entry e is (e / 3) & 1
+    // on every side.  The MMA issue is split over THREE threads (this one for S = Q K^T, one per slot for P V):
+    // with one thread for everything the ~270 dependent instructions it needs per entry (mbarrier polls, uniform-
+    // register descriptor arithmetic, 11 UTCHMMA) took ~2.3 k clocks per entry, 9 k per (crop, head) -- three
+    // times the MUFU time of the softmax it feeds (ncu: the issuing warp never waited, the softmax warps did).
+    // tcgen05.mma from different threads is not ordered, so S(e) waits for the COMMIT of P V(e - 3) (pv_done),
+    // which read P from the buffer S(e) overwrites.
     if (elect_one()) {
-      struct Cursor {
-        int i, j, s;            // item, key block, slot
-        int buf;                // e % 3
-        uint32_t bph;           // (e / 3) & 1
-        int st;                 // K / V ring stage of (i, j)
-        uint32_t kph;           // its phase
-        bool two;               // the item has a second query tile
-      };
-      const int E = my_items * NKB * 2;
-      auto has_two = [&](int i) {
-        if (sh.npair == 1) return sh.nq >= 2;
-        const int item = (int)blockIdx.x + i * (int)gridDim.x;
-        return 2 * (item % sh.npair) + 1 < sh.nq;
-      };
-      auto advance = [&](Cursor &c) {
-        if (++c.buf == FA_SBUF) { c.buf = 0; c.bph ^= 1u; }
-        c.s ^= 1;
-        if (c.s == 0) {
-          if (++c.st == FA_KV_STAGES) { c.st = 0; c.kph ^= 1u; }
-          if (++c.j == NKB) { c.j = 0; ++c.i; c.two = has_two(c.i); }
-        }
-      };
       const uint32_t q_base = smem_u32(sQ), kv_base = smem_u32(sKV);
-      const uint32_t idesc_o = fa_idesc_bmn(128, FA_DH);
-      uint32_t tiles_done[2] = {0u, 0u};
-      auto issue_s = [&](const Cursor &c) {
-        const bool exists = c.s == 0 || c.two;
-        if (exists) {
-          if (c.j == 0) mbar_wait(&bar->q_full[c.i & 1], ((uint32_t)c.i >> 1) & 1u);
-          mbar_wait(&bar->kv_full[c.st], c.kph);
-          tc_fence_after();
-          const uint32_t idesc = umma_idesc_bf16(128, keys_of(c.j));
-          const uint64_t dq = umma_desc_k_sw128(q_base + (uint32_t)((c.i & 1) * 2 + c.s) * FA_TILE_BYTES);
-          const uint64_t dk = umma_desc_k_sw128(kv_base + (uint32_t)c.st * 2 * FA_TILE_BYTES);
-          const uint32_t d = tmem_base + (uint32_t)c.buf * FA_SCOLS;
+      int buf = 0, st = 0;
+      uint32_t bph = 0u, kph = 0u, e = 0u;
+      for (int i = 0; i < my_items; ++i) {
+        bool two = sh.nq >= 2;
+        if (sh.npair > 1) two = 2 * (((int)blockIdx.x + i * (int)gridDim.x) % sh.npair) + 1 < sh.nq;
+        const uint32_t q_addr = q_base + (uint32_t)((i & 1) * 2) * FA_TILE_BYTES;
+        for (int j = 0; j < NKB; ++j) {
+          const uint32_t idesc = umma_idesc_bf16(128, keys_of(j));
+          const uint64_t dk = umma_desc_k_sw128(kv_base + (uint32_t)st * 2 * FA_TILE_BYTES);
 #pragma unroll
-          for (int k = 0; k < FA_DH / 16; ++k)
-            umma_bf16(d, dq + (uint64_t)(k * 2), dk + (uint64_t)(k * 2), idesc, (uint32_t)(k != 0));
-        }
-        umma_commit(&bar->s_full[c.buf]);
-        if (c.j == NKB - 1 && c.s == 1) umma_commit(&bar->q_empty[c.i & 1]);   // every S MMA of the item is issued
-      };
-      auto issue_pv = [&](const Cursor &c) {
-        const bool exists = c.s == 0 || c.two;
-        mbar_wait(&bar->p_full[c.buf], c.bph);
-        if (exists) {
-          if (c.j == 0) {                                                      // O of the slot's previous tile drained
-            mbar_wait(&bar->o_free[c.s], (tiles_done[c.s] & 1u) ^ 1u);
-            ++tiles_done[c.s];
+          for (int sl = 0; sl < 2; ++sl) {
+            if (e >= (uint32_t)FA_SBUF) mbar_wait(&bar->pv_done[buf], bph ^ 1u);   // P V(e - 3) has read its P
+            if (sl == 0 || two) {
+              if (j == 0 && sl == 0) mbar_wait(&bar->q_full[i & 1], ((uint32_t)i >> 1) & 1u);
+              if (sl == 0) mbar_wait(&bar->kv_full[st], kph);
+              tc_fence_after();
+              const uint64_t dq = umma_desc_k_sw128(q_addr + (uint32_t)sl * FA_TILE_BYTES);
+              const uint32_t d = tmem_base + (uint32_t)buf * FA_SCOLS;
+#pragma unroll
+              for (int k = 0; k < FA_DH / 16; ++k)
+                umma_bf16(d, dq + (uint64_t)(k * 2), dk + (uint64_t)(k * 2), idesc, (uint32_t)(k != 0));
+            }
+            umma_commit(&bar->s_full[buf]);
+            if (j == NKB - 1 && sl == 1) umma_commit(&bar->q_empty[i & 1]);        // every S MMA of the item is issued
+            if (++buf == FA_SBUF) { buf = 0; bph ^= 1u; }
+            ++e;
           }
-          tc_fence_after();
-          uint64_t dv = fa_desc_mn_sw128(kv_base + (uint32_t)c.st * 2 * FA_TILE_BYTES + FA_TILE_BYTES);
-          uint32_t pc = tmem_base + (uint32_t)c.buf * FA_SCOLS;
-          const uint32_t o = tmem_base + FA_OCOL + (uint32_t)c.s * FA_DH;
-          const int nch = keys_of(c.j) >> 4, hc = (nch + 1) >> 1;
-          // P chunk k (16 keys = 8 packed columns) sits at the head of the score columns of the half that wrote it:
-          // column 8 k for the first hc chunks, 16 hc + 8 (k - hc) for the rest
-          for (int k = 0; k < nch; ++k, dv += 128) {                           // +16 keys = +2048 B = +128 in (addr >> 4)
-            umma_bf16_ts(o, pc, dv, idesc_o, (uint32_t)((c.j | k) != 0));
-            pc += (k + 1 == hc) ? (uint32_t)(8 * hc + 8) : 8u;
-          }
-          umma_commit(&bar->o_done[c.s]);
+          if (++st == FA_KV_STAGES) { st = 0; kph ^= 1u; }
         }
-        if (c.s == 1) umma_commit(&bar->kv_empty[c.st]);                       // both slots have consumed the block
-      };
-      Cursor cs = {0, 0, 0, 0, 0u, 0, 0u, has_two(0)}, cp = cs;
-      int es = 0;                                                              // entries the S stream has issued
-      for (; es < E && es < FA_SBUF; ++es) { issue_s(cs); advance(cs); }
-      for (int e = 0; e < E; ++e) {
-        issue_pv(cp);
-        advance(cp);
-        if (es < E) { issue_s(cs); advance(cs); ++es; }                        // its buffer is free: P V(e) is in order before it
+      }
+    }
+  } else if (warp < 4) {
+    // ===================== P V issuer of slot warp - 2 =====================
+    if (elect_one()) {
+      const int sl = warp - 2;
+      const uint32_t kv_base = smem_u32(sKV);
+      const uint32_t idesc_o = fa_idesc_bmn(128, FA_DH);
+      const uint32_t o = tmem_base + FA_OCOL + (uint32_t)sl * FA_DH;
+      int buf = sl, st = 0;                          // entry e = 2 * block + sl: buffer e % 3, phase (e / 3) & 1
+      uint32_t bph = 0u, tiles = 0u;
+      for (int i = 0; i < my_items; ++i) {
+        bool exists = sl == 0 || sh.nq >= 2;
+        if (sl == 1 && sh.npair > 1) exists = 2 * (((int)blockIdx.x + i * (int)gridDim.x) % sh.npair) + 1 < sh.nq;
+        for (int j = 0; j < NKB; ++j) {
+          mbar_wait(&bar->p_full[buf], bph);
+          if (exists) {
+            if (j == 0) {                            // O of the slot's previous tile has been drained
+              mbar_wait(&bar->o_free[sl], (tiles & 1u) ^ 1u);
+              ++tiles;
+            }
+            tc_fence_after();
+            uint64_t dv = fa_desc_mn_sw128(kv_base + (uint32_t)st * 2 * FA_TILE_BYTES + FA_TILE_BYTES);
+            uint32_t pc = tmem_base + (uint32_t)buf * FA_SCOLS;
+            const int nch = keys_of(j) >> 4, hc = (nch + 1) >> 1;
+            // P chunk k (16 keys = 8 packed columns) sits at the head of the score columns of the half that wrote it:
+            // column 8 k for the first hc chunks, 16 hc + 8 (k - hc) for the rest
+            for (int k = 0; k < nch; ++k, dv += 128) {                         // +16 keys = +2048 B = +128 in (addr >> 4)
+              umma_bf16_ts(o, pc, dv, idesc_o, (uint32_t)((j | k) != 0));
+              pc += (k + 1 == hc) ? (uint32_t)(8 * hc + 8) : 8u;
+            }
+            umma_commit(&bar->o_done[sl]);
+          }
+          umma_commit(&bar->pv_done[buf]);           // the score buffer may be overwritten by S(e + 3)
+          umma_commit(&bar->kv_empty[st]);           // (2 arrivals: both slots have consumed the block)
+          buf += 2;                                  // e += 2
+          if (buf >= FA_SBUF) { buf -= FA_SBUF; bph ^= 1u; }
+          if (++st == FA_KV_STAGES) st = 0;
+        }
       }
     }
   } else {
     // ===================== softmax groups =====================
-    const int g = (warp - 2) >> 3;                   // group = slot
-    const int h = ((warp - 2) >> 2) & 1;             // key half of the block
+    const int g = (warp - 4) >> 3;                   // group = slot
+    const int h = ((warp - 4) >> 2) & 1;             // key half of the block
     const int q = warp & 3;                          // TMEM lane quarter a warp may access = warp id % 4; the four warps
                                                      // of a (group, half) are consecutive, so they cover all quarters
     const int trow = q * 32 + lane;
@@ -357,29 +358,17 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
         mx = fmaxf(mx, bar->xmax[g][nblk & 1u][h ^ 1][trow]);
         // ---- online softmax: raise the running maximum only when the block exceeds it by more than 2^THR
+        float o_scale = 1.f;                         // factor the O accumulator (and the row sum) take when it is raised
+        bool rescale = false;                        // warp-uniform: some row of this warp raises its maximum
         if (j == 0) {
           m_used = mx;
         } else {
           const bool need = (mx - m_used) * scale_log2e > FA_RESCALE_THR;
-          if (__any_sync(0xffffffffu, need)) {
-            float f = 1.f;
-            if (need) {
-              f = fa_ex2((m_used - mx) * scale_log2e);
-              m_used = mx;
-              l *= f;
-            }
-            mbar_wait(&bar->o_done[g], (nblk - 1u) & 1u);                      // P V of the previous block has retired
-            tc_fence_after();
-#pragma unroll
-            for (int part = 0; part < 2; ++part) {
-              uint32_t o[16];
-              tmem_ld_32x16(o_addr + 16 * part, o);
-              tmem_ld_wait();
-#pragma unroll
-              for (int k = 0; k < 16; ++k) o[k] = __float_as_uint(__uint_as_float(o[k]) * f);
-              tmem_st_32x8(o_addr + 16 * part, *reinterpret_cast<uint32_t(*)[8]>(&o[0]));
-              tmem_st_32x8(o_addr + 16 * part + 8, *reinterpret_cast<uint32_t(*)[8]>(&o[8]));
-            }
+          rescale = __any_sync(0xffffffffu, need);
+          if (need) {
+            o_scale = fa_ex2((m_used - mx) * scale_log2e);
+            m_used = mx;
+            l *= o_scale;
           }
         }
         // ---- pass 2: p = exp2((s - m) * scale); row sum; P -> tensor memory as packed bf16, chunk c0 + i at column
@@ -426,6 +415,26 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           unpk2(sum2, s0, s1);
           l += s0 + s1;
         }
+          if (j > 0) {
+            // The P V of the slot's previous block has retired (it was issued a whole block ago).  EVERY commit on
+            // o_done is observed exactly once and in order -- here, or by the drain for a tile's last block: a
+            // parity wait is only exact while the waiter is at most one phase behind the barrier (a version that
+            // skipped this wait unless a rescale was due let a fast warp reach a tile's drain two phases early).
+            mbar_wait(&bar->o_done[g], (nblk - 1u) & 1u);
+            if (rescale) {                           // rare after the first block: O *= 2^(old max - new max), in place
+              tc_fence_after();
+#pragma unroll
+              for (int part = 0; part < 2; ++part) {
+                uint32_t o[16];
+                tmem_ld_32x16(o_addr + 16 * part, o);
+                tmem_ld_wait();
+#pragma unroll
+                for (int k = 0; k < 16; ++k) o[k] = __float_as_uint(__uint_as_float(o[k]) * o_scale);
+                tmem_st_32x8(o_addr + 16 * part, *reinterpret_cast<uint32_t(*)[8]>(&o[0]));
+                tmem_st_32x8(o_addr + 16 * part + 8, *reinterpret_cast<uint32_t(*)[8]>(&o[8]));
+              }
+            }
+          }
         }  // live
         // the slot's previous tile is drained here, in the first block of the next one (its last P V retired long
         // ago), and before this block's arrival: the MMA warp waits for o_free right after p_full
