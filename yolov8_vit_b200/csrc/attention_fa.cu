@@ -281,9 +281,16 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
               pc += (k + 1 == hc) ? (uint32_t)(8 * hc + 8) : 8u;
             }
             umma_commit(&bar->o_done[sl]);
+            umma_commit(&bar->pv_done[buf]);         // the score buffer may be overwritten by S(e + 3)
+            umma_commit(&bar->kv_empty[st]);         // (2 arrivals: both slots have consumed the block)
+          } else {
+            // a query tile that does not exist: plain arrivals.  (A tcgen05.commit from a thread that has not issued
+            // any MMA yet -- the last pair of an odd tile count on a CTA with one item -- never arrived.)  No
+            // reordering against this thread's earlier commits is possible: consecutive arrivals on either
+            // barrier are separated by a full S / softmax / TMA dependency chain.
+            mbar_arrive(&bar->pv_done[buf]);
+            mbar_arrive(&bar->kv_empty[st]);
           }
-          umma_commit(&bar->pv_done[buf]);           // the score buffer may be overwritten by S(e + 3)
-          umma_commit(&bar->kv_empty[st]);           // (2 arrivals: both slots have consumed the block)
           buf += 2;                                  // e += 2
           if (buf >= FA_SBUF) { buf -= FA_SBUF; bph ^= 1u; }
           if (++st == FA_KV_STAGES) st = 0;
