@@ -56,7 +56,8 @@ constexpr float FA_RESCALE_THR = 8.0f;              // log2 units
 struct FaShared {
   uint64_t q_full[FA_Q_STAGES], q_empty[FA_Q_STAGES];
   uint64_t kv_full[FA_KV_STAGES], kv_empty[FA_KV_STAGES];
-  uint64_t s_full[FA_SBUF], p_full[FA_SBUF], pv_done[FA_SBUF];
+  uint64_t s_full[FA_SBUF], pv_done[FA_SBUF];
+  uint64_t p_full[2][FA_SBUF];       // per slot: its waiter (the slot's P V issuer) sees EVERY phase of its barriers
   uint64_t o_done[2], o_free[2];
   uint32_t tmem_slot, pad;
   float xmax[2][2][2][128];          // [group][block parity][key half][row]
@@ -94,6 +95,24 @@ __device__ __forceinline__ void fa_tmem_ld_32x8(uint32_t taddr, uint32_t (&r)[8]
                : "memory");
 }
 
+// mbar_wait with a name: a protocol bug prints which wait of which warp starved before the launch is failed
+// (bounded spin, like sm100::mbar_wait -- a hang would cost a GPU box)
+__device__ int fa_timeout_reports = 0;
+__device__ __noinline__ void fa_wait_timeout(int tag, uint32_t parity) {
+  if (atomicAdd(&fa_timeout_reports, 1) < 48)
+    printf("attention_fa: wait %d (parity %u) timed out: cta %d warp %d lane %d\n", tag, parity, (int)blockIdx.x,
+         (int)(threadIdx.x >> 5), (int)(threadIdx.x & 31));
+}
+__device__ __forceinline__ void fa_wait(uint64_t *bar, uint32_t parity, int tag) {
+  uint32_t spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    ++spins;
+    if (spins == (1u << 20)) fa_wait_timeout(tag, parity);      // report, give the other starved waits time to report too
+    if (spins > (1u << 24)) __trap();
+  }
+}
+enum { W_Q_EMPTY = 1, W_KV_EMPTY, W_PV_DONE, W_Q_FULL, W_KV_FULL, W_P_FULL, W_O_FREE, W_S_FULL, W_O_DONE_BLK, W_O_DONE_DRAIN, W_O_FREE_DEAD };
+
 struct FaShape {
   int T, heads;
   int nkb;            // key blocks
@@ -108,12 +127,12 @@ struct FaShape {
 __device__ __forceinline__ void fa_drain(FaShared *bar, int g, int lane, bool live, uint32_t ntile, uint32_t phase,
                                          uint32_t o_addr, float inv, __nv_bfloat16 *dst_row) {
   if (!live) {
-    if (ntile > 1u) mbar_wait(&bar->o_free[g], (ntile - 2u) & 1u);
+    if (ntile > 1u) fa_wait(&bar->o_free[g], (ntile - 2u) & 1u, W_O_FREE_DEAD);
     __syncwarp();
     if (lane == 0) mbar_arrive(&bar->o_free[g]);
     return;
   }
-  mbar_wait(&bar->o_done[g], phase);               // the tile's last P V has retired
+  fa_wait(&bar->o_done[g], phase, W_O_DONE_DRAIN);               // the tile's last P V has retired
   tc_fence_after();
   uint32_t o[32];                                  // two x16 loads: the x32 shape runs at a quarter of the x16 rate
   tmem_ld_32x16(o_addr, *reinterpret_cast<uint32_t(*)[16]>(&o[0]));
@@ -159,7 +178,7 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   if (warp == 0 && lane == 0) {
     for (int i = 0; i < FA_Q_STAGES; ++i) { mbar_init(&bar->q_full[i], 1); mbar_init(&bar->q_empty[i], 1); }
     for (int i = 0; i < FA_KV_STAGES; ++i) { mbar_init(&bar->kv_full[i], 1); mbar_init(&bar->kv_empty[i], 2); }   // both P V issuers
-    for (int i = 0; i < FA_SBUF; ++i) { mbar_init(&bar->s_full[i], 1); mbar_init(&bar->p_full[i], 8); mbar_init(&bar->pv_done[i], 1); }   // p_full: 8 warps of a group
+    for (int i = 0; i < FA_SBUF; ++i) { mbar_init(&bar->s_full[i], 1); mbar_init(&bar->p_full[0][i], 8); mbar_init(&bar->p_full[1][i], 8); mbar_init(&bar->pv_done[i], 1); }   // p_full: 8 warps of a group
     for (int i = 0; i < 2; ++i) { mbar_init(&bar->o_done[i], 1); mbar_init(&bar->o_free[i], 8); }
     fence_barrier_init();
   }
@@ -191,14 +210,14 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         const int row0 = crop * T;
         const int qs = i & 1;
         const bool two = tile0 + 1 < sh.nq;
-        mbar_wait(&bar->q_empty[qs], (((uint32_t)i >> 1) & 1u) ^ 1u);          // S MMAs of item i - 2 retired
+        fa_wait(&bar->q_empty[qs], (((uint32_t)i >> 1) & 1u) ^ 1u, W_Q_EMPTY);          // S MMAs of item i - 2 retired
         mbar_arrive_expect_tx(&bar->q_full[qs], (two ? 2u : 1u) * FA_TILE_BYTES);
         tma_load_2d(sQ + (qs * 2 + 0) * FA_TILE_BYTES, &tmQ, &bar->q_full[qs], head * FA_DH, row0 + tile0 * 128);
         if (two) tma_load_2d(sQ + (qs * 2 + 1) * FA_TILE_BYTES, &tmQ, &bar->q_full[qs], head * FA_DH, row0 + (tile0 + 1) * 128);
         for (int j = 0; j < NKB; ++j) {
           const uint32_t g = (uint32_t)(i * NKB + j);
           const int st = (int)(g % FA_KV_STAGES);
-          mbar_wait(&bar->kv_empty[st], ((g / FA_KV_STAGES) & 1u) ^ 1u);       // P V MMAs of the stage's last user retired
+          fa_wait(&bar->kv_empty[st], ((g / FA_KV_STAGES) & 1u) ^ 1u, W_KV_EMPTY);       // P V MMAs of the stage's last user retired
           const CUtensorMap *tm = (j == NKB - 1) ? &tmKV1 : &tmKV0;
           mbar_arrive_expect_tx(&bar->kv_full[st], 2u * (uint32_t)keys_of(j) * FA_DH * 2u);
           uint8_t *sK = sKV + st * 2 * FA_TILE_BYTES;
@@ -231,10 +250,10 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           const uint64_t dk = umma_desc_k_sw128(kv_base + (uint32_t)st * 2 * FA_TILE_BYTES);
 #pragma unroll
           for (int sl = 0; sl < 2; ++sl) {
-            if (e >= (uint32_t)FA_SBUF) mbar_wait(&bar->pv_done[buf], bph ^ 1u);   // P V(e - 3) has read its P
+            if (e >= (uint32_t)FA_SBUF) fa_wait(&bar->pv_done[buf], bph ^ 1u, W_PV_DONE);   // P V(e - 3) has read its P
             if (sl == 0 || two) {
-              if (j == 0 && sl == 0) mbar_wait(&bar->q_full[i & 1], ((uint32_t)i >> 1) & 1u);
-              if (sl == 0) mbar_wait(&bar->kv_full[st], kph);
+              if (j == 0 && sl == 0) fa_wait(&bar->q_full[i & 1], ((uint32_t)i >> 1) & 1u, W_Q_FULL);
+              if (sl == 0) fa_wait(&bar->kv_full[st], kph, W_KV_FULL);
               tc_fence_after();
               const uint64_t dq = umma_desc_k_sw128(q_addr + (uint32_t)sl * FA_TILE_BYTES);
               const uint32_t d = tmem_base + (uint32_t)buf * FA_SCOLS;
@@ -258,16 +277,20 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       const uint32_t kv_base = smem_u32(sKV);
       const uint32_t idesc_o = fa_idesc_bmn(128, FA_DH);
       const uint32_t o = tmem_base + FA_OCOL + (uint32_t)sl * FA_DH;
-      int buf = sl, st = 0;                          // entry e = 2 * block + sl: buffer e % 3, phase (e / 3) & 1
+      // entry e = 2 * block + sl uses score buffer e % 3; the (slot, buffer) pair recurs every 3 blocks, so the phase
+      // of p_full[sl][buf] is (block / 3) & 1.  (One p_full per buffer shared by both slots was wrong: a parity wait
+      // is only exact if the waiter has seen the previous phase complete, and this thread would skip the other
+      // slot's phases -- it ran through a barrier whose previous phase was still open.)
+      int buf = sl, st = 0, k3 = 0;
       uint32_t bph = 0u, tiles = 0u;
       for (int i = 0; i < my_items; ++i) {
         bool exists = sl == 0 || sh.nq >= 2;
         if (sl == 1 && sh.npair > 1) exists = 2 * (((int)blockIdx.x + i * (int)gridDim.x) % sh.npair) + 1 < sh.nq;
         for (int j = 0; j < NKB; ++j) {
-          mbar_wait(&bar->p_full[buf], bph);
+          fa_wait(&bar->p_full[sl][buf], bph, W_P_FULL);
           if (exists) {
             if (j == 0) {                            // O of the slot's previous tile has been drained
-              mbar_wait(&bar->o_free[sl], (tiles & 1u) ^ 1u);
+              fa_wait(&bar->o_free[sl], (tiles & 1u) ^ 1u, W_O_FREE);
               ++tiles;
             }
             tc_fence_after();
@@ -292,7 +315,8 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
             mbar_arrive(&bar->kv_empty[st]);
           }
           buf += 2;                                  // e += 2
-          if (buf >= FA_SBUF) { buf -= FA_SBUF; bph ^= 1u; }
+          if (buf >= FA_SBUF) buf -= FA_SBUF;
+          if (++k3 == 3) { k3 = 0; bph ^= 1u; }
           if (++st == FA_KV_STAGES) st = 0;
         }
       }
@@ -327,7 +351,7 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       for (int j = 0; j < NKB; ++j) {
         const int e = (i * NKB + j) * 2 + g;
         const uint32_t sbuf = lane_addr + (uint32_t)(e % FA_SBUF) * FA_SCOLS;
-        mbar_wait(&bar->s_full[e % FA_SBUF], ((uint32_t)e / FA_SBUF) & 1u);
+        fa_wait(&bar->s_full[e % FA_SBUF], ((uint32_t)e / FA_SBUF) & 1u, W_S_FULL);
         if (live) {
         tc_fence_after();
         const int nch = keys_of(j) >> 4;                                       // 16-key chunks of the block
@@ -427,7 +451,7 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
             // o_done is observed exactly once and in order -- here, or by the drain for a tile's last block: a
             // parity wait is only exact while the waiter is at most one phase behind the barrier (a version that
             // skipped this wait unless a rescale was due let a fast warp reach a tile's drain two phases early).
-            mbar_wait(&bar->o_done[g], (nblk - 1u) & 1u);
+            fa_wait(&bar->o_done[g], (nblk - 1u) & 1u, W_O_DONE_BLK);
             if (rescale) {                           // rare after the first block: O *= 2^(old max - new max), in place
               tc_fence_after();
 #pragma unroll
@@ -454,7 +478,7 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           tc_fence_before();                         // P (and a rescaled O) are in tensor memory before the MMA reads them
         }
         __syncwarp();
-        if (lane == 0) mbar_arrive(&bar->p_full[e % FA_SBUF]);
+        if (lane == 0) mbar_arrive(&bar->p_full[g][e % FA_SBUF]);
         if (exists) ++nblk;
       }
       if (!exists) continue;
