@@ -34,6 +34,7 @@
 //               (O / row sum -> bf16 -> global) inside the first block of the slot's NEXT tile, when its last
 //               P V has long retired.
 // Warps whose 32 query rows are all past T (the tail tile) only pass the barriers on.
+#include <cstdlib>
 #include "common.cuh"
 #include "gemm_sm100.cuh"
 #include "sm100_ptx.cuh"
@@ -47,23 +48,33 @@ constexpr int FA_DH = 64;
 constexpr int FA_THREADS = 20 * 32;                 // TMA, S issuer, 2 P V issuers + 2 groups x 8 softmax warps
 constexpr int FA_TILE_BYTES = 128 * FA_DH * 2;      // one 128-row operand tile: 16 KB
 constexpr int FA_Q_STAGES = 2;
-constexpr int FA_KV_STAGES = 4;
-constexpr int FA_SBUF = 3;                          // rotating score buffers
-constexpr int FA_SCOLS = 128;                       // TMEM columns per score buffer
-constexpr int FA_OCOL = FA_SBUF * FA_SCOLS;         // O accumulators: [384, 448) and [448, 512)
+// Two layouts of tensor / shared memory (template parameter WIDE):
+//   general  key blocks of <= 128: three 128-column score buffers rotating over the entries + one O accumulator per
+//            slot (3 x 128 + 2 x 64 = 512 columns); K / V ring of 4 stages x (16 + 16) KB.
+//   WIDE     16 T' <= 208 keys and two query tiles (ViT-B/16: T = 197): ONE key block per tile, so a tile is one
+//            entry (half the barrier / MMA-issue round trips, no online rescale) in a 208-column score buffer per
+//            slot, and ONE O accumulator that the slots use in turn (2 x 208 + 64 = 480 columns); K / V ring of
+//            2 stages x (26 + 26) KB.
+constexpr int FA_MAX_KV_STAGES = 4;
+constexpr int FA_MAX_SBUF = 3;
+constexpr int FA_WIDE_KEYS = 208;
 constexpr float FA_RESCALE_THR = 8.0f;              // log2 units
 
 struct FaShared {
   uint64_t q_full[FA_Q_STAGES], q_empty[FA_Q_STAGES];
-  uint64_t kv_full[FA_KV_STAGES], kv_empty[FA_KV_STAGES];
-  uint64_t s_full[FA_SBUF], pv_done[FA_SBUF];
-  uint64_t p_full[2][FA_SBUF];       // per slot: its waiter (the slot's P V issuer) sees EVERY phase of its barriers
+  uint64_t kv_full[FA_MAX_KV_STAGES], kv_empty[FA_MAX_KV_STAGES];
+  uint64_t s_full[FA_MAX_SBUF], pv_done[FA_MAX_SBUF];
+  uint64_t p_full[2][FA_MAX_SBUF];       // per slot: its waiter (the slot's P V issuer) sees EVERY phase of its barriers
   uint64_t o_done[2], o_free[2];
   uint32_t tmem_slot, pad;
   float xmax[2][2][2][128];          // [group][block parity][key half][row]
   float xsum[2][2][128];             // [group][key half][row]
 };
-constexpr int FA_SMEM = (FA_Q_STAGES * 2 + FA_KV_STAGES * 2) * FA_TILE_BYTES + (int)sizeof(FaShared) + 1024;
+constexpr int fa_kv_stages(bool wide) { return wide ? 2 : 4; }
+constexpr int fa_kv_tile(bool wide) { return wide ? FA_WIDE_KEYS * FA_DH * 2 : FA_TILE_BYTES; }        // 26 KB / 16 KB
+constexpr int fa_smem(bool wide) {
+  return FA_Q_STAGES * 2 * FA_TILE_BYTES + fa_kv_stages(wide) * 2 * fa_kv_tile(wide) + (int)sizeof(FaShared) + 1024;
+}
 
 // MN-major B operand (V: keys x 64, 128-byte swizzled rows of dh): 8-key groups are 1024 B apart
 __device__ __forceinline__ uint64_t fa_desc_mn_sw128(uint32_t smem_addr) {
@@ -124,12 +135,14 @@ struct FaShape {
 // -> bf16 -> global, and the warp's arrival on o_free.  Every warp of the group arrives once per tile, in the tile's
 // own phase: a warp that has no rows in the tile runs ahead of the others, so it first waits until the previous
 // tile's phase has completed (the MMA warp is waiting for the same phase before the slot's next first P V).
-__device__ __forceinline__ void fa_drain(FaShared *bar, int g, int lane, bool live, uint32_t ntile, uint32_t phase,
-                                         uint32_t o_addr, float inv, __nv_bfloat16 *dst_row) {
+// `freed` is the o_free barrier the 8 warps of the group arrive on: the slot's own (general layout: its P V issuer
+// waits for it before the slot's next tile) or the OTHER slot's (WIDE: the shared accumulator is handed over).
+__device__ __forceinline__ void fa_drain(FaShared *bar, uint64_t *freed, int g, int lane, bool live, uint32_t ntile,
+                                         uint32_t phase, uint32_t o_addr, float inv, __nv_bfloat16 *dst_row) {
   if (!live) {
-    if (ntile > 1u) fa_wait(&bar->o_free[g], (ntile - 2u) & 1u, W_O_FREE_DEAD);
+    if (ntile > 1u) fa_wait(freed, (ntile - 2u) & 1u, W_O_FREE_DEAD);
     __syncwarp();
-    if (lane == 0) mbar_arrive(&bar->o_free[g]);
+    if (lane == 0) mbar_arrive(freed);
     return;
   }
   fa_wait(&bar->o_done[g], phase, W_O_DONE_DRAIN);               // the tile's last P V has retired
@@ -140,7 +153,7 @@ __device__ __forceinline__ void fa_drain(FaShared *bar, int g, int lane, bool li
   tmem_ld_wait();
   tc_fence_before();
   __syncwarp();
-  if (lane == 0) mbar_arrive(&bar->o_free[g]);     // the accumulator may be overwritten by the slot's next tile
+  if (lane == 0) mbar_arrive(freed);               // the accumulator may be overwritten by the next tile that uses it
   if (dst_row) {
     uint4 *dst = reinterpret_cast<uint4 *>(dst_row);
 #pragma unroll
@@ -155,6 +168,7 @@ __device__ __forceinline__ void fa_drain(FaShared *bar, int g, int lane, bool li
   }
 }
 
+template <bool WIDE>
 __global__ void __launch_bounds__(FA_THREADS, 1)
 attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV0,
                     const __grid_constant__ CUtensorMap tmKV1, __nv_bfloat16 *__restrict__ out, int n_items,
@@ -163,8 +177,13 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   uint8_t *smem = fa_raw;
   if ((smem_u32(smem) & 1023u) != 0u) __trap();                  // 128B-swizzled tiles need 1024-byte alignment
   uint8_t *sQ = smem;                                            // [stage][slot] 16 KB
-  uint8_t *sKV = smem + FA_Q_STAGES * 2 * FA_TILE_BYTES;         // [stage] K 16 KB | V 16 KB
-  FaShared *bar = reinterpret_cast<FaShared *>(sKV + FA_KV_STAGES * 2 * FA_TILE_BYTES);
+  constexpr int FA_SBUF = WIDE ? 2 : 3;                          // score buffers (entry e uses buffer e % FA_SBUF)
+  constexpr int FA_SCOLS = WIDE ? FA_WIDE_KEYS : 128;            // TMEM columns per score buffer
+  constexpr int FA_OCOL = FA_SBUF * FA_SCOLS;                    // O accumulator(s) behind the score buffers
+  constexpr int FA_KV_STAGES = fa_kv_stages(WIDE);
+  constexpr int FA_KV_TILE = fa_kv_tile(WIDE);
+  uint8_t *sKV = smem + FA_Q_STAGES * 2 * FA_TILE_BYTES;         // [stage] K | V
+  FaShared *bar = reinterpret_cast<FaShared *>(sKV + FA_KV_STAGES * 2 * FA_KV_TILE);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int T = sh.T, NKB = sh.nkb, D = sh.heads * FA_DH;
@@ -177,8 +196,8 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
   }
   if (warp == 0 && lane == 0) {
     for (int i = 0; i < FA_Q_STAGES; ++i) { mbar_init(&bar->q_full[i], 1); mbar_init(&bar->q_empty[i], 1); }
-    for (int i = 0; i < FA_KV_STAGES; ++i) { mbar_init(&bar->kv_full[i], 1); mbar_init(&bar->kv_empty[i], 2); }   // both P V issuers
-    for (int i = 0; i < FA_SBUF; ++i) { mbar_init(&bar->s_full[i], 1); mbar_init(&bar->p_full[0][i], 8); mbar_init(&bar->p_full[1][i], 8); mbar_init(&bar->pv_done[i], 1); }   // p_full: 8 warps of a group
+    for (int i = 0; i < FA_MAX_KV_STAGES; ++i) { mbar_init(&bar->kv_full[i], 1); mbar_init(&bar->kv_empty[i], 2); }   // both P V issuers
+    for (int i = 0; i < FA_MAX_SBUF; ++i) { mbar_init(&bar->s_full[i], 1); mbar_init(&bar->p_full[0][i], 8); mbar_init(&bar->p_full[1][i], 8); mbar_init(&bar->pv_done[i], 1); }   // p_full: 8 warps of a group
     for (int i = 0; i < 2; ++i) { mbar_init(&bar->o_done[i], 1); mbar_init(&bar->o_free[i], 8); }
     fence_barrier_init();
   }
@@ -220,9 +239,9 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           fa_wait(&bar->kv_empty[st], ((g / FA_KV_STAGES) & 1u) ^ 1u, W_KV_EMPTY);       // P V MMAs of the stage's last user retired
           const CUtensorMap *tm = (j == NKB - 1) ? &tmKV1 : &tmKV0;
           mbar_arrive_expect_tx(&bar->kv_full[st], 2u * (uint32_t)keys_of(j) * FA_DH * 2u);
-          uint8_t *sK = sKV + st * 2 * FA_TILE_BYTES;
+          uint8_t *sK = sKV + st * 2 * FA_KV_TILE;
           tma_load_2d(sK, tm, &bar->kv_full[st], D + head * FA_DH, row0 + j * sh.blk0);
-          tma_load_2d(sK + FA_TILE_BYTES, tm, &bar->kv_full[st], 2 * D + head * FA_DH, row0 + j * sh.blk0);
+          tma_load_2d(sK + FA_KV_TILE, tm, &bar->kv_full[st], 2 * D + head * FA_DH, row0 + j * sh.blk0);
         }
       }
     }
@@ -247,7 +266,7 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         const uint32_t q_addr = q_base + (uint32_t)((i & 1) * 2) * FA_TILE_BYTES;
         for (int j = 0; j < NKB; ++j) {
           const uint32_t idesc = umma_idesc_bf16(128, keys_of(j));
-          const uint64_t dk = umma_desc_k_sw128(kv_base + (uint32_t)st * 2 * FA_TILE_BYTES);
+          const uint64_t dk = umma_desc_k_sw128(kv_base + (uint32_t)st * 2 * FA_KV_TILE);
 #pragma unroll
           for (int sl = 0; sl < 2; ++sl) {
             if (e >= (uint32_t)FA_SBUF) fa_wait(&bar->pv_done[buf], bph ^ 1u, W_PV_DONE);   // P V(e - 3) has read its P
@@ -276,7 +295,7 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
       const int sl = warp - 2;
       const uint32_t kv_base = smem_u32(sKV);
       const uint32_t idesc_o = fa_idesc_bmn(128, FA_DH);
-      const uint32_t o = tmem_base + FA_OCOL + (uint32_t)sl * FA_DH;
+      const uint32_t o = tmem_base + FA_OCOL + (WIDE ? 0u : (uint32_t)sl * FA_DH);      // WIDE: one accumulator, used in turn
       // entry e = 2 * block + sl uses score buffer e % 3; the (slot, buffer) pair recurs every 3 blocks, so the phase
       // of p_full[sl][buf] is (block / 3) & 1.  (One p_full per buffer shared by both slots was wrong: a parity wait
       // is only exact if the waiter has seen the previous phase complete, and this thread would skip the other
@@ -290,11 +309,14 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           fa_wait(&bar->p_full[sl][buf], bph, W_P_FULL);
           if (exists) {
             if (j == 0) {                            // O of the slot's previous tile has been drained
-              fa_wait(&bar->o_free[sl], (tiles & 1u) ^ 1u, W_O_FREE);
+              // general: the group has drained the slot's previous tile.  WIDE: the OTHER group has drained the tile
+              // that used the shared accumulator before this one (slot 1 follows slot 0 of the same item, slot 0
+              // follows slot 1 of the previous item -- so slot 1 really waits for its first phase, slot 0 does not)
+              fa_wait(&bar->o_free[sl], (WIDE && sl == 1) ? (tiles & 1u) : ((tiles & 1u) ^ 1u), W_O_FREE);
               ++tiles;
             }
             tc_fence_after();
-            uint64_t dv = fa_desc_mn_sw128(kv_base + (uint32_t)st * 2 * FA_TILE_BYTES + FA_TILE_BYTES);
+            uint64_t dv = fa_desc_mn_sw128(kv_base + (uint32_t)st * 2 * FA_KV_TILE + FA_KV_TILE);
             uint32_t pc = tmem_base + (uint32_t)buf * FA_SCOLS;
             const int nch = keys_of(j) >> 4, hc = (nch + 1) >> 1;
             // P chunk k (16 keys = 8 packed columns) sits at the head of the score columns of the half that wrote it:
@@ -316,7 +338,7 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
           }
           buf += 2;                                  // e += 2
           if (buf >= FA_SBUF) buf -= FA_SBUF;
-          if (++k3 == 3) { k3 = 0; bph ^= 1u; }
+          if (++k3 == (WIDE ? 1 : 3)) { k3 = 0; bph ^= 1u; }    // the (slot, buffer) pair recurs every 3 blocks (WIDE: every block)
           if (++st == FA_KV_STAGES) st = 0;
         }
       }
@@ -329,11 +351,12 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
                                                      // of a (group, half) are consecutive, so they cover all quarters
     const int trow = q * 32 + lane;
     const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
-    const uint32_t o_addr = lane_addr + FA_OCOL + (uint32_t)g * FA_DH + (uint32_t)h * 32;
+    const uint32_t o_addr = lane_addr + FA_OCOL + (WIDE ? 0u : (uint32_t)g * FA_DH) + (uint32_t)h * 32;
     const uint64_t sc2 = pk2(scale_log2e, scale_log2e);
     const int bar_id = 1 + g * 4 + q;                // 64-thread named barrier of the two warps that share these rows
     uint32_t nblk = 0;                               // blocks of existing tiles this slot has seen (o_done phases, xmax parity)
     uint32_t ntile = 0;                              // existing tiles this slot has seen (o_free phases)
+    uint64_t *freed = &bar->o_free[WIDE ? (g ^ 1) : g];
     // The drain of a finished tile (wait for its last P V, O -> registers -> bf16 -> global) is DEFERRED into the
     // first block of the slot's next tile: by then the MMA has long retired, so the group never sits out the
     // MMA-issue + tensor-pipe round trip at the end of a tile.
@@ -470,7 +493,7 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         // the slot's previous tile is drained here, in the first block of the next one (its last P V retired long
         // ago), and before this block's arrival: the MMA warp waits for o_free right after p_full
         if (j == 0 && pend && exists) {
-          fa_drain(bar, g, lane, pend_live, ntile, pend_phase, o_addr, pend_inv, pend_dst);
+          fa_drain(bar, freed, g, lane, pend_live, ntile, pend_phase, o_addr, pend_inv, pend_dst);
           pend = false;
         }
         if (live) {
@@ -494,8 +517,12 @@ attention_fa_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_consta
         const int tok = tile * 128 + trow;
         pend_dst = tok < T ? out + ((size_t)crop * T + tok) * D + (size_t)head * FA_DH + h * 32 : nullptr;
       }
+      if (WIDE) {                                    // the other slot is waiting for the shared accumulator: drain now
+        fa_drain(bar, freed, g, lane, pend_live, ntile, pend_phase, o_addr, pend_inv, pend_dst);
+        pend = false;
+      }
     }
-    if (pend) fa_drain(bar, g, lane, pend_live, ntile, pend_phase, o_addr, pend_inv, pend_dst);
+    if (pend) fa_drain(bar, freed, g, lane, pend_live, ntile, pend_phase, o_addr, pend_inv, pend_dst);
   }
 
   tc_fence_before();
@@ -514,7 +541,11 @@ int yv_attention_fa_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, 
   sh.T = T;
   sh.heads = heads;
   const int t16 = (T + 15) & ~15, nch = t16 >> 4;
-  if (t16 <= 128) { sh.nkb = 1; sh.blk0 = sh.blk_last = t16; }
+  const int nq = (T + 127) >> 7;
+  // WIDE layout: all keys in one block per tile (<= 208) and exactly two query tiles, i.e. 129 <= T <= 208 (ViT-B/16)
+  static const bool no_wide = []() { const char *e = getenv("YV_ATTN_WIDE"); return e && e[0] == '0'; }();
+  const bool wide = !no_wide && t16 <= FA_WIDE_KEYS && nq == 2;
+  if (wide || t16 <= 128) { sh.nkb = 1; sh.blk0 = sh.blk_last = t16; }
   else if (t16 <= 256) { sh.nkb = 2; sh.blk0 = 16 * ((nch + 1) >> 1); sh.blk_last = t16 - sh.blk0; }
   else { sh.nkb = (t16 + 127) / 128; sh.blk0 = 128; sh.blk_last = t16 - (sh.nkb - 1) * 128; }
   sh.nq = (T + 127) >> 7;
@@ -529,13 +560,15 @@ int yv_attention_fa_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, 
   if ((rc = yv_tmap_bf16_2d(&tmKV0, qkv, (uint64_t)n * T, (uint64_t)3 * D, (uint32_t)sh.blk0))) return rc;
   if ((rc = yv_tmap_bf16_2d(&tmKV1, qkv, (uint64_t)n * T, (uint64_t)3 * D, (uint32_t)sh.blk_last))) return rc;
   rc = yv_device_once(YV_INIT_ATTN_FA, []() -> int {
-    YV_CUDA(cudaFuncSetAttribute(attention_fa_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FA_SMEM));
+    YV_CUDA(cudaFuncSetAttribute(attention_fa_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, fa_smem(false)));
+    YV_CUDA(cudaFuncSetAttribute(attention_fa_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, fa_smem(true)));
     return YV_OK;
   });
   if (rc) return rc;
   YvProf prof(YV_K_ATTN, s, 4.0 * n * heads * (double)T * T * dh);
   const int grid = items < yv_num_sms() ? (int)items : yv_num_sms();
-  attention_fa_kernel<<<grid, FA_THREADS, FA_SMEM, s>>>(tmQ, tmKV0, tmKV1, out, (int)items, sh, scale_log2e);
+  if (wide) attention_fa_kernel<true><<<grid, FA_THREADS, fa_smem(true), s>>>(tmQ, tmKV0, tmKV1, out, (int)items, sh, scale_log2e);
+  else attention_fa_kernel<false><<<grid, FA_THREADS, fa_smem(false), s>>>(tmQ, tmKV0, tmKV1, out, (int)items, sh, scale_log2e);
   YV_LAUNCH_CHECK();
   return YV_OK;
 }
