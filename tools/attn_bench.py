@@ -1,5 +1,5 @@
 """Attention alone: CUDA-event timing of ops.attention_bf16 at the two shapes the ViTs use (ViT-B/16: T = 197, ViT-B/8:
-T = 785), L2 flushed between reps.  YV_ATTN=legacy selects the round-1 kernels.  NCU=1: one launch per shape.
+T = 785), L2 flushed between reps.  YV_ATTN_B16=fa runs the ViT-B/16 shape on the flash-style kernel too.  NCU=1: one launch per shape.
 Reports ms, TFLOP/s (4 T^2 dh flop per (crop, head)) and the fraction of the MUFU floor (16 ex2 per clock per SM at the
 SM clock sampled by nvidia-smi is not known here, so the floor is given in clocks per SM instead)."""
 import json, os, sys
@@ -10,7 +10,7 @@ from yolov8_vit_b200 import ops
 dev = "cuda:0"
 NCU = bool(os.environ.get("NCU"))
 flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
-out = {"kernel": os.environ.get("YV_ATTN", "fa")}
+out = {"b16_kernel": "attention_fa (WIDE)" if os.environ.get("YV_ATTN_B16", "")[:1] == "f" else "attention_pipe", "b8_kernel": "attention_fa"}
 shapes = [("b16", int(os.environ.get("N16", "1072")), 197), ("b8", int(os.environ.get("N8", "256")), 785)]
 for name, n, T in shapes:
     heads, dh = 12, 64

@@ -17,7 +17,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(HERE, "build")
 LIB = os.path.join(HERE, "libyv8vit.so")
-SOURCES = ["api.cu", "decode.cu", "preprocess.cu", "nms.cu", "crop.cu", "gemm_sm100.cu", "vit_ops.cu", "attention_sm100.cu", "attention.cu", "attention_fa.cu", "vit.cu"]
+SOURCES = ["api.cu", "decode.cu", "preprocess.cu", "nms.cu", "crop.cu", "gemm_sm100.cu", "vit_ops.cu", "attention_sm100.cu", "attention_fa.cu", "vit.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-std=c++17", "-lineinfo",
     "-Xcompiler", "-fPIC,-fvisibility=hidden", "--expt-relaxed-constexpr",

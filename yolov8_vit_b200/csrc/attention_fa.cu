@@ -114,12 +114,23 @@ __device__ __noinline__ void fa_wait_timeout(int tag, uint32_t parity) {
     printf("attention_fa: wait %d (parity %u) timed out: cta %d warp %d lane %d\n", tag, parity, (int)blockIdx.x,
          (int)(threadIdx.x >> 5), (int)(threadIdx.x & 31));
 }
+// The wait carries a suspend-time hint: the warp sleeps inside try_wait until the phase completes (or the hint
+// expires) instead of spinning -- every SM sub-partition hosts warps of BOTH groups, and a group that polls steals
+// issue slots from the one that is computing (ncu: half of the executed instructions were wait loops).
 __device__ __forceinline__ void fa_wait(uint64_t *bar, uint32_t parity, int tag) {
-  uint32_t spins = 0;
-  while (!mbar_try_wait(bar, parity)) {
+  uint32_t spins = 0, ok = 0;
+  for (;;) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.b32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity), "r"(4000u)
+        : "memory");
+    if (ok) break;
     ++spins;
-    if (spins == (1u << 20)) fa_wait_timeout(tag, parity);      // report, give the other starved waits time to report too
-    if (spins > (1u << 24)) __trap();
+    if (spins == (1u << 18)) fa_wait_timeout(tag, parity);      // report, give the other starved waits time to report too
+    if (spins > (1u << 22)) __trap();
   }
 }
 enum { W_Q_EMPTY = 1, W_KV_EMPTY, W_PV_DONE, W_Q_FULL, W_KV_FULL, W_P_FULL, W_O_FREE, W_S_FULL, W_O_DONE_BLK, W_O_DONE_DRAIN, W_O_FREE_DEAD };
@@ -543,6 +554,7 @@ int yv_attention_fa_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, 
   const int t16 = (T + 15) & ~15, nch = t16 >> 4;
   const int nq = (T + 127) >> 7;
   // WIDE layout: all keys in one block per tile (<= 208) and exactly two query tiles, i.e. 129 <= T <= 208 (ViT-B/16)
+  // (the default ViT-B/16 kernel is attention_sm100.cu's; this layout runs there with YV_ATTN_B16=fa)
   static const bool no_wide = []() { const char *e = getenv("YV_ATTN_WIDE"); return e && e[0] == '0'; }();
   const bool wide = !no_wide && t16 <= FA_WIDE_KEYS && nq == 2;
   if (wide || t16 <= 128) { sh.nkb = 1; sh.blk0 = sh.blk_last = t16; }

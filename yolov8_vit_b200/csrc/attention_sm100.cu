@@ -3,22 +3,12 @@
 // timm Attention.forward (vit_base_patch{16,8}_224; reached by the reference through
 // utils/utils.py:71-72): qkv [n, T, 3, heads, 64] -> per head softmax(q k^T * 64^-0.5) v.
 //
-// Two kernels: attention_pipe_kernel (further down; software-pipelined, used whenever two score buffers
-// fit in tensor memory, i.e. T <= 224: the ViT-B/16 case) and attention_tc_kernel below (T <= 256).
-//
-// attention_tc_kernel: work item = (crop, head, 128-row query tile).  Two persistent CTAs per SM (84 KB of shared memory and
-// 256 TMEM columns each) walk the items, so one CTA's softmax overlaps the other's MMA / TMA round
-// trips.  Per item (T <= 256 tokens, NK = T rounded up to 16 keys):
-//   TMA      Q (128 x 64), K (NK x 64), V (NK x 64) boxes straight out of the packed qkv activation
-//            (128-byte swizzle = the UMMA operand layout, no staging copies);
-//   MMA      S = Q K^T (128 x NK x 64) into TMEM columns [0, NK);
-//   softmax  8 warps (one thread per query row and column half): max pass, then exp2 / sum pass; P is
-//            written back INTO TENSOR MEMORY as packed bf16 pairs, each half into the head of its own
-//            (already consumed) part of S, so P never touches shared memory;
-//   MMA      O = P V (128 x 64 x NK), A operand from TMEM, V as an MN-major smem operand (no
-//            transpose), into TMEM columns [192, 256);
-//   output   O * (1 / sum) -> bf16 -> global.
-// The fp32 scores never leave the SM; HBM traffic is qkv in, out out.
+// attention_pipe_kernel (below): the kernel for sequences whose whole score row fits twice in tensor memory
+// (16 T' <= 224 keys: ViT-B/16, T = 197).  Every other length -- the reference-literal ViT-B/8 with 785 tokens in
+// particular -- runs on the flash-style multi-key-block kernel of attention_fa.cu; both are tcgen05 / TMEM / TMA
+// kernels (the round-1 mma.sync kernel for long sequences is gone).  attention_fa.cu also has a layout for the
+// ViT-B/16 shape (two query tiles in flight); measured 0.43 ms per 1072-crop launch against 0.38 ms for this
+// kernel, so this one stays the default there (YV_ATTN_B16=fa selects the other, A/B timing).
 #include <cstdlib>
 #include "common.cuh"
 #include "gemm_sm100.cuh"
@@ -30,12 +20,8 @@ using namespace sm100;
 namespace {
 
 constexpr int AT_DH = 64;
-constexpr int AT_THREADS = 12 * 32;                 // TMA, MMA, TMEM-alloc, spare + 8 softmax warps
 constexpr int AT_Q_BYTES = 128 * AT_DH * 2;         // 16 KB
 constexpr int AT_KV_BYTES = 256 * AT_DH * 2;        // 32 KB reserved each (box is NK rows)
-constexpr int AT_SMEM = AT_Q_BYTES + 2 * AT_KV_BYTES + 2048;   // + barriers / exchange
-constexpr int AT_TMEM_COLS = 256;                   // S [0, NK); P inside S; O [192, 256)
-constexpr int AT_O_COL = 192;
 
 // MN-major B operand (V: keys x 64, 128-byte swizzled rows of dh): 8-key groups are 1024 B apart
 __device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t smem_addr) {
@@ -57,221 +43,6 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t *>(&h);
 }
-
-struct AttnBars {
-  uint64_t qk_full, v_full, s_full, p_full, o_full, t_free;
-  uint32_t tmem_slot;
-  uint32_t pad;
-  float xch[2][128];          // [slot][row]: max / sum exchange between the two column halves
-};
-
-// TMEM column of P chunk k (16 keys = 8 packed columns): each column half writes P into the head of
-// its own part of S, which it has already consumed (chunk k of S sits at columns [16k, 16k+16)).
-__device__ __forceinline__ int p_col(int k, int h0_chunks) {
-  return k < h0_chunks ? 8 * k : 16 * h0_chunks + 8 * (k - h0_chunks);
-}
-
-__global__ void __launch_bounds__(AT_THREADS, 2)
-attention_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
-                    __nv_bfloat16 *__restrict__ out, int n_items, int T, int heads, float scale_log2e) {
-  extern __shared__ __align__(1024) uint8_t at_raw[];
-  uint8_t *smem = at_raw;                           // 128B-swizzled tiles need 1024-byte alignment
-  if ((smem_u32(smem) & 1023u) != 0u) __trap();
-  uint8_t *sQ = smem, *sK = sQ + AT_Q_BYTES, *sV = sK + AT_KV_BYTES;
-  AttnBars *bar = reinterpret_cast<AttnBars *>(sV + AT_KV_BYTES);
-
-  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int NK = (T + 15) & ~15;                    // keys per MMA (multiple of 16, <= 256)
-  const int NG = (T + 127) >> 7;                    // query tiles per (crop, head)
-  const int H0C = (NK / 16 + 1) / 2;                // 16-key chunks in the first column half
-  const int D = heads * AT_DH;
-  const uint32_t kv_bytes = (uint32_t)NK * AT_DH * 2;
-
-  if (warp == 0 && lane == 0) {
-    prefetch_tmap(&tmQ);
-    prefetch_tmap(&tmKV);
-  }
-  if (warp == 1 && lane == 0) {
-    mbar_init(&bar->qk_full, 1);
-    mbar_init(&bar->v_full, 1);
-    mbar_init(&bar->s_full, 1);
-    mbar_init(&bar->p_full, 8);                     // the 8 softmax warps
-    mbar_init(&bar->o_full, 1);
-    mbar_init(&bar->t_free, 8);
-    fence_barrier_init();
-  }
-  if (warp == 2) {
-    tmem_alloc(&bar->tmem_slot, AT_TMEM_COLS);
-    tmem_relinquish();
-  }
-  tc_fence_before();
-  __syncthreads();
-  tc_fence_after();
-  const uint32_t tmem_base = bar->tmem_slot;
-
-  if (warp == 0) {
-    // ===================== TMA producer =====================
-    if (elect_one()) {
-      uint32_t it = 0;
-      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
-        const int g = item % NG, ch = item / NG;
-        const int crop = ch / heads, head = ch - crop * heads;
-        const int row0 = crop * T;
-        const uint32_t prev = (it & 1u) ^ 1u;       // parity of the previous item's completions
-        // Q, K are free once the previous item's S MMA retired; V once its P V retired
-        if (it > 0) mbar_wait_sleep(&bar->s_full, prev);
-        mbar_arrive_expect_tx(&bar->qk_full, AT_Q_BYTES + kv_bytes);
-        tma_load_2d(sQ, &tmQ, &bar->qk_full, head * AT_DH, row0 + g * 128);
-        tma_load_2d(sK, &tmKV, &bar->qk_full, D + head * AT_DH, row0);
-        if (it > 0) mbar_wait_sleep(&bar->o_full, prev);
-        mbar_arrive_expect_tx(&bar->v_full, kv_bytes);
-        tma_load_2d(sV, &tmKV, &bar->v_full, 2 * D + head * AT_DH, row0);
-      }
-    }
-  } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    if (elect_one()) {
-      const uint32_t idesc_s = umma_idesc_bf16(128, NK);
-      const uint32_t idesc_o = umma_idesc_bf16_bmn(128, AT_DH);
-      const uint32_t aQ = smem_u32(sQ), aK = smem_u32(sK), aV = smem_u32(sV);
-      uint32_t it = 0;
-      for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
-        const uint32_t ph = it & 1u;
-        mbar_wait_sleep(&bar->qk_full, ph);
-        mbar_wait_sleep(&bar->t_free, ph ^ 1u);           // softmax warps have drained O of the previous item
-        tc_fence_after();
-        {                                           // S = Q K^T
-          const uint64_t dq = umma_desc_k_sw128(aQ), dk = umma_desc_k_sw128(aK);
-#pragma unroll
-          for (int k = 0; k < AT_DH / 16; ++k)
-            umma_bf16(tmem_base, dq + (uint64_t)(k * 2), dk + (uint64_t)(k * 2), idesc_s, (uint32_t)(k != 0));
-          umma_commit(&bar->s_full);
-        }
-        mbar_wait_sleep(&bar->v_full, ph);
-        mbar_wait_sleep(&bar->p_full, ph);
-        tc_fence_after();
-        for (int k = 0; k < NK / 16; ++k)           // O = P V, A (= P) from tensor memory
-          umma_bf16_ts(tmem_base + AT_O_COL, tmem_base + p_col(k, H0C), umma_desc_mn_sw128(aV + k * (16 * 128)),
-                       idesc_o, (uint32_t)(k != 0));
-        umma_commit(&bar->o_full);
-      }
-    }
-  } else if (warp >= 4) {
-    // ===================== softmax + output =====================
-    // 8 warps: TMEM lane quarter q (one thread per query row) x column half hf.  The two threads that
-    // share a row exchange their partial max / sum through shared memory (one named barrier).
-    const int q = warp & 3, hf = (warp - 4) >> 2;
-    const int trow = q * 32 + lane;                 // row inside the tile
-    const uint32_t trow_addr = tmem_base + ((uint32_t)(q * 32) << 16);
-    const int k_lo = hf ? H0C : 0, k_hi = hf ? NK / 16 : H0C;   // this warp's 16-key chunks
-    // slot[hf] carries my max to the partner; once I have read the partner's max from slot[hf ^ 1]
-    // that slot is mine to carry my sum back (each slot has one writer and one reader per phase)
-    float *xmine = bar->xch[hf] + trow, *xother = bar->xch[hf ^ 1] + trow;
-    uint32_t it = 0;
-    for (int item = blockIdx.x; item < n_items; item += gridDim.x, ++it) {
-      const uint32_t ph = it & 1u;
-      const int g = item % NG, ch = item / NG;
-      const int crop = ch / heads, head = ch - crop * heads;
-      const int tok = g * 128 + trow;               // token index inside the crop
-      mbar_wait_sleep(&bar->s_full, ph);
-      tc_fence_after();
-      // pass 1: maximum of this warp's half of the row (keys >= T are masked)
-      float mx = -INFINITY;
-      for (int k = k_lo; k < k_hi; k += 2) {
-        uint32_t a[16], b[16];
-        const bool two = k + 1 < k_hi;
-        tmem_ld_32x16(trow_addr + 16 * k, a);
-        if (two) tmem_ld_32x16(trow_addr + 16 * k + 16, b);
-        tmem_ld_wait();
-        if (16 * k + 32 <= T) {
-#pragma unroll
-          for (int j = 0; j < 16; ++j) mx = fmaxf(mx, fmaxf(__uint_as_float(a[j]), __uint_as_float(b[j])));
-        } else {
-#pragma unroll
-          for (int j = 0; j < 16; ++j)
-            if (16 * k + j < T) mx = fmaxf(mx, __uint_as_float(a[j]));
-          if (two) {
-#pragma unroll
-            for (int j = 0; j < 16; ++j)
-              if (16 * k + 16 + j < T) mx = fmaxf(mx, __uint_as_float(b[j]));
-          }
-        }
-      }
-      *xmine = mx;
-      asm volatile("bar.sync 1, 256;" ::: "memory");
-      mx = fmaxf(mx, *xother);
-      const float mneg = -mx * scale_log2e;
-      const uint64_t sc2 = pk2(scale_log2e, scale_log2e), mn2 = pk2(mneg, mneg);
-      // pass 2: p = exp2(s * scale - max * scale); row sum; P -> TMEM as packed bf16 pairs, written
-      // behind this warp's own read pointer (P chunk k lands in columns this warp has already consumed)
-      uint64_t sum2 = pk2(0.f, 0.f);
-      uint32_t r[16];
-      if (k_lo < k_hi) tmem_ld_32x16(trow_addr + 16 * k_lo, r);
-      for (int k = k_lo; k < k_hi; ++k) {
-        tmem_ld_wait();
-        float p[16];
-#pragma unroll
-        for (int j = 0; j < 16; j += 2) {           // packed FFMA2: two scores per instruction
-          float x0, x1;
-          unpk2(fma2(pk2(__uint_as_float(r[j]), __uint_as_float(r[j + 1])), sc2, mn2), x0, x1);
-          p[j] = ex2_approx(x0);
-          p[j + 1] = ex2_approx(x1);
-        }
-        if (k + 1 < k_hi) tmem_ld_32x16(trow_addr + 16 * (k + 1), r);
-        if (16 * k + 16 > T) {
-#pragma unroll
-          for (int j = 0; j < 16; ++j)
-            if (16 * k + j >= T) p[j] = 0.f;
-        }
-#pragma unroll
-        for (int j = 0; j < 16; j += 4) sum2 = add2(sum2, add2(pk2(p[j], p[j + 1]), pk2(p[j + 2], p[j + 3])));
-        uint32_t w[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) w[j] = pack_bf16x2(p[2 * j], p[2 * j + 1]);
-        tmem_st_32x8(trow_addr + p_col(k, H0C), w);
-      }
-      float sum, sum_hi;
-      unpk2(sum2, sum, sum_hi);
-      sum += sum_hi;
-      tmem_st_wait();
-      tc_fence_before();                            // P stores and S loads precede the MMA that reads P
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&bar->p_full);
-      *xother = sum;
-      asm volatile("bar.sync 1, 256;" ::: "memory");
-      const float inv = 1.0f / (sum + *xmine);
-
-      // O = P V is in TMEM columns [192, 256): this warp normalises and stores 32 of them
-      mbar_wait_sleep(&bar->o_full, ph);
-      tc_fence_after();
-      uint32_t o0[16], o1[16];
-      tmem_ld_32x16(trow_addr + AT_O_COL + hf * 32, o0);
-      tmem_ld_32x16(trow_addr + AT_O_COL + hf * 32 + 16, o1);
-      tmem_ld_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&bar->t_free);     // the accumulator columns may be reused
-      if (tok < T) {
-        uint4 *dst = reinterpret_cast<uint4 *>(out + ((size_t)crop * T + tok) * D + (size_t)head * AT_DH + hf * 32);
-        auto pack8 = [&](const uint32_t *v) {
-          uint4 u;
-          u.x = pack_bf16x2(__uint_as_float(v[0]) * inv, __uint_as_float(v[1]) * inv);
-          u.y = pack_bf16x2(__uint_as_float(v[2]) * inv, __uint_as_float(v[3]) * inv);
-          u.z = pack_bf16x2(__uint_as_float(v[4]) * inv, __uint_as_float(v[5]) * inv);
-          u.w = pack_bf16x2(__uint_as_float(v[6]) * inv, __uint_as_float(v[7]) * inv);
-          return u;
-        };
-        dst[0] = pack8(o0); dst[1] = pack8(o0 + 8);
-        dst[2] = pack8(o1); dst[3] = pack8(o1 + 8);
-      }
-    }
-  }
-
-  tc_fence_before();
-  __syncthreads();
-  if (warp == 2) tmem_dealloc(tmem_base, AT_TMEM_COLS);
-}
-
 
 // =================================================================================================
 // v3: software-pipelined variant for NK <= 224 keys (ViT-B/16: T = 197 -> NK = 208).
@@ -628,38 +399,27 @@ int yv_attention_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, int
                         cudaStream_t s) {
   YV_REQUIRE(dh == AT_DH, "attention: head dim %d unsupported (need %d)", dh, AT_DH);
   YV_REQUIRE(n >= 1 && heads >= 1 && T >= 1, "attention: bad shape");
-  // YV_ATTN=legacy selects the round-1 kernels (A/B timing): attention_pipe / attention_tc for T <= 256 and the
-  // mma.sync multi-block kernel above that; the default is the flash-style tcgen05 kernel of attention_fa.cu
-  static const bool legacy = []() { const char *e = getenv("YV_ATTN"); return e && e[0] == 'l'; }();
-  if (!legacy) return yv_attention_fa_launch(qkv, out, n, T, heads, dh, s);
-  if (T > 256) return yv_attention_long_launch(qkv, out, n, T, heads, dh, s);   // ViT-B/8: mma.sync multi-block path
-  YV_REQUIRE(((uintptr_t)qkv % 16) == 0 && ((uintptr_t)out % 16) == 0, "attention: operands must be 16-byte aligned");
   const int NK = (T + 15) & ~15, NG = (T + 127) >> 7;
+  const bool pipelined = 2 * NK + AT_DH <= 512 && NG <= 2;      // two score buffers + O fit in tensor memory
+  static const bool b16_fa = []() { const char *e = getenv("YV_ATTN_B16"); return e && e[0] == 'f'; }();
+  if (!pipelined || b16_fa) return yv_attention_fa_launch(qkv, out, n, T, heads, dh, s);
+  YV_REQUIRE(((uintptr_t)qkv % 16) == 0 && ((uintptr_t)out % 16) == 0, "attention: operands must be 16-byte aligned");
   const int D = heads * AT_DH;
   const float scale_log2e = (1.0f / sqrtf((float)dh)) * 1.4426950408889634f;
-  const bool pipelined = 2 * NK + AT_DH <= 512;     // two score buffers + O fit in tensor memory
   CUtensorMap tmQ, tmKV;
-  int rc = yv_tmap_bf16_2d(&tmQ, qkv, (uint64_t)n * T, (uint64_t)3 * D, pipelined ? (uint32_t)(128 * NG) : 128u);
+  int rc = yv_tmap_bf16_2d(&tmQ, qkv, (uint64_t)n * T, (uint64_t)3 * D, (uint32_t)(128 * NG));
   if (rc) return rc;
   rc = yv_tmap_bf16_2d(&tmKV, qkv, (uint64_t)n * T, (uint64_t)3 * D, (uint32_t)NK);
   if (rc) return rc;
   rc = yv_device_once(YV_INIT_ATTN, []() -> int {
-    YV_CUDA(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
     YV_CUDA(cudaFuncSetAttribute(attention_pipe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AP_SMEM));
     return YV_OK;
   });
   if (rc) return rc;
   YvProf prof(YV_K_ATTN, s, 4.0 * n * heads * (double)T * T * dh);
-  if (pipelined) {
-    const int units = n * heads;
-    const int grid = units < yv_num_sms() ? units : yv_num_sms();
-    attention_pipe_kernel<<<grid, AP_THREADS, AP_SMEM, s>>>(tmQ, tmKV, out, units, T, heads, scale_log2e, g_trace);
-  } else {
-    const int items = n * heads * NG;
-    const int slots = 2 * yv_num_sms();             // two co-resident CTAs per SM
-    const int grid = items < slots ? items : slots;
-    attention_tc_kernel<<<grid, AT_THREADS, AT_SMEM, s>>>(tmQ, tmKV, out, items, T, heads, scale_log2e);
-  }
+  const int units = n * heads;
+  const int grid = units < yv_num_sms() ? units : yv_num_sms();
+  attention_pipe_kernel<<<grid, AP_THREADS, AP_SMEM, s>>>(tmQ, tmKV, out, units, T, heads, scale_log2e, g_trace);
   YV_LAUNCH_CHECK();
   return YV_OK;
 }

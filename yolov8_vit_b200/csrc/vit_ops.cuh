@@ -20,13 +20,11 @@ int yv_ln2_launch(const void *x, int x_type, size_t in_stride, const __nv_bfloat
                   int rows, int dim, float eps, cudaStream_t s);
 
 // softmax(Q K^T / sqrt(dh)) V; qkv [n*T, 3*heads*dh] bf16 (timm packing: q | k | v, head-major),
-// out [n*T, heads*dh] bf16.  dh == 64.  T <= 256: tcgen05 kernels (attention_sm100.cu); longer sequences
-// (ViT-B/8) are forwarded to the mma.sync multi-block kernel of attention.cu.
+// out [n*T, heads*dh] bf16.  dh == 64.  Both kernels are tcgen05 / TMEM / TMA: attention_sm100.cu for sequences whose
+// score row fits twice in tensor memory (<= 224 keys: ViT-B/16), attention_fa.cu (flash-style, key blocks of <= 128,
+// online softmax) for every other length (ViT-B/8: 785 tokens).
 int yv_attention_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, int T, int heads, int dh,
                         cudaStream_t s);
-int yv_attention_long_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, int T, int heads, int dh,
-                             cudaStream_t s);
-// attention_fa.cu: flash-style tcgen05 kernel for any T (single read of the scores, two query tiles in flight)
 int yv_attention_fa_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, int T, int heads, int dh,
                            cudaStream_t s);
 
