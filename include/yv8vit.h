@@ -237,6 +237,20 @@ int yv_gemm_bf16(const void *A, const void *W, const float *bias,
 int yv_layernorm_bf16(const void *x, const float *gamma, const float *beta,
                       void *y, int rows, int dim, float eps,
                       yv_stream_t stream);
+/* D = [GELU](Linear(LayerNorm(x))) for an f16 x [M,K] (the ViT's residual
+ * stream), W bf16 [N,K], D bf16 [M,N] -- the form the ViT blocks run
+ * (timm vision_transformer Block: norm1 -> attn.qkv, norm2 -> mlp.fc1) with the
+ * LayerNorm FOLDED into the GEMM: the tensor cores multiply the raw f16 rows by
+ * fp16(g (.) W) and the epilogue applies rstd_m (acc - mu_m colsum_n) + c_n,
+ * c = bias + beta . W^T.  Three launches: weight fold (the ViT does it once per
+ * model), row statistics (reads x once, writes 8 B per row), GEMM.  ws holds
+ * the folded weights and statistics: yv_linear_ln_f16_ws_bytes(M, N, K).
+ * K % 256 == 0, 256 <= K <= 1024, N % 16 == 0.                                 */
+size_t yv_linear_ln_f16_ws_bytes(int M, int N, int K);
+int yv_linear_ln_f16(const void *x, const void *W, const float *bias,
+                     const float *gamma, const float *beta, void *D, int M,
+                     int N, int K, float eps, int epi, void *ws, size_t ws_bytes,
+                     yv_stream_t stream);
 /* softmax(Q K^T / sqrt(dh)) V for qkv [n, T, 3, heads, dh] bf16 -> out
  * [n, T, heads*dh] bf16 (timm's qkv packing).                               */
 int yv_attention_bf16(const void *qkv, void *out, int n, int T, int heads,

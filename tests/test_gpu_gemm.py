@@ -107,3 +107,32 @@ def test_gemm_block_shapes_at_bench_m(name, N, K, kw):
     else:
         got = ops.gemm_bf16(a, w, bias=bias)
         _close(got[ri], base, 1e-2, 1e-2)
+
+
+@pytest.mark.parametrize("M,N,K,gelu", [(128, 256, 256, False), (197 * 5, 2304, 768, False), (197 * 5, 3072, 768, True),
+                                        (1000, 768, 1024, False), (333, 272, 512, True), (1, 256, 768, False)])
+def test_linear_with_folded_layernorm(M, N, K, gelu):
+    """yv_linear_ln_f16: Linear(LayerNorm(x)) with the LayerNorm folded into the GEMM (f16 rows x fp16 g(.)W on the
+    tensor cores, rstd (acc - mu colsum) + c in the epilogue) against LayerNorm + matmul in fp32 on the same f16 rows
+    and bf16 weights.  Rows carry a large common offset (mean 3, spread 0.5..4) so the mean subtraction in the
+    epilogue is exercised; tolerance = bf16 output rounding + the fp16 rounding of the folded weights (2^-11 per
+    term, sqrt(K) accumulation)."""
+    g = torch.Generator().manual_seed(M + N + K)
+    scale = torch.rand(M, 1, generator=g) * 3.5 + 0.5
+    x = (torch.randn(M, K, generator=g) * scale + 3.0 * torch.randn(M, 1, generator=g)).to(torch.float16)
+    w = (torch.randn(N, K, generator=g) * 0.05).to(torch.bfloat16)
+    bias = torch.randn(N, generator=g) * 0.1
+    gamma = 1.0 + 0.3 * torch.randn(K, generator=g)
+    beta = 0.2 * torch.randn(K, generator=g)
+    ref = torch.nn.functional.layer_norm(x.double(), (K,), gamma.double(), beta.double(), 1e-6) @ w.double().t() + bias.double()
+    if gelu:
+        ref = torch.nn.functional.gelu(ref)
+    got = ops.linear_ln_f16(x.to(DEV), w.to(DEV), bias.to(DEV), gamma.to(DEV), beta.to(DEV), 1e-6, gelu).cpu()
+    _close(got, ref.float(), rtol=2 ** -7, atol=6e-3)
+    # and it is the same operator as the two-kernel form (LayerNorm kernel to bf16, then the bf16 GEMM), whose
+    # bf16 rounding of the normalised rows is the larger error of the two
+    y = torch.nn.functional.layer_norm(x.float(), (K,), gamma, beta, 1e-6).to(torch.bfloat16)
+    two = ops.gemm_bf16(y.to(DEV), w.to(DEV), bias.to(DEV), gelu=gelu).cpu()
+    e_fold = float((got.double() - ref).abs().max())
+    e_two = float((two.double() - ref).abs().max())
+    assert e_fold <= 1.5 * e_two + 1e-3, (e_fold, e_two)

@@ -43,7 +43,11 @@ constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
 //   EPI_TMA_RES  the same with the RESIDUAL ADD fused: the warp's 32 x 64 piece of the fp16 residual stream is
 //             fetched by TMA into the staging block while the tile's MMAs still run, added in place and stored
 //             back by TMA as fp16 (proj, fc2: x += y W^T + b without a single LSU global access)
-constexpr int EPI_LSU = 0, EPI_TMA = 1, EPI_TMA_RES = 2;
+//   EPI_TMA_LN   EPI_TMA with the LayerNorm that precedes the Linear FOLDED in: A is the raw fp16 residual stream x, W
+//             holds g (.) W_orig as fp16 (kind::f16 with fp16 operands, fp32 accumulation), and the epilogue applies
+//             D = rstd_m (acc - mu_m colsum_n) + cfold_n with (mu, rstd) per row from a statistics kernel that only
+//             READS the stream (2 B per element instead of the 4 B of a LayerNorm kernel that also writes y)
+constexpr int EPI_LSU = 0, EPI_TMA = 1, EPI_TMA_RES = 2, EPI_TMA_LN = 3;
 // smem ring depth: the residual form needs 4 KB of staging per epilogue warp (both 32 x 32 boxes of the tile
 // resident at once) instead of 2 KB, paid for with one stage of the ring
 constexpr int gemm_stages(int direct) { return direct == EPI_TMA_RES ? 5 : 6; }
@@ -167,7 +171,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   } else if (warp == 1 && rank == 0) {
     // ===================== MMA issuer (one elected lane of the leader CTA) =====================
     if (elect_one()) {
-      constexpr uint32_t idesc = umma_idesc_bf16(PM, BN);
+      // operand format bits [7,10) / [10,13): 1 = bf16, 0 = f16 (the folded-LayerNorm form multiplies fp16 x fp16)
+      constexpr uint32_t idesc = DIRECT == EPI_TMA_LN ? (umma_idesc_bf16(PM, BN) & ~((7u << 7) | (7u << 10))) : umma_idesc_bf16(PM, BN);
       int stage = 0;
       uint32_t phase = 0, it = 0;
       for (int tile = pair; tile < num_tiles; tile += npairs, ++it) {
@@ -232,15 +237,24 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + cg * EPI_COLS;
       uint32_t r[2][16];
       if (ep.dbg != 2) tmem_ld_32x16(tbase, r[0]);
+      float ln_nmu = 0.f, ln_rstd = 1.f;           // EPI_TMA_LN: -mean and 1 / std of this thread's row
+      if (DIRECT == EPI_TMA_LN && row0 + lane < M) {
+        const float2 st = __ldg(reinterpret_cast<const float2 *>(ep.row_stats) + row0 + lane);
+        ln_nmu = -st.x;
+        ln_rstd = st.y;
+      }
 #pragma unroll
       for (int ch = 0; ch < 4; ++ch) {
         if (ep.dbg == 2) break;
         const int col = col0 + ch * 16;
-        float4 b4[4];
+        float4 b4[4], s4[DIRECT == EPI_TMA_LN ? 4 : 1];
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
+        for (int j = 0; j < 4; ++j) {
           b4[j] = (ep.bias && col + 4 * j < N) ? __ldg(reinterpret_cast<const float4 *>(ep.bias + col + 4 * j))
                                                : make_float4(0.f, 0.f, 0.f, 0.f);
+          if (DIRECT == EPI_TMA_LN)
+            s4[j] = col + 4 * j < N ? __ldg(reinterpret_cast<const float4 *>(ep.col_s + col + 4 * j)) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
         tmem_ld_wait();
         if (ch + 1 < 4) {
           tmem_ld_32x16(tbase + (ch + 1) * 16, r[(ch + 1) & 1]);
@@ -256,8 +270,15 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const uint32_t *rr = r[ch & 1] + 4 * j;
-          v[j] = make_float4(__uint_as_float(rr[0]) + b4[j].x, __uint_as_float(rr[1]) + b4[j].y,
-                             __uint_as_float(rr[2]) + b4[j].z, __uint_as_float(rr[3]) + b4[j].w);
+          if (DIRECT == EPI_TMA_LN) {                // rstd (acc - mu colsum) + cfold
+            v[j] = make_float4(fmaf(ln_rstd, fmaf(ln_nmu, s4[j].x, __uint_as_float(rr[0])), b4[j].x),
+                               fmaf(ln_rstd, fmaf(ln_nmu, s4[j].y, __uint_as_float(rr[1])), b4[j].y),
+                               fmaf(ln_rstd, fmaf(ln_nmu, s4[j].z, __uint_as_float(rr[2])), b4[j].z),
+                               fmaf(ln_rstd, fmaf(ln_nmu, s4[j].w, __uint_as_float(rr[3])), b4[j].w));
+          } else {
+            v[j] = make_float4(__uint_as_float(rr[0]) + b4[j].x, __uint_as_float(rr[1]) + b4[j].y,
+                               __uint_as_float(rr[2]) + b4[j].z, __uint_as_float(rr[3]) + b4[j].w);
+          }
           if (GELU) gelu4(v[j]);
         }
         uint8_t *blk = stg + (RES ? (ch >> 1) * 2048 : 0);
@@ -453,6 +474,7 @@ void init_once() {
   X(false, T_BF16, 0, 16, EPI_LSU) X(false, T_F32, 0, 16, EPI_LSU) X(true, T_BF16, 0, 16, EPI_LSU) X(true, T_F32, 0, 16, EPI_LSU) \
   X(false, T_F16, 0, 16, EPI_LSU)                                                                                  \
   X(false, T_BF16, 0, 16, EPI_TMA) X(true, T_BF16, 0, 16, EPI_TMA) X(false, T_F16, 0, 16, EPI_TMA_RES)             \
+  X(false, T_BF16, 0, 16, EPI_TMA_LN) X(true, T_BF16, 0, 16, EPI_TMA_LN)                                              \
   X(false, T_BF16, 1, 8, EPI_LSU) X(false, T_F32, 1, 8, EPI_LSU) X(true, T_BF16, 1, 8, EPI_LSU) X(true, T_F32, 1, 8, EPI_LSU)     \
   X(false, T_F16, 1, 8, EPI_LSU)
 int init_device() {
@@ -529,7 +551,10 @@ int yv_gemm_launch(const void *A, const void *W, int M, int N, int K, const Gemm
   static const int force = []() { const char *e = getenv("YV_GEMM_EPI_WARPS"); return e ? atoi(e) : 0; }();
   const bool w16 = force != 8 || ep.out_type == T_F16;
   static const bool direct = []() { const char *e = getenv("YV_GEMM_TMA_STORE"); return !(e && e[0] == '0'); }();
-  const bool tma_out = direct && !extra && !tma_res && ep.out_type == T_BF16;
+  const bool lnfold = ep.row_stats != nullptr;       // A and W are fp16 here (the caller packs them so)
+  YV_REQUIRE(!lnfold || (ep.col_s && ep.bias && !extra && !tma_res && ep.out_type == T_BF16),
+             "yv_gemm: the folded-LayerNorm form needs col_s and bias, a bf16 output and no residual");
+  const bool tma_out = (direct || lnfold) && !extra && !tma_res && ep.out_type == T_BF16;
   CUtensorMap tmD = tmA, tmR = tmA;            // placeholders unless a TMA epilogue runs
   if (tma_out && (rc = make_tmap(&tmD, ep.out, (uint64_t)M, (uint64_t)N, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B))) return rc;
   if (tma_res) {
@@ -537,7 +562,9 @@ int yv_gemm_launch(const void *A, const void *W, int M, int N, int K, const Gemm
     if ((rc = make_tmap(&tmR, ep.residual, (uint64_t)M, (uint64_t)N, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_DATA_TYPE_FLOAT16))) return rc;
   }
 #define YV_GO(G, O, X, W, D) gemm_bf16_kernel<G, O, X, W, D><<<grid, gemm_threads(W), smem_bytes(W, D), s>>>(tmA, tmB, tmD, tmR, ep, M, N, K)
-  if (tma_res) {
+  if (lnfold) {
+    if (ep.gelu) YV_GO(true, T_BF16, 0, 16, EPI_TMA_LN); else YV_GO(false, T_BF16, 0, 16, EPI_TMA_LN);
+  } else if (tma_res) {
     YV_GO(false, T_F16, 0, 16, EPI_TMA_RES);
   } else if (tma_out) {
     if (ep.gelu) YV_GO(true, T_BF16, 0, 16, EPI_TMA); else YV_GO(false, T_BF16, 0, 16, EPI_TMA);

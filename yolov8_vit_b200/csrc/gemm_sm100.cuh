@@ -14,6 +14,11 @@ struct GemmEpilogue {
   bool gelu;
   int out_type;                     // 0 bf16, 1 f32, 2 f16
   int res_type;                     // 0 bf16, 1 f32 (LSU epilogue), 2 f16 (fused TMA residual: needs out_type 2, no GELU)
+  // LayerNorm folded into this Linear (EPI_TMA_LN): A is the raw fp16 stream, W = fp16(g (.) W_orig),
+  // D = rstd_m (acc - mu_m col_s[n]) + bias[n] with bias = b . W_orig^T + bias_orig, col_s[n] = sum_k W[n, k],
+  // row_stats[m] = (mu_m, rstd_m) from yv_row_stats_launch.  null = off.
+  const float *row_stats = nullptr;
+  const float *col_s = nullptr;
   int dbg = 0;                      // measurement only (YV_GEMM_DBG): 1 = no global stores, 2 = no epilogue work
 };
 

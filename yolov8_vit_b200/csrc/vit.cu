@@ -93,6 +93,7 @@ struct VitWs {
   void *x;                      // residual stream: f16 [M, dim] (default) or f32
   __nv_bfloat16 *y, *d, *d2, *qkv, *h, *cls_ln;      // d / d2: fp32-stream mode only
   float *hidden;
+  float *stats;                 // folded-LayerNorm mode: (mean, rstd) per token row
   size_t total;
 };
 
@@ -100,6 +101,12 @@ struct VitWs {
 bool vit_stream_f32() {
   static const bool f32 = []() { const char *e = getenv("YV_VIT_STREAM"); return e && (e[0] == 'f' || e[0] == 'F') && e[1] == '3'; }();
   return f32;
+}
+
+// LayerNorm folded into the qkv / fc1 GEMMs (default for the fp16 stream; YV_VIT_LNFOLD=0 runs the LayerNorm kernels)
+bool vit_lnfold() {
+  static const bool on = []() { const char *e = getenv("YV_VIT_LNFOLD"); return !(e && e[0] == '0'); }();
+  return on && !vit_stream_f32();
 }
 
 VitWs vit_ws(const yv_vit *m, void *base, int chunk) {
@@ -120,6 +127,7 @@ VitWs vit_ws(const yv_vit *m, void *base, int chunk) {
   w.h = (__nv_bfloat16 *)(b + o);      o = yv_align_up(o + M * c.mlp * 2, 1024);
   w.cls_ln = (__nv_bfloat16 *)(b + o); o = yv_align_up(o + (size_t)chunk * c.dim * 2, 1024);
   w.hidden = (float *)(b + o);         o = yv_align_up(o + (size_t)chunk * c.head_out * 4, 1024);
+  w.stats = (float *)(b + o);          o = yv_align_up(o + M * 2 * 4, 1024);
   w.total = o;
   return w;
 }
@@ -146,6 +154,19 @@ int finalize(yv_vit *m, cudaStream_t s) {
                                                    m->F("model.patch_embed.proj.bias"), m->wf + m->pos_table_off,
                                                    m->T, m->cfg.dim);
   YV_LAUNCH_CHECK();
+  if (vit_lnfold()) {
+    const int D = m->cfg.dim;
+    for (int i = 0; i < m->cfg.depth; ++i) {
+      const std::string p = "model.blocks." + std::to_string(i) + ".";
+      int rc;
+      if ((rc = yv_fold_ln_launch(m->B(p + "attn.qkv.weight"), m->F(p + "attn.qkv.bias"), m->F(p + "norm1.weight"), m->F(p + "norm1.bias"),
+                                  3 * D, D, m->wb + m->params.at(p + "norm1.fold.w").off, m->wf + m->params.at(p + "norm1.fold.s").off,
+                                  m->wf + m->params.at(p + "norm1.fold.c").off, s))) return rc;
+      if ((rc = yv_fold_ln_launch(m->B(p + "mlp.fc1.weight"), m->F(p + "mlp.fc1.bias"), m->F(p + "norm2.weight"), m->F(p + "norm2.bias"),
+                                  m->cfg.mlp, D, m->wb + m->params.at(p + "norm2.fold.w").off, m->wf + m->params.at(p + "norm2.fold.s").off,
+                                  m->wf + m->params.at(p + "norm2.fold.c").off, s))) return rc;
+    }
+  }
   m->finalized = true;
   return YV_OK;
 }
@@ -183,6 +204,14 @@ YV_EXPORT int yv_vit_create(const yv_vit_config *cfg, yv_vit_t **out) {
     add_param(m, p + "mlp.fc1.bias", c.mlp, false);
     add_param(m, p + "mlp.fc2.weight", D * c.mlp, true);
     add_param(m, p + "mlp.fc2.bias", D, false);
+    if (vit_lnfold()) {            // fp16 g (.) W (kept in the 16-bit arena), column sums, folded bias: finalize()
+      add_param(m, p + "norm1.fold.w", 3 * D * D, true, true);
+      add_param(m, p + "norm1.fold.s", 3 * D, false, true);
+      add_param(m, p + "norm1.fold.c", 3 * D, false, true);
+      add_param(m, p + "norm2.fold.w", (size_t)c.mlp * D, true, true);
+      add_param(m, p + "norm2.fold.s", c.mlp, false, true);
+      add_param(m, p + "norm2.fold.c", c.mlp, false, true);
+    }
   }
   add_param(m, "model.norm.weight", D, false);
   add_param(m, "model.norm.bias", D, false);
@@ -280,19 +309,35 @@ YV_EXPORT int yv_vit_forward(yv_vit_t *m, const void *patches_bf16, int n, float
     if ((rc = yv_gemm_launch(patches, m->B("model.patch_embed.proj.weight"), cc * NP, D, m->pdim, ep, s))) return rc;
     if ((rc = yv_cls_rows_launch(w.x, !f32, pos_table, cc, T, D, s))) return rc;
     if (!f32) {
-      // fp16 residual stream, updated in place by the proj / fc2 epilogues (residual boxes in and sums out by TMA):
-      // per block and stream element LayerNorm moves 2 x (2 B in + 2 B out) and the two updates 2 x (2 + 2) B.
+      // fp16 residual stream, updated in place by the proj / fc2 epilogues (residual boxes in and sums out by TMA).
+      // Default: the two LayerNorms of a block are FOLDED into the qkv / fc1 GEMMs -- the GEMM reads the fp16 stream
+      // itself against fp16 g (.) W and its epilogue applies rstd (acc - mu colsum) + c; a statistics kernel reads the
+      // stream once (2 B per element, no write).  YV_VIT_LNFOLD=0: LayerNorm kernels (2 B in + 2 B out) into w.y.
+      const bool fold = vit_lnfold();
+      const __nv_bfloat16 *x16 = (const __nv_bfloat16 *)w.x;      // 16-bit rows; the instruction descriptor says f16
       for (int i = 0; i < c.depth; ++i) {
         const std::string p = "model.blocks." + std::to_string(i) + ".";
-        if ((rc = yv_ln_launch(w.x, XT, D, nullptr, 0, false, m->F(p + "norm1.weight"), m->F(p + "norm1.bias"), w.y, M, D, c.eps, s))) return rc;
-        ep = GemmEpilogue{w.qkv, m->F(p + "attn.qkv.bias"), nullptr, nullptr, 0, false, 0, 0};
-        if ((rc = yv_gemm_launch(w.y, m->B(p + "attn.qkv.weight"), M, 3 * D, D, ep, s))) return rc;
+        if (fold) {
+          if ((rc = yv_row_stats_launch(w.x, D, w.stats, M, D, c.eps, s))) return rc;
+          ep = GemmEpilogue{w.qkv, m->F(p + "norm1.fold.c"), nullptr, nullptr, 0, false, 0, 0, w.stats, m->F(p + "norm1.fold.s")};
+          if ((rc = yv_gemm_launch(x16, m->B(p + "norm1.fold.w"), M, 3 * D, D, ep, s))) return rc;
+        } else {
+          if ((rc = yv_ln_launch(w.x, XT, D, nullptr, 0, false, m->F(p + "norm1.weight"), m->F(p + "norm1.bias"), w.y, M, D, c.eps, s))) return rc;
+          ep = GemmEpilogue{w.qkv, m->F(p + "attn.qkv.bias"), nullptr, nullptr, 0, false, 0, 0};
+          if ((rc = yv_gemm_launch(w.y, m->B(p + "attn.qkv.weight"), M, 3 * D, D, ep, s))) return rc;
+        }
         if ((rc = yv_attention_launch(w.qkv, w.y, cc, T, c.heads, D / c.heads, s))) return rc;
         ep = GemmEpilogue{w.x, m->F(p + "attn.proj.bias"), w.x, nullptr, 0, false, 2, 2};
         if ((rc = yv_gemm_launch(w.y, m->B(p + "attn.proj.weight"), M, D, D, ep, s))) return rc;
-        if ((rc = yv_ln_launch(w.x, XT, D, nullptr, 0, false, m->F(p + "norm2.weight"), m->F(p + "norm2.bias"), w.y, M, D, c.eps, s))) return rc;
-        ep = GemmEpilogue{w.h, m->F(p + "mlp.fc1.bias"), nullptr, nullptr, 0, true, 0, 0};
-        if ((rc = yv_gemm_launch(w.y, m->B(p + "mlp.fc1.weight"), M, c.mlp, D, ep, s))) return rc;
+        if (fold) {
+          if ((rc = yv_row_stats_launch(w.x, D, w.stats, M, D, c.eps, s))) return rc;
+          ep = GemmEpilogue{w.h, m->F(p + "norm2.fold.c"), nullptr, nullptr, 0, true, 0, 0, w.stats, m->F(p + "norm2.fold.s")};
+          if ((rc = yv_gemm_launch(x16, m->B(p + "norm2.fold.w"), M, c.mlp, D, ep, s))) return rc;
+        } else {
+          if ((rc = yv_ln_launch(w.x, XT, D, nullptr, 0, false, m->F(p + "norm2.weight"), m->F(p + "norm2.bias"), w.y, M, D, c.eps, s))) return rc;
+          ep = GemmEpilogue{w.h, m->F(p + "mlp.fc1.bias"), nullptr, nullptr, 0, true, 0, 0};
+          if ((rc = yv_gemm_launch(w.y, m->B(p + "mlp.fc1.weight"), M, c.mlp, D, ep, s))) return rc;
+        }
         ep = GemmEpilogue{w.x, m->F(p + "mlp.fc2.bias"), w.x, nullptr, 0, false, 2, 2};
         if ((rc = yv_gemm_launch(w.h, m->B(p + "mlp.fc2.weight"), M, D, c.mlp, ep, s))) return rc;
       }
@@ -336,4 +381,29 @@ YV_EXPORT int yv_vit_forward(yv_vit_t *m, const void *patches_bf16, int n, float
     }
   }
   return YV_OK;
+}
+
+// LayerNorm -> Linear as one operator (the unit the ViT blocks are built from); see include/yv8vit.h.
+YV_EXPORT size_t yv_linear_ln_f16_ws_bytes(int M, int N, int K) {
+  if (M <= 0 || N <= 0 || K <= 0) return 0;
+  return yv_align_up((size_t)N * K * 2, 1024) + 2 * yv_align_up((size_t)N * 4, 1024) + yv_align_up((size_t)M * 8, 1024);
+}
+
+YV_EXPORT int yv_linear_ln_f16(const void *x, const void *W, const float *bias, const float *gamma, const float *beta,
+                               void *D, int M, int N, int K, float eps, int epi, void *ws, size_t ws_bytes,
+                               yv_stream_t stream) {
+  YV_REQUIRE(x && W && bias && gamma && beta && D && ws, "yv_linear_ln_f16: null pointer");
+  YV_REQUIRE(epi == YV_EPI_NONE || epi == YV_EPI_GELU, "yv_linear_ln_f16: unknown epilogue %d", epi);
+  YV_REQUIRE(M >= 1 && N >= 1 && ws_bytes >= yv_linear_ln_f16_ws_bytes(M, N, K), "yv_linear_ln_f16: workspace too small");
+  cudaStream_t s = (cudaStream_t)stream;
+  char *b = (char *)ws;
+  void *wf16 = b;                      b += yv_align_up((size_t)N * K * 2, 1024);
+  float *colsum = (float *)b;          b += yv_align_up((size_t)N * 4, 1024);
+  float *cf = (float *)b;              b += yv_align_up((size_t)N * 4, 1024);
+  float *stats = (float *)b;
+  int rc;
+  if ((rc = yv_fold_ln_launch((const __nv_bfloat16 *)W, bias, gamma, beta, N, K, wf16, colsum, cf, s))) return rc;
+  if ((rc = yv_row_stats_launch(x, (size_t)K, stats, M, K, eps, s))) return rc;
+  GemmEpilogue ep{D, cf, nullptr, nullptr, 0, epi == YV_EPI_GELU, 0, 0, stats, colsum};
+  return yv_gemm_launch((const __nv_bfloat16 *)x, (const __nv_bfloat16 *)wf16, M, N, K, ep, s);
 }

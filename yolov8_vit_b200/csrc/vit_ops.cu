@@ -215,6 +215,90 @@ layernorm_f16_kernel(const __half *__restrict__ x, size_t in_stride, const float
   }
 }
 
+// Row statistics of the fp16 residual stream for the LayerNorm that is folded into the next Linear (gemm_sm100.cu,
+// EPI_TMA_LN): stats[row] = (mean, 1 / sqrt(var + eps)), two-pass on registers like the LayerNorm kernels.  The
+// stream is only READ (2 B per element); nothing of its size is written.
+template <int NCH>
+__global__ void __launch_bounds__(LN_WARPS * 32, 2)
+row_stats_f16_kernel(const __half *__restrict__ x, size_t in_stride, float2 *__restrict__ stats, int rows, float eps) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  constexpr int dim = 256 * NCH, R = NCH <= 2 ? 8 : (NCH == 3 ? 6 : 4);      // rows per warp and trip (72 registers of loads in flight at most)
+  const int ngrp = (rows + LN_WARPS * R - 1) / (LN_WARPS * R);
+  for (int gi = blockIdx.x; gi < ngrp; gi += gridDim.x) {
+    const int row0 = (gi * LN_WARPS + warp) * R;
+    uint4 raw[R][NCH];
+#pragma unroll
+    for (int r = 0; r < R; ++r)
+#pragma unroll
+      for (int c = 0; c < NCH; ++c)
+        if (row0 + r < rows)
+          raw[r][c] = __ldcs(reinterpret_cast<const uint4 *>(x + (size_t)(row0 + r) * in_stride + c * 256 + lane * 8));
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+      if (row0 + r >= rows) continue;              // warp-uniform
+      float sum = 0.f;
+#pragma unroll
+      for (int c = 0; c < NCH; ++c) {
+        const __half2 *h = reinterpret_cast<const __half2 *>(&raw[r][c]);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const float2 f = __half22float2(h[k]);
+          sum += f.x + f.y;
+        }
+      }
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, d);
+      const float mean = sum / (float)dim;
+      float sq = 0.f;
+#pragma unroll
+      for (int c = 0; c < NCH; ++c) {
+        const __half2 *h = reinterpret_cast<const __half2 *>(&raw[r][c]);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const float2 f = __half22float2(h[k]);
+          const float d0 = f.x - mean, d1 = f.y - mean;
+          sq += d0 * d0 + d1 * d1;
+        }
+      }
+#pragma unroll
+      for (int d = 16; d > 0; d >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, d);
+      if (lane == 0) stats[row0 + r] = make_float2(mean, rsqrtf(sq / (float)dim + eps));
+    }
+  }
+}
+
+// One-off weight fold of a LayerNorm (g, beta) into the Linear (w, bias) that follows it, one block per output feature:
+//   wf[n, k] = fp16(g[k] w[n, k]),  colsum[n] = sum_k wf[n, k] (of the ROUNDED values the tensor cores will see),
+//   cf[n] = bias[n] + sum_k beta[k] w[n, k]     so that   Linear(LN(x)) = rstd (x . wf^T - mu colsum) + cf.
+__global__ void __launch_bounds__(256)
+fold_ln_f16_kernel(const __nv_bfloat16 *__restrict__ w, const float *__restrict__ bias, const float *__restrict__ g,
+                   const float *__restrict__ beta, int K, __half *__restrict__ wf, float *__restrict__ colsum,
+                   float *__restrict__ cf) {
+  const int n = blockIdx.x;
+  float s = 0.f, c = 0.f;
+  for (int k = threadIdx.x; k < K; k += 256) {
+    const float wv = __bfloat162float(w[(size_t)n * K + k]);
+    const __half f = __float2half_rn(g[k] * wv);
+    wf[(size_t)n * K + k] = f;
+    s += __half2float(f);
+    c += beta[k] * wv;
+  }
+  __shared__ float sh[2][8];
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, d);
+    c += __shfl_xor_sync(0xffffffffu, c, d);
+  }
+  if ((threadIdx.x & 31) == 0) { sh[0][threadIdx.x >> 5] = s; sh[1][threadIdx.x >> 5] = c; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float ts = 0.f, tc = 0.f;
+    for (int i = 0; i < 8; ++i) { ts += sh[0][i]; tc += sh[1][i]; }
+    colsum[n] = ts;
+    cf[n] = bias[n] + tc;
+  }
+}
+
 // ------------------------------------------------------------------------------------ cls rows
 template <typename XT>
 __global__ void cls_rows_kernel(XT *__restrict__ x, const float *__restrict__ cls_pos0, int n, int T, int dim) {
@@ -353,6 +437,30 @@ int yv_ln2_launch(const void *x, int x_type, size_t in_stride, const __nv_bfloat
     else layernorm_f16_kernel<4><<<g16, LN_WARPS * 32, 0, s>>>((const __half *)x, in_stride, gamma, beta, y, rows, eps);
   }
   else layernorm_kernel<0><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, nullptr, nullptr, 0, 0, gamma, beta, y, rows, dim, eps, rev);
+  YV_LAUNCH_CHECK();
+  return YV_OK;
+}
+
+int yv_row_stats_launch(const void *x16, size_t in_stride, float *stats, int rows, int dim, float eps, cudaStream_t s) {
+  YV_REQUIRE(rows >= 1 && dim % 256 == 0 && dim >= 256 && dim <= 1024 && in_stride % 8 == 0, "row_stats: dim=%d unsupported", dim);
+  YvProf prof(YV_K_LN, s, (double)rows * dim * 2.0);
+  const int R = dim <= 512 ? 8 : (dim == 768 ? 6 : 4);          // = the kernel's R
+  int grid = (rows + LN_WARPS * R - 1) / (LN_WARPS * R);
+  if (grid > yv_num_sms() * 2) grid = yv_num_sms() * 2;
+  float2 *st = reinterpret_cast<float2 *>(stats);
+  const __half *x = (const __half *)x16;
+  if (dim == 768) row_stats_f16_kernel<3><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, st, rows, eps);
+  else if (dim == 256) row_stats_f16_kernel<1><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, st, rows, eps);
+  else if (dim == 512) row_stats_f16_kernel<2><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, st, rows, eps);
+  else row_stats_f16_kernel<4><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, st, rows, eps);
+  YV_LAUNCH_CHECK();
+  return YV_OK;
+}
+
+int yv_fold_ln_launch(const __nv_bfloat16 *w, const float *bias, const float *g, const float *beta, int N, int K,
+                      void *wf16, float *colsum, float *cf, cudaStream_t s) {
+  YvProf prof(YV_K_MISC, s, 0.0);
+  fold_ln_f16_kernel<<<N, 256, 0, s>>>(w, bias, g, beta, K, (__half *)wf16, colsum, cf);
   YV_LAUNCH_CHECK();
   return YV_OK;
 }

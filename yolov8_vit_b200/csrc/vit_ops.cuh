@@ -28,6 +28,12 @@ int yv_attention_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, int
 int yv_attention_fa_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, int T, int heads, int dh,
                            cudaStream_t s);
 
+// LayerNorm folded into the next Linear: per-row (mean, rstd) of the fp16 stream -> stats [rows, 2] f32
+// (the stream is only read), and the one-off weight fold wf16 = fp16(g (.) w), colsum, cf = bias + beta . w^T.
+int yv_row_stats_launch(const void *x16, size_t in_stride, float *stats, int rows, int dim, float eps, cudaStream_t s);
+int yv_fold_ln_launch(const __nv_bfloat16 *w, const float *bias, const float *g, const float *beta, int N, int K,
+                      void *wf16, float *colsum, float *cf, cudaStream_t s);
+
 // x[c*T, :] = cls + pos[0]  (the class-token row of every crop); x is the residual stream, f32 or f16
 int yv_cls_rows_launch(void *x, bool x_f16, const float *cls_pos0, int n, int T, int dim, cudaStream_t s);
 

@@ -238,6 +238,22 @@ def gemm_bf16(a: torch.Tensor, w: torch.Tensor, bias=None, residual=None, gelu: 
     return d
 
 
+def linear_ln_f16(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor,
+                  eps: float = 1e-6, gelu: bool = False):
+    """[GELU](Linear(LayerNorm(x))): x [M,K] f16, w [N,K] bf16 -> bf16 [M,N], the LayerNorm folded into the GEMM."""
+    require_device(x)
+    assert x.dtype == torch.float16 and w.dtype == torch.bfloat16
+    x, w = x.contiguous(), w.contiguous()
+    M, K = x.shape
+    N = w.shape[0]
+    lib = load()
+    ws = torch.empty(int(lib.yv_linear_ln_f16_ws_bytes(M, N, K)), dtype=torch.uint8, device=x.device)
+    d = torch.empty(M, N, dtype=torch.bfloat16, device=x.device)
+    check(lib.yv_linear_ln_f16(ptr(x), ptr(w), ptr(bias), ptr(gamma), ptr(beta), ptr(d), M, N, K, float(eps),
+                               1 if gelu else 0, ptr(ws), ws.numel(), stream_ptr(x.device)), "yv_linear_ln_f16")
+    return d
+
+
 def layernorm_bf16(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float = 1e-6):
     require_device(x)
     assert x.dtype == torch.bfloat16
