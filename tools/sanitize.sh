@@ -7,7 +7,7 @@
 set -u
 mkdir -p gpurun_out
 TOOLS=${*:-"memcheck racecheck initcheck"}
-SEL='nms_golden or nms_cfg2 or decode_golden or decode_cfg2 or dilate_golden or crop_golden or build_crops or gemm_plain or gemm_epilogues or gemm_fp16 or test_attention or test_layernorm or vit_tiny or letterbox'
+SEL='nms_golden or nms_cfg2 or decode_golden or decode_cfg2 or dilate_golden or crop_golden or build_crops or gemm_plain or gemm_epilogues or gemm_fp16 or folded_layernorm or test_attention or test_layernorm or vit_tiny or letterbox'
 rc_all=0
 for tool in $TOOLS; do
   log=gpurun_out/sanitize_${tool}.log

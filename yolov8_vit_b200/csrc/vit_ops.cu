@@ -217,53 +217,90 @@ layernorm_f16_kernel(const __half *__restrict__ x, size_t in_stride, const float
 
 // Row statistics of the fp16 residual stream for the LayerNorm that is folded into the next Linear (gemm_sm100.cu,
 // EPI_TMA_LN): stats[row] = (mean, 1 / sqrt(var + eps)), two-pass on registers like the LayerNorm kernels.  The
-// stream is only READ (2 B per element); nothing of its size is written.
+// stream is only READ (2 B per element); nothing of its size is written.  Software-pipelined: a warp holds two
+// groups of RS_ROWS rows and loads one while it reduces the other (the reduction -- conversions + 10 shuffles per
+// row -- is ~40 % of the load time and would otherwise sit between the loads).
+constexpr int RS_ROWS = 3;
+
 template <int NCH>
-__global__ void __launch_bounds__(LN_WARPS * 32, 2)
+__device__ __forceinline__ void rs_load(uint4 (&raw)[RS_ROWS][NCH], const __half *__restrict__ x, size_t in_stride,
+                                        int row0, int rows, int lane) {
+#pragma unroll
+  for (int r = 0; r < RS_ROWS; ++r)
+#pragma unroll
+    for (int c = 0; c < NCH; ++c)
+      if (row0 + r < rows)
+        raw[r][c] = __ldcs(reinterpret_cast<const uint4 *>(x + (size_t)(row0 + r) * in_stride + c * 256 + lane * 8));
+}
+
+template <int NCH>
+__device__ __forceinline__ void rs_reduce(const uint4 (&raw)[RS_ROWS][NCH], float2 *__restrict__ stats, int row0,
+                                          int rows, int lane, float eps) {
+  constexpr int dim = 256 * NCH;
+  float sum[RS_ROWS], sq[RS_ROWS];
+#pragma unroll
+  for (int r = 0; r < RS_ROWS; ++r) {
+    sum[r] = 0.f;
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) {
+      const __half2 *h = reinterpret_cast<const __half2 *>(&raw[r][c]);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float2 f = __half22float2(h[k]);
+        sum[r] += f.x + f.y;
+      }
+    }
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1)
+#pragma unroll
+    for (int r = 0; r < RS_ROWS; ++r) sum[r] += __shfl_xor_sync(0xffffffffu, sum[r], d);
+#pragma unroll
+  for (int r = 0; r < RS_ROWS; ++r) {
+    const float mean = sum[r] * (1.f / (float)dim);
+    sum[r] = mean;
+    sq[r] = 0.f;
+#pragma unroll
+    for (int c = 0; c < NCH; ++c) {
+      const __half2 *h = reinterpret_cast<const __half2 *>(&raw[r][c]);
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float2 f = __half22float2(h[k]);
+        const float d0 = f.x - mean, d1 = f.y - mean;
+        sq[r] = fmaf(d0, d0, fmaf(d1, d1, sq[r]));
+      }
+    }
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1)
+#pragma unroll
+    for (int r = 0; r < RS_ROWS; ++r) sq[r] += __shfl_xor_sync(0xffffffffu, sq[r], d);
+  if (lane < RS_ROWS && row0 + lane < rows) {
+    float m = sum[0], q = sq[0];
+#pragma unroll
+    for (int r = 1; r < RS_ROWS; ++r)
+      if (lane == r) { m = sum[r]; q = sq[r]; }
+    stats[row0 + lane] = make_float2(m, rsqrtf(q * (1.f / (float)dim) + eps));
+  }
+}
+
+template <int NCH>
+__global__ void __launch_bounds__(LN_WARPS * 32, NCH <= 3 ? 2 : 1)
 row_stats_f16_kernel(const __half *__restrict__ x, size_t in_stride, float2 *__restrict__ stats, int rows, float eps) {
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-  constexpr int dim = 256 * NCH, R = NCH <= 2 ? 8 : (NCH == 3 ? 6 : 4);      // rows per warp and trip (72 registers of loads in flight at most)
-  const int ngrp = (rows + LN_WARPS * R - 1) / (LN_WARPS * R);
-  for (int gi = blockIdx.x; gi < ngrp; gi += gridDim.x) {
-    const int row0 = (gi * LN_WARPS + warp) * R;
-    uint4 raw[R][NCH];
-#pragma unroll
-    for (int r = 0; r < R; ++r)
-#pragma unroll
-      for (int c = 0; c < NCH; ++c)
-        if (row0 + r < rows)
-          raw[r][c] = __ldcs(reinterpret_cast<const uint4 *>(x + (size_t)(row0 + r) * in_stride + c * 256 + lane * 8));
-#pragma unroll
-    for (int r = 0; r < R; ++r) {
-      if (row0 + r >= rows) continue;              // warp-uniform
-      float sum = 0.f;
-#pragma unroll
-      for (int c = 0; c < NCH; ++c) {
-        const __half2 *h = reinterpret_cast<const __half2 *>(&raw[r][c]);
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const float2 f = __half22float2(h[k]);
-          sum += f.x + f.y;
-        }
-      }
-#pragma unroll
-      for (int d = 16; d > 0; d >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, d);
-      const float mean = sum / (float)dim;
-      float sq = 0.f;
-#pragma unroll
-      for (int c = 0; c < NCH; ++c) {
-        const __half2 *h = reinterpret_cast<const __half2 *>(&raw[r][c]);
-#pragma unroll
-        for (int k = 0; k < 4; ++k) {
-          const float2 f = __half22float2(h[k]);
-          const float d0 = f.x - mean, d1 = f.y - mean;
-          sq += d0 * d0 + d1 * d1;
-        }
-      }
-#pragma unroll
-      for (int d = 16; d > 0; d >>= 1) sq += __shfl_xor_sync(0xffffffffu, sq, d);
-      if (lane == 0) stats[row0 + r] = make_float2(mean, rsqrtf(sq / (float)dim + eps));
-    }
+  const int ngrp = (rows + LN_WARPS * RS_ROWS - 1) / (LN_WARPS * RS_ROWS);
+  const int step = gridDim.x;
+  uint4 a[RS_ROWS][NCH], b[RS_ROWS][NCH];
+  int gi = blockIdx.x;
+  if (gi < ngrp) rs_load<NCH>(a, x, in_stride, (gi * LN_WARPS + warp) * RS_ROWS, rows, lane);
+  while (gi < ngrp) {
+    const int g1 = gi + step, g2 = g1 + step;
+    if (g1 < ngrp) rs_load<NCH>(b, x, in_stride, (g1 * LN_WARPS + warp) * RS_ROWS, rows, lane);
+    rs_reduce<NCH>(a, stats, (gi * LN_WARPS + warp) * RS_ROWS, rows, lane, eps);
+    if (g1 >= ngrp) break;
+    if (g2 < ngrp) rs_load<NCH>(a, x, in_stride, (g2 * LN_WARPS + warp) * RS_ROWS, rows, lane);
+    rs_reduce<NCH>(b, stats, (g1 * LN_WARPS + warp) * RS_ROWS, rows, lane, eps);
+    gi = g2;
   }
 }
 
@@ -444,9 +481,9 @@ int yv_ln2_launch(const void *x, int x_type, size_t in_stride, const __nv_bfloat
 int yv_row_stats_launch(const void *x16, size_t in_stride, float *stats, int rows, int dim, float eps, cudaStream_t s) {
   YV_REQUIRE(rows >= 1 && dim % 256 == 0 && dim >= 256 && dim <= 1024 && in_stride % 8 == 0, "row_stats: dim=%d unsupported", dim);
   YvProf prof(YV_K_LN, s, (double)rows * dim * 2.0);
-  const int R = dim <= 512 ? 8 : (dim == 768 ? 6 : 4);          // = the kernel's R
-  int grid = (rows + LN_WARPS * R - 1) / (LN_WARPS * R);
-  if (grid > yv_num_sms() * 2) grid = yv_num_sms() * 2;
+  int grid = (rows + LN_WARPS * RS_ROWS - 1) / (LN_WARPS * RS_ROWS);
+  static const int per_sm = []() { const char *e = getenv("YV_STATS_CTAS"); int v = e ? atoi(e) : 0; return v > 0 ? v : 2; }();
+  if (grid > yv_num_sms() * per_sm) grid = yv_num_sms() * per_sm;
   float2 *st = reinterpret_cast<float2 *>(stats);
   const __half *x = (const __half *)x16;
   if (dim == 768) row_stats_f16_kernel<3><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, st, rows, eps);
