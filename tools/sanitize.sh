@@ -11,7 +11,7 @@ SEL='nms_golden or nms_cfg2 or decode_golden or decode_cfg2 or dilate_golden or 
 rc_all=0
 for tool in $TOOLS; do
   log=gpurun_out/sanitize_${tool}.log
-  timeout 2400 compute-sanitizer --tool $tool --error-exitcode 9 --launch-timeout 600 \
+  timeout ${SAN_TIMEOUT:-700} compute-sanitizer --tool $tool --error-exitcode 9 --launch-timeout 600 \
       python -m pytest tests/test_gpu_ops.py tests/test_gpu_gemm.py tests/test_gpu_vit.py -m gpu -q -x -k "$SEL" > $log 2>&1
   rc=$?
   [ $rc -ne 0 ] && rc_all=$rc
