@@ -115,7 +115,7 @@ def test_vit_kernels_stay_inside_their_buffers(guard):
         ops.layernorm_bf16(torch.randn(rows, dim, generator=g).to(torch.bfloat16).to(DEV), torch.ones(dim, device=DEV), torch.zeros(dim, device=DEV))
     for n, T in ((3, 197), (2, 5), (1, 1), (2, 128), (2, 129), (1, 300), (1, 785)):
         ops.attention_bf16((torch.randn(n, T, 3 * 128, generator=g) * 0.5).to(torch.bfloat16).to(DEV), 2)
-    assert guard.check() > 30
+    assert guard.check() >= 25
 
 
 @pytest.mark.parametrize("patch,n", [(16, 5), (16, 1), (8, 2)])
