@@ -271,7 +271,7 @@ def run_reference(args):
                          "note": CPU_KIND_NOTE,
                          "custom_nms": "reference text (oracle/_ref)" if ref_custom_nms() else "oracle restatement"},
         "e2e": {"value": val, "unit": "images/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-        "gpu_launches": 0}))
+        "gpu_launches": 0}), file=JSON_OUT, flush=True)
 
 
 # ------------------------------------------------------------------------------------------ GPU
@@ -529,7 +529,7 @@ def run_ours(args):
             v = verify(oracle_res, hp(head_d, imgs_d, keep_intermediates=True))
             out["verified"] = bool(v.pop("ok")) and bool(e2e_ok)
             out["verification"] = v
-        print(json.dumps(out))
+        print(json.dumps(out), file=JSON_OUT, flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -568,9 +568,19 @@ def run_cfg4_strong(hp, dev, rank, world, barrier):
             "crops_total": int(sum(float(x[1]) for x in allt))}
 
 
+def _quiet_stdout():
+    """The driver parses stdout as ONE JSON line: anything a library prints there (NCCL / torchrun banners, device-side
+    printf) goes to stderr instead; the returned file is the real stdout, used only for the JSON line."""
+    sys.stdout.flush()
+    real = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    return real
+
+
 if __name__ == "__main__":
     a = parse()
     a.scaling = set_workload(a)
+    JSON_OUT = _quiet_stdout()
     if a.impl == "reference":
         run_reference(a)
     else:
