@@ -118,6 +118,27 @@ int yv_nms_batched(const float *boxes, const float *scores,
                    int32_t *keep_counts, void *ws, size_t ws_bytes,
                    yv_stream_t stream);
 
+/* yv_nms_batched (custom_nms rule) WITHOUT a caller workspace and without any
+ * allocation: the kernel's scratch lives in a 4 MiB __device__ array inside the
+ * library (held by every GPU that loads the library until exit), for callers
+ * that cannot allocate -- code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc.  This entry point has NO counterpart in the
+ * reference.
+ * Limit: yv_nms_workspace_bytes(B, stride) <= YV_NMS_NOALLOC_BYTES, i.e. about
+ * 65 000 boxes per call (B x stride x 56 B); larger calls return YV_EINVAL with a
+ * message naming both sizes.  It calls no cudaMalloc / cudaFree / allocating
+ * library routine (and, unlike the other entry points, is not seen by the launch
+ * profiler, whose event pool may grow).  All calls on a device share the one
+ * array: calls that may overlap on the GPU (different streams without an
+ * ordering between them) RACE -- serialise them.  The array keeps the last
+ * call's contents; the kernel writes every element before it reads it, so
+ * nothing needs clearing.  Outputs and semantics are those of yv_nms_batched.   */
+#define YV_NMS_NOALLOC_BYTES (4u << 20)
+int yv_nms_batched_noalloc(const float *boxes, const float *scores,
+                           const int32_t *counts, int B, int stride, int n_all,
+                           float iou_thr, int max_keep, int32_t *keep,
+                           int32_t *keep_counts, yv_stream_t stream);
+
 /* Same kernel with the survivor rule selectable (row f4): YV_NMS_RULE_CUSTOM is
  * custom_nms (suppress unless iou < thr); YV_NMS_RULE_STANDARD is
  * torchvision.ops.nms / the engine's EfficientNMS plugin (suppress iff iou > thr;

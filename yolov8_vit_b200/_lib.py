@@ -19,7 +19,7 @@ LIB_PATH = os.path.join(_HERE, "libyv8vit.so")
 SYMBOLS = [
     "yv_version", "yv_last_error", "yv_check_device",
     "yv_decode_filter_workspace_bytes", "yv_decode_filter", "yv_decode_filter_raw", "yv_letterbox_geometry", "yv_letterbox_blob",
-    "yv_nms_workspace_bytes", "yv_nms_batched", "yv_nms_batched_rule",
+    "yv_nms_workspace_bytes", "yv_nms_batched", "yv_nms_batched_rule", "yv_nms_batched_noalloc",
     "yv_dilate_boxes", "yv_build_crops", "yv_crop_resize",
     "yv_vit_create", "yv_vit_destroy", "yv_vit_set_param", "yv_vit_missing_params",
     "yv_vit_workspace_bytes", "yv_vit_forward",
@@ -69,6 +69,8 @@ def load() -> ctypes.CDLL:
                                    c_void_p, c_void_p, c_size_t, c_void_p]
     lib.yv_nms_batched_rule.argtypes = [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_int, c_int,
                                         c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]
+    lib.yv_nms_batched_noalloc.argtypes = [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float, c_int, c_void_p,
+                                           c_void_p, c_void_p]
     lib.yv_dilate_boxes.argtypes = [c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p]
     lib.yv_build_crops.argtypes = [c_void_p] * 6 + [c_int] * 8 + [c_void_p] * 10 + [c_int, c_void_p, c_void_p]
     lib.yv_crop_resize.argtypes = [c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_void_p, c_int,

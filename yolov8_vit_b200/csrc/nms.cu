@@ -24,6 +24,7 @@
 // resulting offsets of the ONE global list.  Two cluster barriers per pass.
 #include "common.cuh"
 #include <cstdlib>
+#include <mutex>
 
 namespace {
 
@@ -413,4 +414,86 @@ YV_EXPORT int yv_nms_batched(const float *boxes, const float *scores, const int3
                              int32_t *keep_counts, void *ws, size_t ws_bytes, yv_stream_t stream) {
   return yv_nms_batched_rule(boxes, scores, counts, B, stride, n_all, iou_thr, max_keep, YV_NMS_RULE_CUSTOM, keep,
                              keep_counts, ws, ws_bytes, stream);
+}
+
+// ------------------------------------------------------------------------------------ no-allocation variant
+// yv_nms_batched_noalloc: the same kernels with their scratch (radix keys / indices and the two survivor lists,
+// 56 B per box) in a file-scope __device__ array instead of a caller workspace, for callers that cannot allocate
+// (CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Every GPU that loads the library holds the 4 MiB until exit.
+// In HOST code `g_nms_static_ws` is only a stand-in for the symbol, not a device address: the address is fetched
+// once per device with cudaGetSymbolAddress (with that device current) and passed to the kernel.
+static_assert(YV_NMS_NOALLOC_BYTES == (4u << 20), "include/yv8vit.h states 4 MiB");
+static __device__ __align__(256) unsigned char g_nms_static_ws[YV_NMS_NOALLOC_BYTES];
+
+namespace {
+constexpr int NOALLOC_MAX_DEVICES = 64;
+std::mutex g_noalloc_mu;
+void *g_noalloc_ptr[NOALLOC_MAX_DEVICES] = {};
+
+// device address of the scratch array on the CURRENT device (looked up once per device)
+int nms_static_ws(void **out) {
+  int dev = -1;
+  YV_CUDA(cudaGetDevice(&dev));
+  YV_REQUIRE(dev >= 0 && dev < NOALLOC_MAX_DEVICES, "yv_nms_batched_noalloc: device %d out of range", dev);
+  std::lock_guard<std::mutex> lk(g_noalloc_mu);
+  if (!g_noalloc_ptr[dev]) {
+    void *p = nullptr;
+    YV_CUDA(cudaGetSymbolAddress(&p, g_nms_static_ws));
+    YV_REQUIRE(p != nullptr && ((uintptr_t)p % 256) == 0, "yv_nms_batched_noalloc: bad scratch address %p", p);
+    g_noalloc_ptr[dev] = p;
+  }
+  *out = g_noalloc_ptr[dev];
+  return YV_OK;
+}
+}  // namespace
+
+YV_EXPORT int yv_nms_batched_noalloc(const float *boxes, const float *scores, const int32_t *counts, int B,
+                                     int stride, int n_all, float iou_thr, int max_keep, int32_t *keep,
+                                     int32_t *keep_counts, yv_stream_t stream) {
+  YV_REQUIRE(B >= 0 && stride >= 1, "yv_nms_batched_noalloc: bad shape B=%d stride=%d", B, stride);
+  if (B == 0) return YV_OK;
+  YV_REQUIRE(boxes && scores && keep && keep_counts, "yv_nms_batched_noalloc: null pointer");
+  YV_REQUIRE(((uintptr_t)boxes % 16) == 0, "yv_nms_batched_noalloc: boxes must be 16-byte aligned");
+  YV_REQUIRE(counts || (n_all >= 0 && n_all <= stride), "yv_nms_batched_noalloc: n_all=%d outside [0, stride=%d]", n_all, stride);
+  YV_REQUIRE(stride <= NMS_MAX_N, "yv_nms_batched_noalloc: stride=%d exceeds %d candidates per image", stride, NMS_MAX_N);
+  const NmsLayout L = nms_layout(B, stride);
+  if (L.total > (size_t)YV_NMS_NOALLOC_BYTES) {
+    yv_set_error("yv_nms_batched_noalloc: B=%d x stride=%d needs %zu B of scratch, the built-in array holds %u B "
+                 "(about 65 000 boxes per call); use yv_nms_batched with a caller workspace",
+                 B, stride, L.total, (unsigned)YV_NMS_NOALLOC_BYTES);
+    return YV_EINVAL;
+  }
+  void *ws = nullptr;
+  int rc = nms_static_ws(&ws);
+  if (rc) return rc;
+  char *w = (char *)ws;
+  NmsWs W;
+  for (int i = 0; i < 2; ++i) {
+    W.key[i] = (unsigned *)(w + L.o_key[i]);
+    W.idx[i] = (int32_t *)(w + L.o_idx[i]);
+    W.lidx[i] = (int32_t *)(w + L.o_lidx[i]);
+    W.lbox[i] = (float4 *)(w + L.o_lbox[i]);
+  }
+  // The kernel writes every scratch element before it reads it (sort keys, then the lists), so nothing has to be
+  // cleared between calls.  No launch profiler here: its event pool may create events (an allocation).
+  const bool cluster = !counts && n_all >= NMS_CLUSTER_MIN_N;      // the rule of yv_nms_batched
+  if (cluster) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)B * NMS_CLUSTER);
+    cfg.blockDim = dim3(NMS_T);
+    cfg.stream = (cudaStream_t)stream;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = NMS_CLUSTER; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    YV_CUDA(cudaLaunchKernelEx(&cfg, nms_kernel<NMS_CLUSTER>, (const float4 *)boxes, scores, counts, stride, n_all,
+                               iou_thr, max_keep, keep, keep_counts, W, (int)YV_NMS_RULE_CUSTOM));
+  } else {
+    nms_kernel<1><<<B, NMS_T, 0, (cudaStream_t)stream>>>((const float4 *)boxes, scores, counts, stride, n_all,
+                                                         iou_thr, max_keep, keep, keep_counts, W, (int)YV_NMS_RULE_CUSTOM);
+  }
+  YV_LAUNCH_CHECK();
+  return YV_OK;
 }

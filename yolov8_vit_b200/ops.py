@@ -126,6 +126,28 @@ def nms_batched(boxes: torch.Tensor, scores: torch.Tensor, counts: torch.Tensor 
     return keep, keep_counts
 
 
+NMS_NOALLOC_BYTES = 4 << 20          # include/yv8vit.h: YV_NMS_NOALLOC_BYTES
+
+
+def nms_batched_noalloc(boxes: torch.Tensor, scores: torch.Tensor, counts: torch.Tensor | None, keep: torch.Tensor,
+                        keep_counts: torch.Tensor, iou_threshold: float = 0.45, max_keep: int = 0):
+    """``nms_batched`` (custom_nms rule) through ``yv_nms_batched_noalloc``: the CALLER brings ``keep`` [B,S] i32 and
+    ``keep_counts`` [B] i32, the scratch is the library's built-in 4 MiB device array, and nothing is allocated here
+    or in the library (no counterpart in the reference; for callers that cannot allocate).  Calls on one device share
+    that array: do not overlap them on different streams.  B x S x 56 B must fit the array."""
+    require_device(boxes)
+    assert boxes.dtype == torch.float32 and scores.dtype == torch.float32
+    assert boxes.is_contiguous() and scores.is_contiguous() and keep.is_contiguous() and keep_counts.is_contiguous()
+    B, S = scores.shape
+    assert keep.dtype == torch.int32 and keep.shape == (B, S) and keep_counts.dtype == torch.int32 and keep_counts.shape == (B,)
+    if counts is not None:
+        assert counts.dtype == torch.int32 and counts.is_cuda
+    check(load().yv_nms_batched_noalloc(ptr(boxes), ptr(scores), ptr(counts), B, S, S, float(np.float32(iou_threshold)),
+                                        int(max_keep), ptr(keep), ptr(keep_counts), stream_ptr(boxes.device)),
+          "yv_nms_batched_noalloc")
+    return keep, keep_counts
+
+
 def efficient_nms(boxes: torch.Tensor, scores: torch.Tensor, labels: torch.Tensor, counts: torch.Tensor | None = None,
                   iou_threshold: float = 0.65, max_det: int = 100):
     """Row f4: the engine's class-aware EfficientNMS stage (iou .65, top-100;
