@@ -272,6 +272,17 @@ int yv_linear_ln_f16(const void *x, const void *W, const float *bias,
                      const float *gamma, const float *beta, void *D, int M,
                      int N, int K, float eps, int epi, void *ws, size_t ws_bytes,
                      yv_stream_t stream);
+/* x += A W^T + bias on the f16 residual stream x [M,N] IN PLACE (A bf16 [M,K], W
+ * bf16 [N,K]) -- attn.proj / mlp.fc2 of a timm Block followed by its residual
+ * add -- and, when stats != NULL, the (mean, 1/sqrt(var + eps)) pair of every
+ * UPDATED row into stats [M,2] f32 as a by-product of the GEMM epilogue (partial
+ * sums per 64 columns in ws, then a combine kernel), i.e. the statistics the next
+ * yv_linear_ln_f16-style GEMM needs without another pass over x.
+ * N % 64 == 0, N <= 1024; ws: yv_residual_linear_f16_ws_bytes(M, N).           */
+size_t yv_residual_linear_f16_ws_bytes(int M, int N);
+int yv_residual_linear_f16(const void *A, const void *W, const float *bias,
+                           void *x, int M, int N, int K, float eps, float *stats,
+                           void *ws, size_t ws_bytes, yv_stream_t stream);
 /* softmax(Q K^T / sqrt(dh)) V for qkv [n, T, 3, heads, dh] bf16 -> out
  * [n, T, heads*dh] bf16 (timm's qkv packing).                               */
 int yv_attention_bf16(const void *qkv, void *out, int n, int T, int heads,

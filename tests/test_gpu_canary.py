@@ -111,6 +111,10 @@ def test_vit_kernels_stay_inside_their_buffers(guard):
         x = torch.randn(M, K, generator=g).to(torch.float16).to(DEV)
         w = (torch.randn(N, K, generator=g) * 0.05).to(torch.bfloat16).to(DEV)
         ops.linear_ln_f16(x, w, torch.randn(N, generator=g).to(DEV), torch.ones(K, device=DEV), torch.zeros(K, device=DEV), 1e-6, True)
+    for M, N, K in ((130, 768, 64), (1, 256, 128), (259, 1024, 192)):
+        a = (torch.randn(M, K, generator=g) * 0.5).to(torch.bfloat16).to(DEV)
+        w = (torch.randn(N, K, generator=g) * 0.05).to(torch.bfloat16).to(DEV)
+        ops.residual_linear_f16(a, w, None, torch.randn(M, N, generator=g).to(torch.float16).to(DEV))
     for rows, dim in ((1, 768), (33, 256), (1001, 1024)):
         ops.layernorm_bf16(torch.randn(rows, dim, generator=g).to(torch.bfloat16).to(DEV), torch.ones(dim, device=DEV), torch.zeros(dim, device=DEV))
     for n, T in ((3, 197), (2, 5), (1, 1), (2, 128), (2, 129), (1, 300), (1, 785)):

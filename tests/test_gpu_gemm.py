@@ -136,3 +136,31 @@ def test_linear_with_folded_layernorm(M, N, K, gelu):
     e_fold = float((got.double() - ref).abs().max())
     e_two = float((two.double() - ref).abs().max())
     assert e_fold <= 1.5 * e_two + 1e-3, (e_fold, e_two)
+
+
+@pytest.mark.parametrize("M,N,K", [(197 * 5, 768, 768), (197 * 5, 768, 3072), (1000, 256, 128), (77, 1024, 192), (1, 768, 64)])
+def test_residual_update_with_row_statistics(M, N, K):
+    """yv_residual_linear_f16: x += a w^T + b in place (the fused TMA residual epilogue) with the (mean, rstd) of the
+    UPDATED rows as a by-product of the epilogue (partial sums per 64 columns + combine kernel).  The update must be
+    bit-identical to the same GEMM without statistics, and the statistics must match fp64 statistics of the stored
+    fp16 rows: the epilogue sums the fp32 values BEFORE their fp16 rounding, so the mean may differ by the average
+    rounding error (<= 2^-12 max|row|) and rstd by 1e-3 relative.  Rows carry a large common offset."""
+    g = torch.Generator().manual_seed(M + N + K)
+    a, w, bias = _mk(M, N, K, seed=M + K)
+    x0 = (torch.randn(M, N, generator=g) * (torch.rand(M, 1, generator=g) * 3 + 0.3) + 4.0 * torch.randn(M, 1, generator=g)).to(torch.float16).to(DEV)
+    x_plain = x0.clone()
+    ops.gemm_bf16(a, w, bias, residual=x_plain, out=x_plain)
+    x = x0.clone()
+    stats = ops.residual_linear_f16(a, w, bias, x)
+    assert torch.equal(x, x_plain)
+    ref = x0.double() + a.double() @ w.double().t() + bias.double()
+    _close(x, ref.float(), rtol=2 ** -10, atol=2e-3)
+    xd = x.double()
+    mean = xd.mean(1)
+    rstd = (xd.var(1, unbiased=False) + 1e-6).rsqrt()
+    tol_mean = 2.0 ** -12 * xd.abs().amax(1) + 1e-5
+    assert bool(((stats[:, 0].double() - mean).abs() <= tol_mean).all()), float((stats[:, 0].double() - mean).abs().max())
+    assert bool(((stats[:, 1].double() / rstd - 1).abs() <= 1e-3).all()), float((stats[:, 1].double() / rstd - 1).abs().max())
+    # without statistics the entry point is the plain in-place update
+    x2 = x0.clone()
+    assert ops.residual_linear_f16(a, w, bias, x2, want_stats=False) is None and torch.equal(x2, x_plain)

@@ -237,6 +237,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const uint32_t tbase = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + cg * EPI_COLS;
       uint32_t r[2][16];
       if (ep.dbg != 2) tmem_ld_32x16(tbase, r[0]);
+      float st_shift = 0.f;                        // EPI_TMA_RES + stats_part: shifted sums of this thread's 64 new values
+      uint64_t st_s1 = 0ull, st_s2 = 0ull;         // (packed fp32 pairs: even / odd columns)
       float ln_nmu = 0.f, ln_rstd = 1.f;           // EPI_TMA_LN: -mean and 1 / std of this thread's row
       if (DIRECT == EPI_TMA_LN && row0 + lane < M) {
         const float2 st = __ldg(reinterpret_cast<const float2 *>(ep.row_stats) + row0 + lane);
@@ -299,10 +301,19 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             const float2 x1 = __half22float2(*reinterpret_cast<const __half2 *>(&x.y));
             const float2 x2 = __half22float2(*reinterpret_cast<const __half2 *>(&x.z));
             const float2 x3 = __half22float2(*reinterpret_cast<const __half2 *>(&x.w));
-            u.x = pack_h2(v[2 * j].x + x0.x, v[2 * j].y + x0.y);
-            u.y = pack_h2(v[2 * j].z + x1.x, v[2 * j].w + x1.y);
-            u.z = pack_h2(v[2 * j + 1].x + x2.x, v[2 * j + 1].y + x2.y);
-            u.w = pack_h2(v[2 * j + 1].z + x3.x, v[2 * j + 1].w + x3.y);
+            const float f0 = v[2 * j].x + x0.x, f1 = v[2 * j].y + x0.y, f2 = v[2 * j].z + x1.x, f3 = v[2 * j].w + x1.y;
+            const float f4 = v[2 * j + 1].x + x2.x, f5 = v[2 * j + 1].y + x2.y, f6 = v[2 * j + 1].z + x3.x, f7 = v[2 * j + 1].w + x3.y;
+            if (ep.stats_part) {                     // statistics of the next LayerNorm, shifted by the row's first value
+              if (ch == 0 && j == 0) st_shift = f0;
+              const uint64_t sh = pk2(-st_shift, -st_shift);
+              const uint64_t d0 = add2(pk2(f0, f1), sh), d1 = add2(pk2(f2, f3), sh), d2 = add2(pk2(f4, f5), sh), d3 = add2(pk2(f6, f7), sh);
+              st_s1 = add2(add2(st_s1, add2(d0, d1)), add2(d2, d3));
+              st_s2 = fma2(d0, d0, fma2(d1, d1, fma2(d2, d2, fma2(d3, d3, st_s2))));
+            }
+            u.x = pack_h2(f0, f1);
+            u.y = pack_h2(f2, f3);
+            u.z = pack_h2(f4, f5);
+            u.w = pack_h2(f6, f7);
           } else {
             u.x = pack_b2(v[2 * j].x, v[2 * j].y);
             u.y = pack_b2(v[2 * j].z, v[2 * j].w);
@@ -321,6 +332,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
       }
       if (RES && box0) ++rit;
+      if (RES && ep.stats_part && box0 && row0 + lane < M) {
+        float a0, a1, q0, q1;
+        unpk2(st_s1, a0, a1);
+        unpk2(st_s2, q0, q1);
+        const float s1 = a0 + a1, s2 = q0 + q1;    // sum (x - shift), sum (x - shift)^2 over the 64 columns
+        reinterpret_cast<float2 *>(ep.stats_part)[(size_t)(col0 >> 6) * M + row0 + lane] =
+            make_float2(fmaf(64.f, st_shift, s1), fmaxf(fmaf(-s1 * (1.f / 64.f), s1, s2), 0.f));
+      }
       if (ep.dbg == 2) {                           // (measurement mode: nothing was read)
         if (RES && box0) mbar_wait(&rbar[ew], (rit - 1) & 1u);
         tc_fence_before();
@@ -551,6 +570,7 @@ int yv_gemm_launch(const void *A, const void *W, int M, int N, int K, const Gemm
   static const int force = []() { const char *e = getenv("YV_GEMM_EPI_WARPS"); return e ? atoi(e) : 0; }();
   const bool w16 = force != 8 || ep.out_type == T_F16;
   static const bool direct = []() { const char *e = getenv("YV_GEMM_TMA_STORE"); return !(e && e[0] == '0'); }();
+  YV_REQUIRE(!ep.stats_part || (tma_res && N % 64 == 0), "yv_gemm: partial row statistics need the fused fp16 residual epilogue and N %% 64 == 0");
   const bool lnfold = ep.row_stats != nullptr;       // A and W are fp16 here (the caller packs them so)
   YV_REQUIRE(!lnfold || (ep.col_s && ep.bias && !extra && !tma_res && ep.out_type == T_BF16),
              "yv_gemm: the folded-LayerNorm form needs col_s and bias, a bf16 output and no residual");

@@ -19,6 +19,10 @@ struct GemmEpilogue {
   // row_stats[m] = (mu_m, rstd_m) from yv_row_stats_launch.  null = off.
   const float *row_stats = nullptr;
   const float *col_s = nullptr;
+  // Fused TMA residual epilogue only: partial LayerNorm statistics of the UPDATED rows, one (sum, M2) pair per row and
+  // 64-column group, stats_part[(n / 64) * M + m] as float2 (M2 = sum of squares about the group's own mean); N % 64 == 0.
+  // yv_stats_finalize_launch combines the N / 64 groups of a row into (mean, rstd).  null = off.
+  float *stats_part = nullptr;
   int dbg = 0;                      // measurement only (YV_GEMM_DBG): 1 = no global stores, 2 = no epilogue work
 };
 

@@ -94,6 +94,7 @@ struct VitWs {
   __nv_bfloat16 *y, *d, *d2, *qkv, *h, *cls_ln;      // d / d2: fp32-stream mode only
   float *hidden;
   float *stats;                 // folded-LayerNorm mode: (mean, rstd) per token row
+  float *part;                  // ... and the partial statistics of the proj / fc2 epilogues, [dim / 64][M] float2
   size_t total;
 };
 
@@ -107,6 +108,13 @@ bool vit_stream_f32() {
 bool vit_lnfold() {
   static const bool on = []() { const char *e = getenv("YV_VIT_LNFOLD"); return !(e && e[0] == '0'); }();
   return on && !vit_stream_f32();
+}
+
+// Row statistics of the folded LayerNorms: by default they come out of the proj / fc2 GEMM epilogues (partial sums per
+// 64-column group + a tiny combine kernel); YV_VIT_STATS=kernel runs the stream-reading statistics kernel instead (A/B).
+bool vit_stats_fused() {
+  static const bool on = []() { const char *e = getenv("YV_VIT_STATS"); return !(e && (e[0] == 'k' || e[0] == 'K')); }();
+  return on;
 }
 
 VitWs vit_ws(const yv_vit *m, void *base, int chunk) {
@@ -128,6 +136,7 @@ VitWs vit_ws(const yv_vit *m, void *base, int chunk) {
   w.cls_ln = (__nv_bfloat16 *)(b + o); o = yv_align_up(o + (size_t)chunk * c.dim * 2, 1024);
   w.hidden = (float *)(b + o);         o = yv_align_up(o + (size_t)chunk * c.head_out * 4, 1024);
   w.stats = (float *)(b + o);          o = yv_align_up(o + M * 2 * 4, 1024);
+  w.part = (float *)(b + o);           o = yv_align_up(o + M * (size_t)(c.dim / 64) * 2 * 4, 1024);
   w.total = o;
   return w;
 }
@@ -314,11 +323,13 @@ YV_EXPORT int yv_vit_forward(yv_vit_t *m, const void *patches_bf16, int n, float
       // itself against fp16 g (.) W and its epilogue applies rstd (acc - mu colsum) + c; a statistics kernel reads the
       // stream once (2 B per element, no write).  YV_VIT_LNFOLD=0: LayerNorm kernels (2 B in + 2 B out) into w.y.
       const bool fold = vit_lnfold();
+      const bool fused = fold && vit_stats_fused();          // statistics out of the proj / fc2 epilogues
       const __nv_bfloat16 *x16 = (const __nv_bfloat16 *)w.x;      // 16-bit rows; the instruction descriptor says f16
       for (int i = 0; i < c.depth; ++i) {
         const std::string p = "model.blocks." + std::to_string(i) + ".";
         if (fold) {
-          if ((rc = yv_row_stats_launch(w.x, D, w.stats, M, D, c.eps, s))) return rc;
+          // block 0 reads the rows the patch embedding wrote; later blocks got their statistics from fc2's epilogue
+          if (!fused || i == 0) { if ((rc = yv_row_stats_launch(w.x, D, w.stats, M, D, c.eps, s))) return rc; }
           ep = GemmEpilogue{w.qkv, m->F(p + "norm1.fold.c"), nullptr, nullptr, 0, false, 0, 0, w.stats, m->F(p + "norm1.fold.s")};
           if ((rc = yv_gemm_launch(x16, m->B(p + "norm1.fold.w"), M, 3 * D, D, ep, s))) return rc;
         } else {
@@ -328,9 +339,11 @@ YV_EXPORT int yv_vit_forward(yv_vit_t *m, const void *patches_bf16, int n, float
         }
         if ((rc = yv_attention_launch(w.qkv, w.y, cc, T, c.heads, D / c.heads, s))) return rc;
         ep = GemmEpilogue{w.x, m->F(p + "attn.proj.bias"), w.x, nullptr, 0, false, 2, 2};
+        if (fused) ep.stats_part = w.part;
         if ((rc = yv_gemm_launch(w.y, m->B(p + "attn.proj.weight"), M, D, D, ep, s))) return rc;
         if (fold) {
-          if ((rc = yv_row_stats_launch(w.x, D, w.stats, M, D, c.eps, s))) return rc;
+          if (fused) { if ((rc = yv_stats_finalize_launch(w.part, M, D, c.eps, w.stats, s))) return rc; }
+          else if ((rc = yv_row_stats_launch(w.x, D, w.stats, M, D, c.eps, s))) return rc;
           ep = GemmEpilogue{w.h, m->F(p + "norm2.fold.c"), nullptr, nullptr, 0, true, 0, 0, w.stats, m->F(p + "norm2.fold.s")};
           if ((rc = yv_gemm_launch(x16, m->B(p + "norm2.fold.w"), M, c.mlp, D, ep, s))) return rc;
         } else {
@@ -339,7 +352,10 @@ YV_EXPORT int yv_vit_forward(yv_vit_t *m, const void *patches_bf16, int n, float
           if ((rc = yv_gemm_launch(w.y, m->B(p + "mlp.fc1.weight"), M, c.mlp, D, ep, s))) return rc;
         }
         ep = GemmEpilogue{w.x, m->F(p + "mlp.fc2.bias"), w.x, nullptr, 0, false, 2, 2};
+        const bool next = fused && i + 1 < c.depth;          // the last block feeds the class-row LayerNorm instead
+        if (next) ep.stats_part = w.part;
         if ((rc = yv_gemm_launch(w.h, m->B(p + "mlp.fc2.weight"), M, D, c.mlp, ep, s))) return rc;
+        if (next && (rc = yv_stats_finalize_launch(w.part, M, D, c.eps, w.stats, s))) return rc;
       }
       // final norm on the class-token rows only, then the heads
       if ((rc = yv_ln_launch(w.x, XT, (size_t)T * D, nullptr, 0, false, m->F("model.norm.weight"), m->F("model.norm.bias"), w.cls_ln, cc, D, c.eps, s))) return rc;
@@ -406,4 +422,24 @@ YV_EXPORT int yv_linear_ln_f16(const void *x, const void *W, const float *bias, 
   if ((rc = yv_row_stats_launch(x, (size_t)K, stats, M, K, eps, s))) return rc;
   GemmEpilogue ep{D, cf, nullptr, nullptr, 0, epi == YV_EPI_GELU, 0, 0, stats, colsum};
   return yv_gemm_launch((const __nv_bfloat16 *)x, (const __nv_bfloat16 *)wf16, M, N, K, ep, s);
+}
+
+// x += A W^T + b on an fp16 stream x [M,N] (in place) with the row statistics of the UPDATED rows as a by-product of
+// the GEMM epilogue -- the other half of a ViT block next to yv_linear_ln_f16; see include/yv8vit.h.
+YV_EXPORT size_t yv_residual_linear_f16_ws_bytes(int M, int N) {
+  if (M <= 0 || N <= 0) return 0;
+  return yv_align_up((size_t)M * (size_t)((N + 63) / 64) * 8, 1024);
+}
+
+YV_EXPORT int yv_residual_linear_f16(const void *A, const void *W, const float *bias, void *x, int M, int N, int K,
+                                     float eps, float *stats, void *ws, size_t ws_bytes, yv_stream_t stream) {
+  YV_REQUIRE(A && W && x, "yv_residual_linear_f16: null pointer");
+  YV_REQUIRE(M >= 1 && N >= 64 && N % 64 == 0 && N <= 1024, "yv_residual_linear_f16: N=%d (need a multiple of 64 up to 1024)", N);
+  YV_REQUIRE(!stats || (ws && ws_bytes >= yv_residual_linear_f16_ws_bytes(M, N)), "yv_residual_linear_f16: workspace too small");
+  cudaStream_t s = (cudaStream_t)stream;
+  GemmEpilogue ep{x, bias, x, nullptr, 0, false, 2, 2};
+  if (stats) ep.stats_part = (float *)ws;
+  int rc = yv_gemm_launch(A, W, M, N, K, ep, s);
+  if (rc || !stats) return rc;
+  return yv_stats_finalize_launch((const float *)ws, M, N, eps, stats, s);
 }

@@ -304,6 +304,34 @@ row_stats_f16_kernel(const __half *__restrict__ x, size_t in_stride, float2 *__r
   }
 }
 
+// Combines the per-(row, 64-column group) partial statistics written by the GEMM's fused residual epilogue
+// (gemm_sm100.cu, stats_part: (sum, M2 about the group's own mean), [groups][rows] float2) into the (mean, rstd) pair
+// per row the folded-LayerNorm epilogue reads: mean = sum_g sum_g / dim, M2 = sum_g (M2_g + 64 (mean_g - mean)^2)
+// (Chan's parallel update).  One thread per row, coalesced over rows: 8 B x groups read, 8 B written per row.
+__global__ void __launch_bounds__(256)
+stats_finalize_kernel(const float2 *__restrict__ part, int groups, int rows, float eps, float2 *__restrict__ stats) {
+  const int row = blockIdx.x * 256 + threadIdx.x;
+  if (row >= rows) return;
+  float2 p[16];
+  float sum = 0.f;
+#pragma unroll
+  for (int g = 0; g < 16; ++g)
+    if (g < groups) {
+      p[g] = __ldcs(part + (size_t)g * rows + row);
+      sum += p[g].x;
+    }
+  const float inv_dim = 1.f / (64.f * (float)groups);
+  const float mean = sum * inv_dim;
+  float m2 = 0.f;
+#pragma unroll
+  for (int g = 0; g < 16; ++g)
+    if (g < groups) {
+      const float d = fmaf(p[g].x, 1.f / 64.f, -mean);
+      m2 += fmaf(64.f * d, d, p[g].y);
+    }
+  stats[row] = make_float2(mean, rsqrtf(m2 * inv_dim + eps));
+}
+
 // One-off weight fold of a LayerNorm (g, beta) into the Linear (w, bias) that follows it, one block per output feature:
 //   wf[n, k] = fp16(g[k] w[n, k]),  colsum[n] = sum_k wf[n, k] (of the ROUNDED values the tensor cores will see),
 //   cf[n] = bias[n] + sum_k beta[k] w[n, k]     so that   Linear(LN(x)) = rstd (x . wf^T - mu colsum) + cf.
@@ -490,6 +518,15 @@ int yv_row_stats_launch(const void *x16, size_t in_stride, float *stats, int row
   else if (dim == 256) row_stats_f16_kernel<1><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, st, rows, eps);
   else if (dim == 512) row_stats_f16_kernel<2><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, st, rows, eps);
   else row_stats_f16_kernel<4><<<grid, LN_WARPS * 32, 0, s>>>(x, in_stride, st, rows, eps);
+  YV_LAUNCH_CHECK();
+  return YV_OK;
+}
+
+int yv_stats_finalize_launch(const float *part, int rows, int dim, float eps, float *stats, cudaStream_t s) {
+  YV_REQUIRE(rows >= 1 && dim % 64 == 0 && dim >= 64 && dim <= 1024, "stats_finalize: dim=%d unsupported", dim);
+  YvProf prof(YV_K_LN, s, (double)rows * (dim / 64 + 1) * 8.0);
+  stats_finalize_kernel<<<(rows + 255) / 256, 256, 0, s>>>(reinterpret_cast<const float2 *>(part), dim / 64, rows, eps,
+                                                           reinterpret_cast<float2 *>(stats));
   YV_LAUNCH_CHECK();
   return YV_OK;
 }

@@ -31,6 +31,9 @@ int yv_attention_fa_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, 
 // LayerNorm folded into the next Linear: per-row (mean, rstd) of the fp16 stream -> stats [rows, 2] f32
 // (the stream is only read), and the one-off weight fold wf16 = fp16(g (.) w), colsum, cf = bias + beta . w^T.
 int yv_row_stats_launch(const void *x16, size_t in_stride, float *stats, int rows, int dim, float eps, cudaStream_t s);
+// (mean, rstd) per row from the partial statistics of the GEMM's fused residual epilogue (GemmEpilogue::stats_part,
+// [dim / 64][rows] float2): the statistics pass over the stream disappears.
+int yv_stats_finalize_launch(const float *part, int rows, int dim, float eps, float *stats, cudaStream_t s);
 int yv_fold_ln_launch(const __nv_bfloat16 *w, const float *bias, const float *g, const float *beta, int N, int K,
                       void *wf16, float *colsum, float *cf, cudaStream_t s);
 

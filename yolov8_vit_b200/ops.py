@@ -276,6 +276,24 @@ def linear_ln_f16(x: torch.Tensor, w: torch.Tensor, bias: torch.Tensor, gamma: t
     return d
 
 
+def residual_linear_f16(a: torch.Tensor, w: torch.Tensor, bias: torch.Tensor | None, x: torch.Tensor,
+                        want_stats: bool = True, eps: float = 1e-6):
+    """x += a @ w.T + bias IN PLACE on the f16 stream x [M,N] (a bf16 [M,K], w bf16 [N,K]); returns the (mean, rstd)
+    rows [M,2] f32 of the updated x computed inside the GEMM epilogue (or None)."""
+    require_device(a)
+    assert a.dtype == torch.bfloat16 and w.dtype == torch.bfloat16 and x.dtype == torch.float16 and x.is_contiguous()
+    a, w = a.contiguous(), w.contiguous()
+    M, K = a.shape
+    N = w.shape[0]
+    assert x.shape == (M, N)
+    lib = load()
+    stats = torch.empty(M, 2, dtype=torch.float32, device=a.device) if want_stats else None
+    ws = _ws(lib.yv_residual_linear_f16_ws_bytes(M, N), a.device) if want_stats else None
+    check(lib.yv_residual_linear_f16(ptr(a), ptr(w), ptr(bias), ptr(x), M, N, K, float(eps), ptr(stats), ptr(ws),
+                                     ws.numel() if ws is not None else 0, stream_ptr(a.device)), "yv_residual_linear_f16")
+    return stats
+
+
 def layernorm_bf16(x: torch.Tensor, gamma: torch.Tensor, beta: torch.Tensor, eps: float = 1e-6):
     require_device(x)
     assert x.dtype == torch.bfloat16
