@@ -4,7 +4,7 @@
 mkdir -p gpurun_out
 python -c "import __graft_entry__ as g; g.build()" > gpurun_out/r2f_build.log 2>&1
 : > gpurun_out/r2f_pytest.log
-for f in tests/test_gpu_gemm.py tests/test_gpu_ops.py tests/test_gpu_ref.py tests/test_gpu_vit.py tests/test_gpu_shapes.py tests/test_wrapper.py; do
+for f in tests/test_gpu_canary.py tests/test_gpu_gemm.py tests/test_gpu_ops.py tests/test_gpu_ref.py tests/test_gpu_vit.py tests/test_gpu_shapes.py tests/test_wrapper.py tests/test_zz_no_alloc.py; do
   echo "=== $f" >> gpurun_out/r2f_pytest.log
   timeout 1500 python -m pytest $f -m gpu -q --timeout 900 --maxfail=6 >> gpurun_out/r2f_pytest.log 2>&1
   echo "rc=$?" >> gpurun_out/r2f_pytest.log

@@ -11,7 +11,7 @@ PY
 timeout 300 $CMD > gpurun_out/r2p_plain.log 2>&1 && \
 timeout 1200 ncu --metrics gpu__time_duration.sum --clock-control none -c 3000 --csv --log-file gpurun_out/r2p_launches.csv $CMD > gpurun_out/r2p_ncu_list.log 2>&1
 echo "ncu list rc=$?"
-timeout 900 ncu --set full --clock-control none --import-source on -k regex:"gemm_bf16|attention|row_stats" -s 30 -c 12 -o gpurun_out/r2p_vit $CMD > gpurun_out/r2p_ncu_full.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:"gemm_bf16|attention|row_stats|stats_finalize" -s 30 -c 14 -o gpurun_out/r2p_vit $CMD > gpurun_out/r2p_ncu_full.log 2>&1
 echo "ncu full rc=$?"
 timeout 600 python tools/vit_b8_bench.py > gpurun_out/r2p_vit_b8.json 2>&1 && \
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:"attention_fa" -s 2 -c 2 -o gpurun_out/r2p_b8_attn python tools/vit_b8_bench.py > gpurun_out/r2p_ncu_b8.log 2>&1

@@ -76,36 +76,36 @@ decode_filter_kernel(const float *__restrict__ head, int nc, int A, float conf, 
 
   if (in_range) {
     const float *cp = hp + (size_t)BOXROWS * A + a0;
-    // Update rule = torch.max(dim): first max wins on ties, and a NaN score wins over every number and is never
-    // replaced (the first NaN's index is returned): !(v <= best) is "v > best or unordered", best == best locks a
-    // NaN that is already held.  The running max starts at -inf / label 0, which under this rule gives exactly what
-    // an initialisation from class 0 gives (-inf stays with label 0, any number or NaN of class 0 replaces it).
-    // Rolling window of DEC_UNROLL row loads: a slot is refilled with the row DEC_UNROLL classes ahead as soon as it
-    // has been consumed, so the loads of the next batch are in flight while this one is compared -- a thread's
-    // chain is ceil(rows / DEC_UNROLL) memory round trips with no serial tail (nc = 80: 10 instead of 18, which is
-    // what bounded the single-wave shapes such as [64, 84, 8400]).
+    {  // class 0 initialises the running max.  Update rule = torch.max(dim): first max wins on ties, and a NaN
+       // score wins over every number and is never replaced (the first NaN's index is returned):
+       // !(v <= best) is "v > best or unordered", best == best locks a NaN that is already held
+      RowVec<VEC> r;
+      r.load(cp);
 #pragma unroll
-    for (int j = 0; j < VEC; ++j) best[j] = -INFINITY;
-    RowVec<VEC> r[DEC_UNROLL];
+      for (int j = 0; j < VEC; ++j) best[j] = r.v[j];
+    }
+    int c = 1;
+    for (; c + DEC_UNROLL <= nc; c += DEC_UNROLL) {
+      RowVec<VEC> r[DEC_UNROLL];
 #pragma unroll
-    for (int u = 0; u < DEC_UNROLL; ++u)
-      if (u < nc) r[u].load(cp + (size_t)u * A);
-    if (!RAW) {                       // the 4 box rows travel with the first batch
+      for (int u = 0; u < DEC_UNROLL; ++u) r[u].load(cp + (size_t)(c + u) * A);
+#pragma unroll
+      for (int u = 0; u < DEC_UNROLL; ++u)
+#pragma unroll
+        for (int j = 0; j < VEC; ++j)
+          if (!(r[u].v[j] <= best[j]) && best[j] == best[j]) { best[j] = r[u].v[j]; lab[j] = c + u; }
+    }
+    for (; c < nc; ++c) {
+      RowVec<VEC> r;
+      r.load(cp + (size_t)c * A);
+#pragma unroll
+      for (int j = 0; j < VEC; ++j)
+        if (!(r.v[j] <= best[j]) && best[j] == best[j]) { best[j] = r.v[j]; lab[j] = c; }
+    }
+    if (!RAW) {
 #pragma unroll
       for (int k = 0; k < 4; ++k) bx[k].load(hp + (size_t)k * A + a0);
-    }
-    for (int c = 0; c < nc; c += DEC_UNROLL) {
-#pragma unroll
-      for (int u = 0; u < DEC_UNROLL; ++u) {
-        if (c + u < nc) {
-#pragma unroll
-          for (int j = 0; j < VEC; ++j)
-            if (!(r[u].v[j] <= best[j]) && best[j] == best[j]) { best[j] = r[u].v[j]; lab[j] = c + u; }
-          if (c + DEC_UNROLL + u < nc) r[u].load(cp + (size_t)(c + DEC_UNROLL + u) * A);
-        }
-      }
-    }
-    if (RAW) {
+    } else {
       // class probabilities are sigmoid(logit): monotonic, so the arg-max is taken on the logits and only
       // the winner is squashed (torch.sigmoid in fp32)
 #pragma unroll
