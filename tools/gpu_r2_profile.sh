@@ -16,4 +16,7 @@ echo "ncu full rc=$?"
 timeout 600 python tools/vit_b8_bench.py > gpurun_out/r2p_vit_b8.json 2>&1 && \
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:"attention_fa" -s 2 -c 2 -o gpurun_out/r2p_b8_attn python tools/vit_b8_bench.py > gpurun_out/r2p_ncu_b8.log 2>&1
 echo "ncu b8 rc=$?"; tail -1 gpurun_out/r2p_vit_b8.json
+NCU=1 timeout 600 python tools/stage_bench.py > gpurun_out/r2p_stage_plain.log 2>&1 && \
+NCU=1 timeout 900 ncu --set full --clock-control none --import-source on -k regex:"nms_kernel|decode_filter" -c 8 -o gpurun_out/r2p_stages python tools/stage_bench.py > gpurun_out/r2p_ncu_stages.log 2>&1
+echo "ncu stages rc=$?"
 ls -la gpurun_out | grep r2p

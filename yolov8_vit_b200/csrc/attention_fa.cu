@@ -34,6 +34,11 @@
 //               (O / row sum -> bf16 -> global) inside the first block of the slot's NEXT tile, when its last
 //               P V has long retired.
 // Warps whose 32 query rows are all past T (the tail tile) only pass the barriers on.
+//
+// Which lengths run here (yv_attention_launch, attention_sm100.cu): every shape the round-1 pipelined kernel does
+// not take -- ViT-B/8 and any T > 224.  For ViT-B/16 itself this kernel measured 0.43 - 0.47 ms per 268 crops
+// against 0.38 ms for attention_pipe_kernel (tools/attn_bench.py), so that one stays the default there and
+// YV_ATTN_B16=fa selects this kernel for A/B; the parity tests run both.
 #include <cstdlib>
 #include "common.cuh"
 #include "gemm_sm100.cuh"
