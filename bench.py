@@ -47,13 +47,13 @@ IMG = 640
 SEED = 20240410 + 1
 FLOP_PER_CROP = 35.128e9           # SURVEY.md §8d (ViT-B/16 + heads)
 # ncu --set full, dram__bytes_read.sum + dram__bytes_write.sum per launch, mean of the four block GEMMs of the
-# one-pass ViT at M = 1072 crops x 197 = 211 184 rows (profiles/r02_vit_ncu_v2.md, folded-LayerNorm build):
-# qkv 330 + 924, proj 650 + 286 (fp16 stream in and out), fc1 333 + 1250, fc2 1664 + 311 MB -> mean 1437 MB
-# = 6.80 KB per token row (algorithmic: 1297 / 973 / 1622 / 1946 MB, mean 1460 MB; part of the stream is still in
-# L2 from the previous kernel); scaled by the run's own row count below (the driver's workload gives 1072 crops)
-GEMM_DRAM_BYTES_PER_ROW = 1437e6 / 211184
+# one-pass ViT at M = 1072 crops x 197 = 211 184 rows (profiles/r02_vit_ncu_v3.md, final round-2 build):
+# qkv 330 + 920, proj 650 + 300 (fp16 stream in and out + partial statistics), fc1 330 + 1250, fc2 1660 + 330 MB
+# -> mean 1443 MB = 6.83 KB per token row (algorithmic: 1297 / 993 / 1622 / 1966 MB, mean 1470 MB; part of the
+# stream is still in L2 from the previous kernel); scaled by the run's own row count below
+GEMM_DRAM_BYTES_PER_ROW = 1443e6 / 211184
 GEMM_TRAFFIC_NOTE = ("mean dram read+write bytes of the qkv/proj/fc1/fc2 launches of the one-pass ViT (M = crops x 197 "
-                     "rows), ncu --set full (profiles/r02_vit_ncu_v2.md: 1437 MB at 1072 crops; algorithmic 1460 MB)")
+                     "rows), ncu --set full (profiles/r02_vit_ncu_v3.md: 1443 MB at 1072 crops; algorithmic 1470 MB)")
 
 
 def parse():
