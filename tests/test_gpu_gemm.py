@@ -164,3 +164,43 @@ def test_residual_update_with_row_statistics(M, N, K):
     # without statistics the entry point is the plain in-place update
     x2 = x0.clone()
     assert ops.residual_linear_f16(a, w, bias, x2, want_stats=False) is None and torch.equal(x2, x_plain)
+
+
+def test_cluster_of_four_multicast_form_parity():
+    """YV_GEMM_CLUSTER=4: two CTA pairs per cluster on M-adjacent tiles with the W operand multicast to both (opt-in,
+    measured slower than pairs at the power cap).  Same results bit for bit as the default form on the
+    three TMA epilogues (plain / GELU bf16, fused fp16 residual with statistics, folded LayerNorm), including an odd
+    number of M-tiles (the second pair of the last cluster works on an all-padding tile) and a single-tile M."""
+    import os, subprocess, sys, tempfile
+    code = r"""
+import sys, torch
+sys.path.insert(0, %r)
+from yolov8_vit_b200 import ops
+dev = 'cuda:0'
+g = torch.Generator().manual_seed(5)
+out = []
+for M, N, K in ((197 * 13, 768, 768), (300, 1024, 768), (1290, 512, 256), (256, 256, 256)):
+    a = (torch.randn(M, K, generator=g) * 0.5).to(torch.bfloat16).to(dev)
+    w = (torch.randn(N, K, generator=g) * 0.05).to(torch.bfloat16).to(dev)
+    b = torch.randn(N, generator=g).to(dev)
+    out.append(ops.gemm_bf16(a, w, b).cpu())
+    out.append(ops.gemm_bf16(a, w, b, gelu=True).cpu())
+    x = torch.randn(M, N, generator=g).to(torch.float16).to(dev)
+    st = ops.residual_linear_f16(a, w, b, x)
+    out += [x.cpu(), st.cpu()]
+    xf = (torch.randn(M, K, generator=g) + 2).to(torch.float16).to(dev)
+    out.append(ops.linear_ln_f16(xf, w, b, torch.ones(K, device=dev), torch.zeros(K, device=dev), 1e-6, True).cpu())
+torch.save(out, sys.argv[1])
+print('ok')
+""" % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    res = []
+    with tempfile.TemporaryDirectory() as d:
+        for mode in ("2", "4"):
+            f = os.path.join(d, mode + ".pt")
+            r = subprocess.run([sys.executable, "-c", code, f], env=dict(os.environ, YV_GEMM_CLUSTER=mode),
+                               capture_output=True, text=True, timeout=280)
+            assert r.returncode == 0 and "ok" in r.stdout, r.stdout + r.stderr
+            res.append(torch.load(f))
+    assert len(res[0]) == len(res[1]) == 20
+    for k, (p, q) in enumerate(zip(*res)):
+        assert torch.equal(p, q), k

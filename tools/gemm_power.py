@@ -45,7 +45,7 @@ def sustained(f, flops):
     ms = e0.elapsed_time(e1)
     rows = [r for r in smi.rows if r[0] - t0 > 0.8]           # after the power limiter has settled
     pw = sorted(r[1] for r in rows); ck = sorted(r[2] for r in rows)
-    return {"tflops": round(flops * n / ms / 1e9, 1), "launches": n, "power_w_median": pw[len(pw) // 2] if pw else None,
+    return {"tflops": round(flops * n / ms / 1e9, 1), "ms_per_launch": round(ms / n, 4), "launches": n, "power_w_median": pw[len(pw) // 2] if pw else None,
             "sm_mhz_median": ck[len(ck) // 2] if ck else None}
 
 

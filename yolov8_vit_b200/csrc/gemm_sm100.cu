@@ -20,6 +20,7 @@
 #include "sm100_ptx.cuh"
 
 #include <cuda_fp16.h>
+#include <cstdio>
 #include <cstdlib>
 #include <mutex>
 
@@ -102,8 +103,11 @@ __device__ __forceinline__ uint32_t pack_b2(float a, float b) {
 // GELU / OUT select the epilogue arithmetic at compile time; MODE 1 compiles in the rarely used position-table
 // (patch embedding) and residual operands of the LSU form.
 constexpr int EPI_PLAIN = 0, EPI_EXTRA = 1;
-template <bool GELU, int OUT, int MODE, int NEW, int DIRECT = EPI_LSU>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(gemm_threads(NEW), 1)
+// CS = CTAs per cluster: 2 (one CTA pair) or 4 (two pairs on M-adjacent tiles of the same N-tile: the W operand is
+// loaded once and MULTICAST to both pairs -- 25 % less L2 -> shared-memory traffic, which is what the kernel's power
+// goes into: the operand feed alone, without a single MMA, pins the GPU at its 1000 W cap (tools/gemm_power.py)).
+template <bool GELU, int OUT, int MODE, int NEW, int DIRECT = EPI_LSU, int CS = 2>
+__global__ void __cluster_dims__(CS, 1, 1) __launch_bounds__(gemm_threads(NEW), 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  const __grid_constant__ CUtensorMap tmD, const __grid_constant__ CUtensorMap tmR,
                  const GemmEpilogue ep, int M, int N, int K) {
@@ -122,8 +126,16 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m_tiles = (M + PM - 1) / PM, n_tiles = (N + BN - 1) / BN;
   const int num_tiles = m_tiles * n_tiles, kblocks = K / BK;
-  const uint32_t rank = cluster_ctarank();            // 0 = leader of the CTA pair (issues the MMAs)
-  const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+  const uint32_t crank = cluster_ctarank();           // rank in the cluster
+  const uint32_t rank = crank & 1u;                   // 0 = leader of the CTA pair (issues the MMAs)
+  const uint32_t lead = crank & ~1u;                  // cluster rank of this pair's leader
+  const int pr = (int)(crank >> 1);                   // which pair of the cluster (CS == 4: 0 / 1)
+  // work units: tiles (CS == 2) or SUPER-tiles of two M-adjacent tiles (CS == 4, pair pr takes M-tile 2 u / n_tiles + pr;
+  // an M-tile past the end is all zero-fill loads and clipped stores)
+  const int pair = CS == 4 ? (int)(blockIdx.x >> 2) : (int)(blockIdx.x >> 1);
+  const int npairs = CS == 4 ? (int)(gridDim.x >> 2) : (int)(gridDim.x >> 1);
+  const int num_units = CS == 4 ? ((m_tiles + 1) / 2) * n_tiles : num_tiles;
+  const uint16_t pair_mask = (uint16_t)(3u << lead);
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
@@ -134,7 +146,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 1 && lane == 0) {
     // full: one arrive per producer of the pair (+ the bytes of both); empty / tfull: one multicast
     // tcgen05.commit; tempty (leader's copy is the one waited on): every epilogue warp of both CTAs
-    for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 2); mbar_init(&empty[i], 1); }
+    // (CS == 4: a stage is free when BOTH pairs' MMAs have read it -- pair 0 multicasts W into pair 1's slots too)
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 2); mbar_init(&empty[i], CS == 4 ? 2 : 1); }
     for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 2 * NEW); }
     for (int i = 0; i < 16; ++i) mbar_init(&rbar[i], 1);
     fence_barrier_init();
@@ -154,16 +167,18 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = pair; tile < num_tiles; tile += npairs) {
+      for (int tile = pair; tile < num_units; tile += npairs) {
         // this CTA stages its 128 rows of A and its 128 (of 256) rows of W
-        const int m0 = (tile / n_tiles) * PM + (int)rank * BM, n0 = (tile % n_tiles) * BN + (int)rank * BNH;
+        const int mt = CS == 4 ? 2 * (tile / n_tiles) + pr : tile / n_tiles;
+        const int m0 = mt * PM + (int)rank * BM, n0 = (tile % n_tiles) * BN + (int)rank * BNH;
         for (int kb = 0; kb < kblocks; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1u);
           uint8_t *sa = smem + (size_t)stage * STAGE_BYTES, *sb = sa + A_BYTES;
           if (rank == 0) mbar_arrive_expect_tx(&full[stage], 2 * STAGE_BYTES);   // bytes of both CTAs
           tma_load_2d_pair(sa, &tmA, &full[stage], kb * BK, m0);
-          tma_load_2d_pair(sb, &tmB, &full[stage], kb * BK, n0);
-          if (rank != 0) mbar_arrive_remote(&full[stage], 0);
+          if (CS == 2) tma_load_2d_pair(sb, &tmB, &full[stage], kb * BK, n0);
+          else if (pr == 0) tma_load_2d_pair_mc(sb, &tmB, &full[stage], kb * BK, n0, (uint16_t)(5u << rank));   // -> ranks r, r + 2
+          if (rank != 0) mbar_arrive_remote(&full[stage], lead);
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
       }
@@ -175,7 +190,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       constexpr uint32_t idesc = DIRECT == EPI_TMA_LN ? (umma_idesc_bf16(PM, BN) & ~((7u << 7) | (7u << 10))) : umma_idesc_bf16(PM, BN);
       int stage = 0;
       uint32_t phase = 0, it = 0;
-      for (int tile = pair; tile < num_tiles; tile += npairs, ++it) {
+      for (int tile = pair; tile < num_units; tile += npairs, ++it) {
         const uint32_t as = it & 1u, aph = (it >> 1) & 1u;
         mbar_wait(&tempty[as], aph ^ 1u);          // epilogue has drained this accumulator
         tc_fence_after();
@@ -188,12 +203,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 #pragma unroll
           for (int k = 0; k < BK / UMMA_K; ++k) {
             // advance 16 elements (32 B) along K inside the swizzle atom: +2 in the addr>>4 field
-            umma_bf16_pair(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (uint32_t)((kb | k) != 0));
+            if (ep.dbg != 8)      // (measurement: dbg 8 = operand feed only, no MMAs -- what the L2 -> smem stream costs in power)
+              umma_bf16_pair(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (uint32_t)((kb | k) != 0));
           }
-          umma_commit_pair(&empty[stage]);         // both CTAs' smem slots free once these MMAs retire
+          umma_commit_pair(&empty[stage], CS == 4 ? (uint16_t)15 : pair_mask);   // smem slots free once these MMAs retire
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
-        umma_commit_pair(&tfull[as]);              // accumulator complete -> both CTAs' epilogues
+        umma_commit_pair(&tfull[as], pair_mask);   // accumulator complete -> both CTAs' epilogues
       }
     }
   } else if (warp >= 4 && DIRECT != EPI_LSU) {
@@ -217,9 +233,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     uint8_t *stg = epi_smem + ew * epi_warp_bytes(DIRECT);
     const uint32_t sw = (uint32_t)(lane >> 1) & 3u;
     uint32_t it = 0, rit = 0;
-    for (int tile = pair; tile < num_tiles; tile += npairs, ++it) {
+    for (int tile = pair; tile < num_units; tile += npairs, ++it) {
       const uint32_t as = it & 1u, aph = (it >> 1) & 1u;
-      const int m0 = (tile / n_tiles) * PM + (int)rank * BM, n0 = (tile % n_tiles) * BN;
+      const int m0 = (CS == 4 ? 2 * (tile / n_tiles) + pr : tile / n_tiles) * PM + (int)rank * BM, n0 = (tile % n_tiles) * BN;
       const int row0 = m0 + q * 32;
       const int col0 = n0 + cg * EPI_COLS;
       const bool box0 = row0 < M && col0 < N, box1 = row0 < M && col0 + 32 < N;      // warp-uniform
@@ -265,7 +281,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           __syncwarp();
           if (lane == 0) {
             if (rank == 0) mbar_arrive(&tempty[as]);
-            else mbar_arrive_remote(&tempty[as], 0);
+            else mbar_arrive_remote(&tempty[as], lead);
           }
         }
         float4 v[4];
@@ -346,7 +362,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         __syncwarp();
         if (lane == 0) {
           if (rank == 0) mbar_arrive(&tempty[as]);
-          else mbar_arrive_remote(&tempty[as], 0);
+          else mbar_arrive_remote(&tempty[as], lead);
         }
       }
     }
@@ -366,9 +382,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     const int trow = lane >> 2, tseg = lane & 3;   // transposed role: row-in-group, 16-byte segment
     constexpr int NCH = EPI_COLS / 16;             // 16-column chunks per warp
     uint32_t it = 0;
-    for (int tile = pair; tile < num_tiles; tile += npairs, ++it) {
+    for (int tile = pair; tile < num_units; tile += npairs, ++it) {
       const uint32_t as = it & 1u, aph = (it >> 1) & 1u;
-      const int m0 = (tile / n_tiles) * PM + (int)rank * BM, n0 = (tile % n_tiles) * BN;
+      const int m0 = (CS == 4 ? 2 * (tile / n_tiles) + pr : tile / n_tiles) * PM + (int)rank * BM, n0 = (tile % n_tiles) * BN;
       const int colw = n0 + cg * EPI_COLS + tseg * 4;       // this thread's first column (chunk 0)
       float4 bias4[NCH];
 #pragma unroll
@@ -454,7 +470,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       __syncwarp();
       if (lane == 0) {                             // this warp is done with the accumulator (leader's barrier)
         if (rank == 0) mbar_arrive(&tempty[as]);
-        else mbar_arrive_remote(&tempty[as], 0);
+        else mbar_arrive_remote(&tempty[as], lead);
       }
     }
   }
@@ -496,6 +512,10 @@ void init_once() {
   X(false, T_BF16, 0, 16, EPI_TMA_LN) X(true, T_BF16, 0, 16, EPI_TMA_LN)                                              \
   X(false, T_BF16, 1, 8, EPI_LSU) X(false, T_F32, 1, 8, EPI_LSU) X(true, T_BF16, 1, 8, EPI_LSU) X(true, T_F32, 1, 8, EPI_LSU)     \
   X(false, T_F16, 1, 8, EPI_LSU)
+// the instances that also exist for clusters of 4 (the ViT block GEMMs)
+#define YV_GEMM_INSTANCES4(X)                                                                                      \
+  X(false, T_BF16, 0, 16, EPI_TMA) X(true, T_BF16, 0, 16, EPI_TMA) X(false, T_F16, 0, 16, EPI_TMA_RES)             \
+  X(false, T_BF16, 0, 16, EPI_TMA_LN) X(true, T_BF16, 0, 16, EPI_TMA_LN)
 int init_device() {
   cudaError_t e = cudaSuccess;
 #define YV_SET(G, O, X, W, D)                                                                                      \
@@ -503,6 +523,11 @@ int init_device() {
     e = cudaFuncSetAttribute(gemm_bf16_kernel<G, O, X, W, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes(W, D));
   YV_GEMM_INSTANCES(YV_SET)
 #undef YV_SET
+#define YV_SET4(G, O, X, W, D)                                                                                     \
+  if (e == cudaSuccess)                                                                                          \
+    e = cudaFuncSetAttribute(gemm_bf16_kernel<G, O, X, W, D, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes(W, D));
+  YV_GEMM_INSTANCES4(YV_SET4)
+#undef YV_SET4
   if (e != cudaSuccess) return yv_cuda_fail(e, "cudaFuncSetAttribute(gemm smem)", __FILE__, __LINE__);
   return YV_OK;
 }
@@ -582,6 +607,42 @@ int yv_gemm_launch(const void *A, const void *W, int M, int N, int K, const Gemm
     if ((rc = make_tmap(&tmR, ep.residual, (uint64_t)M, (uint64_t)N, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_DATA_TYPE_FLOAT16))) return rc;
   }
 #define YV_GO(G, O, X, W, D) gemm_bf16_kernel<G, O, X, W, D><<<grid, gemm_threads(W), smem_bytes(W, D), s>>>(tmA, tmB, tmD, tmR, ep, M, N, K)
+  // Clusters of 4 (W multicast to two M-adjacent CTA pairs) for the TMA-epilogue forms: opt-in with YV_GEMM_CLUSTER=4.
+  // Measured (tools/gemm_power.py, profiles/r02_gemm_power.md): 25 % less L2 -> smem traffic raises the power-capped
+  // clock by 11 - 24 %, but only 33 clusters of 4 fit the GPCs (132 of 148 SMs) and the sustained rate ends 2 - 3 %
+  // BELOW the CTA-pair form, so pairs stay the default.
+  static const int cs_env = []() { const char *e = getenv("YV_GEMM_CLUSTER"); return e ? atoi(e) : 0; }();
+  const int m_tiles_h = (M + PM - 1) / PM;
+  const bool cl4 = (cs_env == 4) && (lnfold || tma_res || tma_out) && m_tiles_h >= 2;
+  if (cl4) {
+    static std::mutex mu;
+    static int max_cl[64] = {};
+    int dev = 0;
+    YV_CUDA(cudaGetDevice(&dev));
+    const int units = ((m_tiles_h + 1) / 2) * ((N + BN - 1) / BN);
+    cudaLaunchConfig_t cfg = {};                   // (the cluster size is compiled into the kernel: no launch attribute)
+    cfg.blockDim = dim3(gemm_threads(16));
+    cfg.dynamicSmemBytes = smem_bytes(16, EPI_TMA);
+    cfg.stream = s;
+    {
+      std::lock_guard<std::mutex> lk(mu);
+      if (dev >= 0 && dev < 64 && max_cl[dev] == 0) {
+        cfg.gridDim = dim3((unsigned)(yv_num_sms() / 4 * 4));
+        int n = 0;
+        cudaError_t qe = cudaOccupancyMaxActiveClusters(&n, gemm_bf16_kernel<false, T_BF16, 0, 16, EPI_TMA, 4>, &cfg);
+        if (qe != cudaSuccess || n < 1) { (void)cudaGetLastError(); n = yv_num_sms() / 4; }
+        max_cl[dev] = n;
+        if (getenv("YV_GEMM_VERBOSE")) fprintf(stderr, "[yv8vit] clusters of 4 co-resident on device %d: %d (%d SMs), query rc %d\n", dev, n, 4 * n, (int)qe);
+      }
+    }
+    const int ncl = units < max_cl[dev] ? units : max_cl[dev];
+    const int grid4 = 4 * ncl;
+#define YV_GO4(G, O, X, W, D) gemm_bf16_kernel<G, O, X, W, D, 4><<<grid4, gemm_threads(W), smem_bytes(W, D), s>>>(tmA, tmB, tmD, tmR, ep, M, N, K)
+    if (lnfold) { if (ep.gelu) YV_GO4(true, T_BF16, 0, 16, EPI_TMA_LN); else YV_GO4(false, T_BF16, 0, 16, EPI_TMA_LN); }
+    else if (tma_res) YV_GO4(false, T_F16, 0, 16, EPI_TMA_RES);
+    else { if (ep.gelu) YV_GO4(true, T_BF16, 0, 16, EPI_TMA); else YV_GO4(false, T_BF16, 0, 16, EPI_TMA); }
+#undef YV_GO4
+  } else
   if (lnfold) {
     if (ep.gelu) YV_GO(true, T_BF16, 0, 16, EPI_TMA_LN); else YV_GO(false, T_BF16, 0, 16, EPI_TMA_LN);
   } else if (tma_res) {

@@ -23,7 +23,7 @@ struct GemmEpilogue {
   // 64-column group, stats_part[(n / 64) * M + m] as float2 (M2 = sum of squares about the group's own mean); N % 64 == 0.
   // yv_stats_finalize_launch combines the N / 64 groups of a row into (mean, rstd).  null = off.
   float *stats_part = nullptr;
-  int dbg = 0;                      // measurement only (YV_GEMM_DBG): 1 = no global stores, 2 = no epilogue work
+  int dbg = 0;                      // measurement only (YV_GEMM_DBG): 1 = no global stores, 2 = no epilogue work, 8 = no MMAs (operand feed only)
 };
 
 // D = A[M,K] * W[N,K]^T with the epilogue above.  K % 64 == 0, N % 8 == 0.

@@ -147,6 +147,17 @@ __device__ __forceinline__ void tma_load_2d_pair(void *dst, const CUtensorMap *m
       : "memory");
 }
 
+// The same load MULTICAST to the CTAs of `cta_mask` (cluster ranks): the box lands at the same smem offset in each of
+// them and its bytes are signalled on the mbarrier at this offset in the pair leader of EACH destination CTA.
+__device__ __forceinline__ void tma_load_2d_pair_mc(void *dst, const CUtensorMap *m, uint64_t *bar, int c0, int c1,
+                                                    uint16_t cta_mask) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster "
+      "[%0], [%1, {%3, %4}], [%2], %5;"
+      ::"r"(smem_u32(dst)), "l"(m), "r"(smem_u32(bar) & 0xFEFFFFFFu), "r"(c0), "r"(c1), "h"(cta_mask)
+      : "memory");
+}
+
 // ---- tcgen05 ---------------------------------------------------------------------------------
 __device__ __forceinline__ void tmem_alloc(uint32_t *dst_smem, uint32_t cols) {
   asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(dst_smem)), "r"(cols)
@@ -233,10 +244,10 @@ __device__ __forceinline__ void umma_bf16_pair(uint32_t tmem_d, uint64_t desc_a,
       : "memory");
 }
 // completion of the leader's MMAs arrives on the mbarrier at this offset in BOTH CTAs of the pair
-__device__ __forceinline__ void umma_commit_pair(uint64_t *bar) {
+__device__ __forceinline__ void umma_commit_pair(uint64_t *bar, uint16_t cta_mask = 3) {
   asm volatile(
       "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;"
-      ::"r"(smem_u32(bar)), "h"((uint16_t)3)
+      ::"r"(smem_u32(bar)), "h"(cta_mask)
       : "memory");
 }
 
