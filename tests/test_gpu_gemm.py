@@ -167,7 +167,7 @@ def test_residual_update_with_row_statistics(M, N, K):
 
 
 def test_cluster_of_four_multicast_form_parity():
-    """YV_GEMM_CLUSTER=4: two CTA pairs per cluster on M-adjacent tiles with the W operand multicast to both (opt-in,
+    """YV_GEMM_CLUSTER=4 / 6: two / three CTA pairs per cluster on M-adjacent tiles with the W operand multicast to all of them (opt-in,
     measured slower than pairs at the power cap).  Same results bit for bit as the default form on the
     three TMA epilogues (plain / GELU bf16, fused fp16 residual with statistics, folded LayerNorm), including an odd
     number of M-tiles (the second pair of the last cluster works on an all-padding tile) and a single-tile M."""
@@ -195,12 +195,12 @@ print('ok')
 """ % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
     res = []
     with tempfile.TemporaryDirectory() as d:
-        for mode in ("2", "4"):
+        for mode in ("2", "4", "6"):
             f = os.path.join(d, mode + ".pt")
             r = subprocess.run([sys.executable, "-c", code, f], env=dict(os.environ, YV_GEMM_CLUSTER=mode),
                                capture_output=True, text=True, timeout=280)
             assert r.returncode == 0 and "ok" in r.stdout, r.stdout + r.stderr
             res.append(torch.load(f))
-    assert len(res[0]) == len(res[1]) == 20
-    for k, (p, q) in enumerate(zip(*res)):
-        assert torch.equal(p, q), k
+    assert len(res[0]) == len(res[1]) == len(res[2]) == 20
+    for k, (p, q, r6) in enumerate(zip(*res)):
+        assert torch.equal(p, q) and torch.equal(p, r6), k

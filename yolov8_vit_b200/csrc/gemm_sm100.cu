@@ -129,12 +129,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const uint32_t crank = cluster_ctarank();           // rank in the cluster
   const uint32_t rank = crank & 1u;                   // 0 = leader of the CTA pair (issues the MMAs)
   const uint32_t lead = crank & ~1u;                  // cluster rank of this pair's leader
-  const int pr = (int)(crank >> 1);                   // which pair of the cluster (CS == 4: 0 / 1)
-  // work units: tiles (CS == 2) or SUPER-tiles of two M-adjacent tiles (CS == 4, pair pr takes M-tile 2 u / n_tiles + pr;
+  const int pr = (int)(crank >> 1);                   // which pair of the cluster
+  // work units: tiles (CS == 2) or SUPER-tiles of PC M-adjacent tiles (CS == 4 / 6, pair pr takes M-tile PC (u / n_tiles) + pr;
   // an M-tile past the end is all zero-fill loads and clipped stores)
-  const int pair = CS == 4 ? (int)(blockIdx.x >> 2) : (int)(blockIdx.x >> 1);
-  const int npairs = CS == 4 ? (int)(gridDim.x >> 2) : (int)(gridDim.x >> 1);
-  const int num_units = CS == 4 ? ((m_tiles + 1) / 2) * n_tiles : num_tiles;
+  constexpr int PC = CS / 2;                          // CTA pairs per cluster (1, 2 or 3)
+  const int pair = (int)blockIdx.x / CS;              // cluster index = first work unit
+  const int npairs = (int)gridDim.x / CS;
+  const int num_units = ((m_tiles + PC - 1) / PC) * n_tiles;
   const uint16_t pair_mask = (uint16_t)(3u << lead);
 
   if (warp == 0 && lane == 0) {
@@ -147,7 +148,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     // full: one arrive per producer of the pair (+ the bytes of both); empty / tfull: one multicast
     // tcgen05.commit; tempty (leader's copy is the one waited on): every epilogue warp of both CTAs
     // (CS == 4: a stage is free when BOTH pairs' MMAs have read it -- pair 0 multicasts W into pair 1's slots too)
-    for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 2); mbar_init(&empty[i], CS == 4 ? 2 : 1); }
+    for (int i = 0; i < STAGES; ++i) { mbar_init(&full[i], 2); mbar_init(&empty[i], PC); }
     for (int i = 0; i < 2; ++i) { mbar_init(&tfull[i], 1); mbar_init(&tempty[i], 2 * NEW); }
     for (int i = 0; i < 16; ++i) mbar_init(&rbar[i], 1);
     fence_barrier_init();
@@ -169,7 +170,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       uint32_t phase = 0;
       for (int tile = pair; tile < num_units; tile += npairs) {
         // this CTA stages its 128 rows of A and its 128 (of 256) rows of W
-        const int mt = CS == 4 ? 2 * (tile / n_tiles) + pr : tile / n_tiles;
+        const int mt = PC * (tile / n_tiles) + pr;
         const int m0 = mt * PM + (int)rank * BM, n0 = (tile % n_tiles) * BN + (int)rank * BNH;
         for (int kb = 0; kb < kblocks; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1u);
@@ -177,7 +178,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           if (rank == 0) mbar_arrive_expect_tx(&full[stage], 2 * STAGE_BYTES);   // bytes of both CTAs
           tma_load_2d_pair(sa, &tmA, &full[stage], kb * BK, m0);
           if (CS == 2) tma_load_2d_pair(sb, &tmB, &full[stage], kb * BK, n0);
-          else if (pr == 0) tma_load_2d_pair_mc(sb, &tmB, &full[stage], kb * BK, n0, (uint16_t)(5u << rank));   // -> ranks r, r + 2
+          else if (pr == 0) tma_load_2d_pair_mc(sb, &tmB, &full[stage], kb * BK, n0, (uint16_t)((CS == 6 ? 21u : 5u) << rank));   // -> ranks r, r + 2 (, r + 4)
           if (rank != 0) mbar_arrive_remote(&full[stage], lead);
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
@@ -206,7 +207,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             if (ep.dbg != 8)      // (measurement: dbg 8 = operand feed only, no MMAs -- what the L2 -> smem stream costs in power)
               umma_bf16_pair(d_tmem, da + (uint64_t)(k * 2), db + (uint64_t)(k * 2), idesc, (uint32_t)((kb | k) != 0));
           }
-          umma_commit_pair(&empty[stage], CS == 4 ? (uint16_t)15 : pair_mask);   // smem slots free once these MMAs retire
+          umma_commit_pair(&empty[stage], CS > 2 ? (uint16_t)((1u << CS) - 1u) : pair_mask);   // smem slots free once these MMAs retire
           if (++stage == STAGES) { stage = 0; phase ^= 1u; }
         }
         umma_commit_pair(&tfull[as], pair_mask);   // accumulator complete -> both CTAs' epilogues
@@ -235,7 +236,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     uint32_t it = 0, rit = 0;
     for (int tile = pair; tile < num_units; tile += npairs, ++it) {
       const uint32_t as = it & 1u, aph = (it >> 1) & 1u;
-      const int m0 = (CS == 4 ? 2 * (tile / n_tiles) + pr : tile / n_tiles) * PM + (int)rank * BM, n0 = (tile % n_tiles) * BN;
+      const int m0 = (PC * (tile / n_tiles) + pr) * PM + (int)rank * BM, n0 = (tile % n_tiles) * BN;
       const int row0 = m0 + q * 32;
       const int col0 = n0 + cg * EPI_COLS;
       const bool box0 = row0 < M && col0 < N, box1 = row0 < M && col0 + 32 < N;      // warp-uniform
@@ -384,7 +385,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     uint32_t it = 0;
     for (int tile = pair; tile < num_units; tile += npairs, ++it) {
       const uint32_t as = it & 1u, aph = (it >> 1) & 1u;
-      const int m0 = (CS == 4 ? 2 * (tile / n_tiles) + pr : tile / n_tiles) * PM + (int)rank * BM, n0 = (tile % n_tiles) * BN;
+      const int m0 = (PC * (tile / n_tiles) + pr) * PM + (int)rank * BM, n0 = (tile % n_tiles) * BN;
       const int colw = n0 + cg * EPI_COLS + tseg * 4;       // this thread's first column (chunk 0)
       float4 bias4[NCH];
 #pragma unroll
@@ -525,7 +526,9 @@ int init_device() {
 #undef YV_SET
 #define YV_SET4(G, O, X, W, D)                                                                                     \
   if (e == cudaSuccess)                                                                                          \
-    e = cudaFuncSetAttribute(gemm_bf16_kernel<G, O, X, W, D, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes(W, D));
+    e = cudaFuncSetAttribute(gemm_bf16_kernel<G, O, X, W, D, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes(W, D)); \
+  if (e == cudaSuccess)                                                                                          \
+    e = cudaFuncSetAttribute(gemm_bf16_kernel<G, O, X, W, D, 6>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_bytes(W, D));
   YV_GEMM_INSTANCES4(YV_SET4)
 #undef YV_SET4
   if (e != cudaSuccess) return yv_cuda_fail(e, "cudaFuncSetAttribute(gemm smem)", __FILE__, __LINE__);
@@ -607,41 +610,47 @@ int yv_gemm_launch(const void *A, const void *W, int M, int N, int K, const Gemm
     if ((rc = make_tmap(&tmR, ep.residual, (uint64_t)M, (uint64_t)N, 32, 32, CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_DATA_TYPE_FLOAT16))) return rc;
   }
 #define YV_GO(G, O, X, W, D) gemm_bf16_kernel<G, O, X, W, D><<<grid, gemm_threads(W), smem_bytes(W, D), s>>>(tmA, tmB, tmD, tmR, ep, M, N, K)
-  // Clusters of 4 (W multicast to two M-adjacent CTA pairs) for the TMA-epilogue forms: opt-in with YV_GEMM_CLUSTER=4.
+  // Clusters of 4 / 6 (W multicast to two / three M-adjacent CTA pairs) for the TMA-epilogue forms: opt-in with
+  // YV_GEMM_CLUSTER=4 / 6 (clusters of 6: 22 co-resident = the same 132 SMs, same outcome).
   // Measured (tools/gemm_power.py, profiles/r02_gemm_power.md): 25 % less L2 -> smem traffic raises the power-capped
   // clock by 11 - 24 %, but only 33 clusters of 4 fit the GPCs (132 of 148 SMs) and the sustained rate ends 2 - 3 %
   // BELOW the CTA-pair form, so pairs stay the default.
   static const int cs_env = []() { const char *e = getenv("YV_GEMM_CLUSTER"); return e ? atoi(e) : 0; }();
   const int m_tiles_h = (M + PM - 1) / PM;
-  const bool cl4 = (cs_env == 4) && (lnfold || tma_res || tma_out) && m_tiles_h >= 2;
-  if (cl4) {
+  const int cs = (cs_env == 4 || cs_env == 6) && (lnfold || tma_res || tma_out) && m_tiles_h >= cs_env / 2 ? cs_env : 2;
+  if (cs > 2) {
     static std::mutex mu;
-    static int max_cl[64] = {};
+    static int max_cl[64][2] = {};
     int dev = 0;
     YV_CUDA(cudaGetDevice(&dev));
-    const int units = ((m_tiles_h + 1) / 2) * ((N + BN - 1) / BN);
-    cudaLaunchConfig_t cfg = {};                   // (the cluster size is compiled into the kernel: no launch attribute)
-    cfg.blockDim = dim3(gemm_threads(16));
-    cfg.dynamicSmemBytes = smem_bytes(16, EPI_TMA);
-    cfg.stream = s;
+    YV_REQUIRE(dev >= 0 && dev < 64, "yv_gemm: device %d out of range", dev);
+    const int pc = cs / 2, slot = cs == 6;
+    const int units = ((m_tiles_h + pc - 1) / pc) * ((N + BN - 1) / BN);
     {
       std::lock_guard<std::mutex> lk(mu);
-      if (dev >= 0 && dev < 64 && max_cl[dev] == 0) {
-        cfg.gridDim = dim3((unsigned)(yv_num_sms() / 4 * 4));
+      if (max_cl[dev][slot] == 0) {
+        cudaLaunchConfig_t cfg = {};                 // (the cluster size is compiled into the kernel: no launch attribute)
+        cfg.blockDim = dim3(gemm_threads(16));
+        cfg.dynamicSmemBytes = smem_bytes(16, EPI_TMA);
+        cfg.stream = s;
+        cfg.gridDim = dim3((unsigned)(yv_num_sms() / cs * cs));
         int n = 0;
-        cudaError_t qe = cudaOccupancyMaxActiveClusters(&n, gemm_bf16_kernel<false, T_BF16, 0, 16, EPI_TMA, 4>, &cfg);
-        if (qe != cudaSuccess || n < 1) { (void)cudaGetLastError(); n = yv_num_sms() / 4; }
-        max_cl[dev] = n;
-        if (getenv("YV_GEMM_VERBOSE")) fprintf(stderr, "[yv8vit] clusters of 4 co-resident on device %d: %d (%d SMs), query rc %d\n", dev, n, 4 * n, (int)qe);
+        cudaError_t qe = cs == 6 ? cudaOccupancyMaxActiveClusters(&n, gemm_bf16_kernel<false, T_BF16, 0, 16, EPI_TMA, 6>, &cfg)
+                                 : cudaOccupancyMaxActiveClusters(&n, gemm_bf16_kernel<false, T_BF16, 0, 16, EPI_TMA, 4>, &cfg);
+        if (qe != cudaSuccess || n < 1) { (void)cudaGetLastError(); n = yv_num_sms() / cs; }
+        max_cl[dev][slot] = n;
+        if (getenv("YV_GEMM_VERBOSE")) fprintf(stderr, "[yv8vit] clusters of %d co-resident on device %d: %d (%d SMs), query rc %d\n", cs, dev, n, cs * n, (int)qe);
       }
     }
-    const int ncl = units < max_cl[dev] ? units : max_cl[dev];
-    const int grid4 = 4 * ncl;
-#define YV_GO4(G, O, X, W, D) gemm_bf16_kernel<G, O, X, W, D, 4><<<grid4, gemm_threads(W), smem_bytes(W, D), s>>>(tmA, tmB, tmD, tmR, ep, M, N, K)
-    if (lnfold) { if (ep.gelu) YV_GO4(true, T_BF16, 0, 16, EPI_TMA_LN); else YV_GO4(false, T_BF16, 0, 16, EPI_TMA_LN); }
-    else if (tma_res) YV_GO4(false, T_F16, 0, 16, EPI_TMA_RES);
-    else { if (ep.gelu) YV_GO4(true, T_BF16, 0, 16, EPI_TMA); else YV_GO4(false, T_BF16, 0, 16, EPI_TMA); }
-#undef YV_GO4
+    const int ncl = units < max_cl[dev][slot] ? units : max_cl[dev][slot];
+    const int gridc = cs * ncl;
+#define YV_GOC(G, O, X, W, D)                                                                                                        \
+    do { if (cs == 6) gemm_bf16_kernel<G, O, X, W, D, 6><<<gridc, gemm_threads(W), smem_bytes(W, D), s>>>(tmA, tmB, tmD, tmR, ep, M, N, K); \
+         else gemm_bf16_kernel<G, O, X, W, D, 4><<<gridc, gemm_threads(W), smem_bytes(W, D), s>>>(tmA, tmB, tmD, tmR, ep, M, N, K); } while (0)
+    if (lnfold) { if (ep.gelu) YV_GOC(true, T_BF16, 0, 16, EPI_TMA_LN); else YV_GOC(false, T_BF16, 0, 16, EPI_TMA_LN); }
+    else if (tma_res) YV_GOC(false, T_F16, 0, 16, EPI_TMA_RES);
+    else { if (ep.gelu) YV_GOC(true, T_BF16, 0, 16, EPI_TMA); else YV_GOC(false, T_BF16, 0, 16, EPI_TMA); }
+#undef YV_GOC
   } else
   if (lnfold) {
     if (ep.gelu) YV_GO(true, T_BF16, 0, 16, EPI_TMA_LN); else YV_GO(false, T_BF16, 0, 16, EPI_TMA_LN);
