@@ -104,13 +104,6 @@ __device__ __forceinline__ uint32_t fa_pack_bf16x2(float lo, float hi) {
   __nv_bfloat162 h = __floats2bfloat162_rn(lo, hi);
   return *reinterpret_cast<uint32_t *>(&h);
 }
-__device__ __forceinline__ void fa_tmem_ld_32x8(uint32_t taddr, uint32_t (&r)[8]) {
-  asm volatile("tcgen05.ld.sync.aligned.32x32b.x8.b32 {%0, %1, %2, %3, %4, %5, %6, %7}, [%8];"
-               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7])
-               : "r"(taddr)
-               : "memory");
-}
-
 // mbar_wait with a name: a protocol bug prints which wait of which warp starved before the launch is failed
 // (bounded spin, like sm100::mbar_wait -- a hang would cost a GPU box)
 __device__ int fa_timeout_reports = 0;

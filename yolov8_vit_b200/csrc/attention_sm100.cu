@@ -94,15 +94,6 @@ __device__ __forceinline__ int ap_cstart(int c, int nch) {
   const int base = nch >> 2, rem = nch & 3;
   return c * base + (c < rem ? c : rem);
 }
-// TMEM column (inside a score buffer) of P chunk k: quarter c keeps its packed P at the head of its S part
-__device__ __forceinline__ int ap_pcol(int k, int nch) {
-  int c = 3;
-#pragma unroll
-  for (int i = 3; i >= 1; --i)
-    if (k < ap_cstart(i, nch)) c = i - 1;
-  const int s0 = ap_cstart(c, nch);
-  return 16 * s0 + 8 * (k - s0);
-}
 
 __global__ void __launch_bounds__(AP_THREADS, 1)
 attention_pipe_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,

@@ -125,7 +125,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int m_tiles = (M + PM - 1) / PM, n_tiles = (N + BN - 1) / BN;
-  const int num_tiles = m_tiles * n_tiles, kblocks = K / BK;
+  const int kblocks = K / BK;
   const uint32_t crank = cluster_ctarank();           // rank in the cluster
   const uint32_t rank = crank & 1u;                   // 0 = leader of the CTA pair (issues the MMAs)
   const uint32_t lead = crank & ~1u;                  // cluster rank of this pair's leader
