@@ -283,6 +283,12 @@ size_t yv_residual_linear_f16_ws_bytes(int M, int N);
 int yv_residual_linear_f16(const void *A, const void *W, const float *bias,
                            void *x, int M, int N, int K, float eps, float *stats,
                            void *ws, size_t ws_bytes, yv_stream_t stream);
+/* Scheduling knob: the number of SMs a GEMM launch / a ViT-B/16 attention launch
+ * may occupy (persistent grids; 0 = all SMs, the default).  With budgets that add
+ * up to the SM count a GEMM and an attention launch issued on two streams run side
+ * by side on disjoint SMs.  Process-wide, not thread-safe against running
+ * launches: set it between forwards.  GEMM budget must be even (CTA pairs).     */
+int yv_tune_sm_budget(int gemm_sms, int attention_sms);
 /* softmax(Q K^T / sqrt(dh)) V for qkv [n, T, 3, heads, dh] bf16 -> out
  * [n, T, heads*dh] bf16 (timm's qkv packing).                               */
 int yv_attention_bf16(const void *qkv, void *out, int n, int T, int heads,

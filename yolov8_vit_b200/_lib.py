@@ -23,7 +23,7 @@ SYMBOLS = [
     "yv_dilate_boxes", "yv_build_crops", "yv_crop_resize",
     "yv_vit_create", "yv_vit_destroy", "yv_vit_set_param", "yv_vit_missing_params",
     "yv_vit_workspace_bytes", "yv_vit_forward",
-    "yv_gemm_bf16", "yv_linear_ln_f16_ws_bytes", "yv_linear_ln_f16", "yv_residual_linear_f16_ws_bytes", "yv_residual_linear_f16", "yv_layernorm_bf16", "yv_attention_bf16", "yv_pack_results",
+    "yv_tune_sm_budget", "yv_gemm_bf16", "yv_linear_ln_f16_ws_bytes", "yv_linear_ln_f16", "yv_residual_linear_f16_ws_bytes", "yv_residual_linear_f16", "yv_layernorm_bf16", "yv_attention_bf16", "yv_pack_results",
     "yv_prof_enable", "yv_prof_kinds", "yv_prof_kind_name", "yv_prof_read", "yv_debug_attn_trace",
 ]
 
@@ -90,6 +90,7 @@ def load() -> ctypes.CDLL:
     lib.yv_linear_ln_f16_ws_bytes.restype = ctypes.c_size_t
     lib.yv_linear_ln_f16.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int,
                                      c_float, c_int, c_void_p, ctypes.c_size_t, c_void_p]
+    lib.yv_tune_sm_budget.argtypes = [c_int, c_int]
     lib.yv_residual_linear_f16_ws_bytes.argtypes = [c_int, c_int]
     lib.yv_residual_linear_f16_ws_bytes.restype = c_size_t
     lib.yv_residual_linear_f16.argtypes = [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_float,

@@ -142,3 +142,14 @@ YV_EXPORT int yv_prof_read(double *ms, long long *launches, double *work) {
   }
   return YV_OK;
 }
+
+// ---- SM budgets (measurement / scheduling knob) ----------------------------------------------------------------
+namespace { int g_gemm_sms = 0, g_attn_sms = 0; }
+int yv_gemm_sm_budget() { const int n = yv_num_sms(); return g_gemm_sms > 0 && g_gemm_sms < n ? g_gemm_sms : n; }
+int yv_attention_sm_budget() { const int n = yv_num_sms(); return g_attn_sms > 0 && g_attn_sms < n ? g_attn_sms : n; }
+YV_EXPORT int yv_tune_sm_budget(int gemm_sms, int attention_sms) {
+  YV_REQUIRE(gemm_sms >= 0 && attention_sms >= 0 && gemm_sms % 2 == 0, "yv_tune_sm_budget: bad budget %d / %d (GEMM SMs must be even)", gemm_sms, attention_sms);
+  g_gemm_sms = gemm_sms;
+  g_attn_sms = attention_sms;
+  return YV_OK;
+}

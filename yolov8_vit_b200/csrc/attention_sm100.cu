@@ -409,7 +409,7 @@ int yv_attention_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, int
   if (rc) return rc;
   YvProf prof(YV_K_ATTN, s, 4.0 * n * heads * (double)T * T * dh);
   const int units = n * heads;
-  const int grid = units < yv_num_sms() ? units : yv_num_sms();
+  const int grid = units < yv_attention_sm_budget() ? units : yv_attention_sm_budget();
   attention_pipe_kernel<<<grid, AP_THREADS, AP_SMEM, s>>>(tmQ, tmKV, out, units, T, heads, scale_log2e, g_trace);
   YV_LAUNCH_CHECK();
   return YV_OK;

@@ -38,6 +38,10 @@ int yv_cuda_fail(cudaError_t e, const char *what, const char *file, int line);
 
 static inline size_t yv_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 int yv_num_sms();                                  // of the CURRENT device (cached per device)
+// SMs a GEMM / an attention launch may occupy (yv_tune_sm_budget; 0 = all): lets the two run side by side on
+// disjoint SMs from two streams
+int yv_gemm_sm_budget();
+int yv_attention_sm_budget();
 // one-time setup per (slot, current device), thread-safe: cudaFuncSetAttribute and friends (api.cu)
 enum YvInitSlot { YV_INIT_GEMM = 0, YV_INIT_ATTN, YV_INIT_ATTN_FA, YV_INIT_COUNT };
 int yv_device_once(int slot, int (*fn)());

@@ -582,7 +582,7 @@ int yv_gemm_launch(const void *A, const void *W, int M, int N, int K, const Gemm
   rc = make_tmap(&tmB, W, (uint64_t)N, (uint64_t)K, BNH);
   if (rc) return rc;
   const int tiles = ((M + PM - 1) / PM) * ((N + BN - 1) / BN);
-  const int pairs = yv_num_sms() / 2;
+  const int pairs = yv_gemm_sm_budget() / 2;
   const int grid = 2 * (tiles < pairs ? tiles : pairs);
   YvProf prof(YV_K_GEMM, s, 2.0 * M * (double)N * K);
   static const int dbg = []() { const char *e = getenv("YV_GEMM_DBG"); return e ? atoi(e) : 0; }();
