@@ -65,7 +65,8 @@ __device__ __forceinline__ void tmem_st8(uint32_t taddr, uint32_t v) {
   asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1,%1,%1,%1,%1,%1,%1,%1};" ::"r"(taddr), "r"(v) : "memory");
 }
 
-// mode 0: ld x8, 1: ld x16, 2: ld x32, 3: two x16 in flight, 4: st x8, 5: ex2, 6: ffma2, 7: fmax3, 8: fmax (2-input)
+// mode 0: ld x8, 1: ld x16, 2: ld x32, 3: two x16 in flight, 4: st x8, 5: ex2, 6: ffma2, 7: fmax3, 8: fmax (2-input),
+// 9: cvt.rn.bf16x2.f32 (F2FP, 32 per iteration), 10: 32 ex2 + 16 cvt.rn.bf16x2.f32 interleaved (do they share a pipe?)
 template <int MODE>
 __global__ void __launch_bounds__(1024, 1) bench(long long *cycles, uint32_t *sink, int iters) {
   __shared__ uint32_t slot;
@@ -113,6 +114,26 @@ __global__ void __launch_bounds__(1024, 1) bench(long long *cycles, uint32_t *si
       for (int k = 0; k < 16; ++k) {
         asm volatile("max.f32 %0, %0, %1, %2;" : "+f"(f0) : "f"(f1), "f"(f2));
         asm volatile("max.f32 %0, %0, %1, %2;" : "+f"(f3) : "f"(f1), "f"(f2));
+      }
+    }
+    if (MODE == 9) {
+#pragma unroll
+      for (int k = 0; k < 16; ++k) {
+        uint32_t w0, w1;
+        asm volatile("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(w0) : "f"(f0), "f"(f1));
+        asm volatile("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(w1) : "f"(f2), "f"(f3));
+        acc ^= w0 ^ w1;
+      }
+    }
+    if (MODE == 10) {
+#pragma unroll
+      for (int k = 0; k < 8; ++k) {
+        uint32_t w0, w1;
+        asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(f0)); asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(f1));
+        asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(f2)); asm volatile("ex2.approx.ftz.f32 %0, %0;" : "+f"(f3));
+        asm volatile("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(w0) : "f"(f0), "f"(f1));
+        asm volatile("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(w1) : "f"(f2), "f"(f3));
+        acc ^= w0 ^ w1;
       }
     }
     if (MODE == 8) {
@@ -163,6 +184,8 @@ int main() {
     c = run<6>(warps, iters, d_cyc, d_sink); printf("\"ffma2_w%d_lanes_per_clk\": %.2f, ", warps, (double)warps * 32 * 32 * 2 * iters / c);
     c = run<7>(warps, iters, d_cyc, d_sink); printf("\"fmax3_w%d_per_clk\": %.2f, ", warps, (double)warps * 32 * 32 * iters / c);
     c = run<8>(warps, iters, d_cyc, d_sink); printf("\"fmax2_w%d_per_clk\": %.2f, ", warps, (double)warps * 32 * 32 * iters / c);
+    c = run<9>(warps, iters, d_cyc, d_sink); printf("\"cvt_bf16x2_w%d_per_clk\": %.2f, ", warps, (double)warps * 32 * 32 * iters / c);
+    c = run<10>(warps, iters, d_cyc, d_sink); printf("\"ex2_32_plus_cvt_16_w%d_clk_per_iter_per_smsp_warpgroup\": %.1f, ", warps, c / iters);
   }
   printf("\"iters\": %d}\n", iters);
   return 0;

@@ -76,7 +76,6 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float lo, float hi) {
 // instructions at 8 cycles (1664 cycles) plus the bf16 packs and ~1000 issue slots in a dependent chain
 // (max -> smem exchange -> exp -> pack -> tcgen05.st).  The simpler two-pass kernel is kept.
 constexpr int AP_THREADS = 24 * 32;              // TMA, MMA, alloc, spare, 16 softmax, 4 output
-constexpr int AP_THREADS_STRIP = 16 * 32;        // ... 8 softmax (strip form), 4 output: 128 registers per thread
 constexpr int AP_Q_BYTES = 256 * AT_DH * 2;         // 32 KB: both query tiles of a unit
 constexpr int AP_STAGE = AP_Q_BYTES + 2 * AT_KV_BYTES;   // 96 KB
 constexpr int AP_STAGES = 2;
@@ -90,9 +89,9 @@ struct ApBars {
 };
 constexpr int AP_SMEM = AP_STAGES * AP_STAGE + (int)sizeof(ApBars) + 1024;
 
-// first 16-key chunk of column quarter c when nch chunks are split as evenly as possible
-__device__ __forceinline__ int ap_cstart(int c, int nch) {
-  const int base = nch >> 2, rem = nch & 3;
+// first 16-key chunk of column part c when nch chunks are split over `parts` parts as evenly as possible
+__device__ __forceinline__ int ap_cstart(int c, int nch, int parts) {
+  const int base = nch / parts, rem = nch - base * parts;
   return c * base + (c < rem ? c : rem);
 }
 
@@ -102,11 +101,16 @@ __device__ __forceinline__ int ap_cstart(int c, int nch) {
 // STRIP = true: 8 softmax warps, each owns a whole 32-row x NK-column strip of a tile -- no exchange, no barrier -- and
 // the two warps of a sub-partition work on DIFFERENT tiles (even / odd, both score buffers are in flight anyway), so one
 // warp's max pass runs under the other's exp pass.
-template <bool STRIP, bool P2X2 = false>
-__global__ void __launch_bounds__(STRIP ? AP_THREADS_STRIP : AP_THREADS, 1)
+// General form: SLOTS tiles in flight (1 or 2) x PARTS column parts per strip: <1, 4> is the first form, <2, 1> the strip
+// form, <2, 2> splits each strip between two warps that exchange the row maximum (a 64-thread barrier).
+template <int SLOTS, int PARTS>
+__global__ void __launch_bounds__((8 + 4 * SLOTS * PARTS) * 32, 1)
 attention_pipe_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmKV,
                       __nv_bfloat16 *__restrict__ out, int n_units, int T, int heads, float scale_log2e,
                       unsigned long long *__restrict__ trace) {
+  constexpr bool STRIP = PARTS == 1;                // a strip per warp: no exchange
+  constexpr int NSW = 4 * SLOTS * PARTS;            // softmax warps
+  constexpr int OUTW = 4 + NSW;                     // first output warp
   // trace (debug, normally null): CTA 0 stamps clock64() per tile and role, 8 slots per tile
 #define AP_STAMP(t, e) do { if (trace && blockIdx.x == 0 && (t) < 64) trace[(t) * 8 + (e)] = clock64(); } while (0)
   extern __shared__ __align__(1024) uint8_t ap_raw[];
@@ -138,7 +142,7 @@ attention_pipe_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&bar->s_full[i], 1);
-      mbar_init(&bar->p_full[i], STRIP ? 4 : 16);   // the softmax warps of a tile
+      mbar_init(&bar->p_full[i], 4 * PARTS);        // the softmax warps of a tile
     }
     mbar_init(&bar->o_full, 1);
     mbar_init(&bar->o_free, 4);                     // the 4 output warps
@@ -211,21 +215,13 @@ attention_pipe_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
           uint64_t dv = umma_desc_mn_sw128(aV);     // +16 keys = +2048 B = +128 in the (addr >> 4) field
           uint32_t acc = 0;
 #pragma unroll
-          if (STRIP) {                              // P chunk k sits at column 8 k of the score buffer
-            uint32_t pc = pbase;
-            for (int k = 0; k < NCH; ++k, pc += 8, dv += 128) {
+#pragma unroll
+          for (int c = 0; c < PARTS; ++c) {         // part c keeps its packed P at the head of its own score columns
+            const int s0 = ap_cstart(c, NCH, PARTS), s1 = ap_cstart(c + 1, NCH, PARTS);
+            uint32_t pc = pbase + 16u * (uint32_t)s0;
+            for (int k = s0; k < s1; ++k, pc += 8, dv += 128) {
               umma_bf16_ts(tmem_base + o_col, pc, dv, idesc_o, acc);
               acc = 1;
-            }
-          } else {
-#pragma unroll
-            for (int c = 0; c < 4; ++c) {
-              const int s0 = ap_cstart(c, NCH), s1 = ap_cstart(c + 1, NCH);
-              uint32_t pc = pbase + 16u * (uint32_t)s0;
-              for (int k = s0; k < s1; ++k, pc += 8, dv += 128) {
-                umma_bf16_ts(tmem_base + o_col, pc, dv, idesc_o, acc);
-                acc = 1;
-              }
             }
           }
         }
@@ -236,17 +232,17 @@ attention_pipe_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
     }
   }
 
-  else if (warp >= 4 && warp < (STRIP ? 12 : 20)) {
+  else if (warp >= 4 && warp < OUTW) {
     // ===================== softmax: 4 lane quarters x (4 column quarters | 2 tile parities) =====================
-    const int q = warp & 3, cq = STRIP ? 0 : (warp - 4) >> 2;
-    const int slot = (warp - 4) >> 2;               // STRIP: this warp takes the tiles of this parity
+    const int q = warp & 3, cq = ((warp - 4) >> 2) % PARTS;        // lane quarter, column part
+    const int slot = ((warp - 4) >> 2) / PARTS;     // SLOTS == 2: this warp takes the tiles of this parity
     const int trow = q * 32 + lane;
     const uint32_t lane_addr = tmem_base + ((uint32_t)(q * 32) << 16);
-    const int k_lo = STRIP ? 0 : ap_cstart(cq, NCH), k_hi = STRIP ? NCH : ap_cstart(cq + 1, NCH);
+    const int k_lo = ap_cstart(cq, NCH, PARTS), k_hi = ap_cstart(cq + 1, NCH, PARTS);
     const uint64_t sc2 = pk2(scale_log2e, scale_log2e);
     float *xsum = &bar->xsum[0][cq][trow];
     int np = 0;                                     // tiles this warp has processed (not skipped)
-    for (int t = STRIP ? slot : 0; t < NT; t += STRIP ? 2 : 1) {
+    for (int t = slot; t < NT; t += SLOTS) {
       const int g = t & (NG - 1);
       const int b = t & 1;
       const uint32_t sbuf = lane_addr + (uint32_t)b * (uint32_t)NK;
@@ -318,66 +314,20 @@ attention_pipe_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
           }
         }
       }
-      if (!STRIP) {                                 // row maximum over the four column quarters
-        xm[cq * 128] = mx;
-        asm volatile("bar.sync %0, 128;" ::"r"(1 + q) : "memory");
-        mx = fmaxf(fmaxf(xm[0], xm[128]), fmaxf(xm[256], xm[384]));
+      if (PARTS > 1) {                              // row maximum over the column parts of this strip
+        float *xp = xm + slot * PARTS * 128;
+        xp[cq * 128] = mx;
+        asm volatile("bar.sync %0, %1;" ::"r"(1 + slot * 4 + q), "n"(32 * PARTS) : "memory");
+        mx = xp[0];
+#pragma unroll
+        for (int i = 1; i < PARTS; ++i) mx = fmaxf(mx, xp[i * 128]);
       }
       const float mneg = -mx * scale_log2e;
       const uint64_t mn2 = pk2(mneg, mneg);
       // pass 2: p = exp2(s * scale - max * scale); partial row sum; P -> TMEM as packed bf16 pairs behind
       // this thread's own read pointer
       uint64_t sum2 = pk2(0.f, 0.f);
-      if (STRIP && P2X2) {
-        // two chunks (32 keys) per trip: a lone warp per strip needs the instruction-level parallelism -- 32 independent
-        // exponentials in flight, the next pair of score chunks already requested
-        uint64_t sum2b = pk2(0.f, 0.f);
-        uint32_t ra[16], rb[16];
-        tmem_ld_32x16(sbuf, ra);
-        if (1 < k_hi) tmem_ld_32x16(sbuf + 16, rb);
-        for (int k = 0; k < k_hi; k += 2) {
-          const bool two = k + 1 < k_hi;            // warp-uniform
-          tmem_ld_wait();
-          float pa[16], pb[16];
-#pragma unroll
-          for (int j = 0; j < 16; j += 2) {
-            float x0, x1, y0, y1;
-            unpk2(fma2(pk2(__uint_as_float(ra[j]), __uint_as_float(ra[j + 1])), sc2, mn2), x0, x1);
-            unpk2(fma2(pk2(__uint_as_float(rb[j]), __uint_as_float(rb[j + 1])), sc2, mn2), y0, y1);
-            pa[j] = x0; pa[j + 1] = x1;
-            pb[j] = y0; pb[j + 1] = y1;
-          }
-          if (k + 2 < k_hi) tmem_ld_32x16(sbuf + 16 * (k + 2), ra);
-          if (k + 3 < k_hi) tmem_ld_32x16(sbuf + 16 * (k + 3), rb);
-#pragma unroll
-          for (int j = 0; j < 16; ++j) {
-            pa[j] = ex2_approx(pa[j]);
-            pb[j] = ex2_approx(pb[j]);
-          }
-          if (16 * k + 32 > T) {                    // the tail: keys >= T contribute nothing
-#pragma unroll
-            for (int j = 0; j < 16; ++j) {
-              if (16 * k + j >= T) pa[j] = 0.f;
-              if (!two || 16 * k + 16 + j >= T) pb[j] = 0.f;
-            }
-          }
-#pragma unroll
-          for (int j = 0; j < 16; j += 4) {
-            sum2 = add2(sum2, add2(pk2(pa[j], pa[j + 1]), pk2(pa[j + 2], pa[j + 3])));
-            sum2b = add2(sum2b, add2(pk2(pb[j], pb[j + 1]), pk2(pb[j + 2], pb[j + 3])));
-          }
-          uint32_t w[8];
-#pragma unroll
-          for (int j = 0; j < 8; ++j) w[j] = pack_bf16x2(pa[2 * j], pa[2 * j + 1]);
-          tmem_st_32x8(sbuf + 8 * k, w);
-          if (two) {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) w[j] = pack_bf16x2(pb[2 * j], pb[2 * j + 1]);
-            tmem_st_32x8(sbuf + 8 * k + 8, w);
-          }
-        }
-        sum2 = add2(sum2, sum2b);
-      } else {
+      {
       uint32_t r[16];
       if (k_lo < k_hi) tmem_ld_32x16(sbuf + 16 * k_lo, r);
       for (int k = k_lo; k < k_hi; ++k) {
@@ -413,7 +363,7 @@ attention_pipe_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
       if (lane == 0) mbar_arrive(&bar->p_full[b]);
       if (warp == 4 && lane == 0) AP_STAMP(t, 5);
     }
-  } else if (warp >= (STRIP ? 12 : 20)) {
+  } else if (warp >= OUTW) {
     // ===================== output: drain O, normalise, store =====================
     const int q = warp & 3;
     const int trow = q * 32 + lane;
@@ -425,12 +375,15 @@ attention_pipe_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
       const int tok = g * 128 + trow;
       mbar_wait_sleep(&bar->o_full, (uint32_t)t & 1u);
       tc_fence_after();
-      if (warp == (STRIP ? 12 : 20) && lane == 0) AP_STAMP(t, 6);
+      if (warp == OUTW && lane == 0) AP_STAMP(t, 6);
       const bool live = g * 128 + q * 32 < T;       // warp-uniform
       float inv = 0.f;
       if (live) {
         const float *xs = &bar->xsum[t & 3][0][trow];
-        inv = STRIP ? 1.0f / xs[0] : 1.0f / ((xs[0] + xs[128]) + (xs[256] + xs[384]));
+        float tot = xs[0];
+#pragma unroll
+        for (int i = 1; i < PARTS; ++i) tot += xs[i * 128];
+        inv = 1.0f / tot;
       }
       auto pack8 = [&](const uint32_t *v) {
         uint4 w;
@@ -455,7 +408,7 @@ attention_pipe_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_cons
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(&bar->o_free);     // the accumulator may be overwritten by P V(t+1)
-      if (warp == (STRIP ? 12 : 20) && lane == 0) AP_STAMP(t, 7);
+      if (warp == OUTW && lane == 0) AP_STAMP(t, 7);
       if (live && tok < T) {
         uint4 *dst = reinterpret_cast<uint4 *>(out + ((size_t)crop * T + tok) * D + (size_t)head * AT_DH);
 #pragma unroll
@@ -510,19 +463,21 @@ int yv_attention_launch(const __nv_bfloat16 *qkv, __nv_bfloat16 *out, int n, int
   rc = yv_tmap_bf16_2d(&tmKV, qkv, (uint64_t)n * T, (uint64_t)3 * D, (uint32_t)NK);
   if (rc) return rc;
   rc = yv_device_once(YV_INIT_ATTN, []() -> int {
-    YV_CUDA(cudaFuncSetAttribute(attention_pipe_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AP_SMEM));
-    YV_CUDA(cudaFuncSetAttribute(attention_pipe_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AP_SMEM));
-    YV_CUDA((cudaFuncSetAttribute(attention_pipe_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AP_SMEM)));
+    YV_CUDA((cudaFuncSetAttribute(attention_pipe_kernel<1, 4>, cudaFuncAttributeMaxDynamicSharedMemorySize, AP_SMEM)));
+    YV_CUDA((cudaFuncSetAttribute(attention_pipe_kernel<2, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, AP_SMEM)));
+    YV_CUDA((cudaFuncSetAttribute(attention_pipe_kernel<2, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, AP_SMEM)));
     return YV_OK;
   });
   if (rc) return rc;
   YvProf prof(YV_K_ATTN, s, 4.0 * n * heads * (double)T * T * dh);
   const int units = n * heads;
   const int grid = units < yv_attention_sm_budget() ? units : yv_attention_sm_budget();
-  static const int strip = []() { const char *e = getenv("YV_ATTN_B16"); return e && e[0] == 's' ? (e[5] == '2' ? 2 : 1) : 0; }();      // A/B: strip / strip2
-  if (strip == 2) attention_pipe_kernel<true, true><<<grid, AP_THREADS_STRIP, AP_SMEM, s>>>(tmQ, tmKV, out, units, T, heads, scale_log2e, g_trace);
-  else if (strip) attention_pipe_kernel<true><<<grid, AP_THREADS_STRIP, AP_SMEM, s>>>(tmQ, tmKV, out, units, T, heads, scale_log2e, g_trace);
-  else attention_pipe_kernel<false><<<grid, AP_THREADS, AP_SMEM, s>>>(tmQ, tmKV, out, units, T, heads, scale_log2e, g_trace);
+  // softmax form: strip (default; measured 0.324 ms per 1072 crops against 0.383 for quarters and 0.343 for split);
+  // YV_ATTN_B16=quarters | split | strip selects one for A/B
+  static const int form = []() { const char *e = getenv("YV_ATTN_B16"); return !e ? 1 : e[0] == 'q' ? 0 : (e[0] == 's' && e[1] == 'p') ? 2 : 1; }();
+  if (form == 1) attention_pipe_kernel<2, 1><<<grid, (8 + 8) * 32, AP_SMEM, s>>>(tmQ, tmKV, out, units, T, heads, scale_log2e, g_trace);
+  else if (form == 2) attention_pipe_kernel<2, 2><<<grid, (8 + 16) * 32, AP_SMEM, s>>>(tmQ, tmKV, out, units, T, heads, scale_log2e, g_trace);
+  else attention_pipe_kernel<1, 4><<<grid, (8 + 16) * 32, AP_SMEM, s>>>(tmQ, tmKV, out, units, T, heads, scale_log2e, g_trace);
   YV_LAUNCH_CHECK();
   return YV_OK;
 }
