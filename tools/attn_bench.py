@@ -12,6 +12,7 @@ NCU = bool(os.environ.get("NCU"))
 flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)
 out = {"b16_kernel": "attention_fa (WIDE)" if os.environ.get("YV_ATTN_B16", "")[:1] == "f" else "attention_pipe", "b8_kernel": "attention_fa"}
 shapes = [("b16", int(os.environ.get("N16", "1072")), 197), ("b8", int(os.environ.get("N8", "256")), 785)]
+shapes = [s for s in shapes if s[1] > 0]            # N8=0 skips the ViT-B/8 shape
 for name, n, T in shapes:
     heads, dh = 12, 64
     qkv = (torch.randn(n, T, 3 * heads * dh, device=dev) * 0.7).to(torch.bfloat16)
