@@ -253,13 +253,16 @@ constexpr int CR_T = 256;
 constexpr int CR_PX = 8;     // output pixels per thread (one 16-byte bf16 store per channel)
 
 // One thread = 8 consecutive output x pixels of one output row, all 3 channels.
-// Thread order inside a crop is (patch, row-in-patch, 8-px segment) so that the 16-byte stores
-// of a warp are contiguous in the patch-major output (512 B per channel for patch 16).
+// Thread order inside a crop is (output row, 8-px segment): a warp's 256 pixels lie in one or two output rows, so every
+// load instruction of the warp touches two to four source rows.  (Round 1 ordered the threads (patch, row-in-patch,
+// segment) so that a warp's 16-byte stores were contiguous in the patch-major output -- 512 B per channel -- but then
+// each load instruction touched the 16 source rows of a patch and the kernel was bound by L1 wavefronts: 0.72 ms per
+// 1072 crops against 0.47 ms in row order, where a warp's stores are 32-byte pieces 1536 B apart.)
 template <int INTERP, int LAYOUT, bool WORDS>
 __global__ void __launch_bounds__(CR_T)
 crop_resize_kernel(const uint8_t *__restrict__ images, int H, int W, const int4 *__restrict__ crop_box,
                    const int32_t *__restrict__ crop_img, int n, const int32_t *__restrict__ n_dev,
-                   int out, int patch, size_t total, void *__restrict__ dst) {
+                   int out, int patch, size_t total, void *__restrict__ dst, int rowmap) {
   const int crop = blockIdx.y;
   if (crop >= n || (n_dev && crop >= *n_dev)) return;
   const int segs_per_patch = patch * patch / CR_PX;
@@ -267,10 +270,22 @@ crop_resize_kernel(const uint8_t *__restrict__ images, int H, int W, const int4 
   const int work = gp * gp * segs_per_patch;
   const int t = blockIdx.x * CR_T + threadIdx.x;
   if (t >= work) return;
-  const int p = t / segs_per_patch, sp = t % segs_per_patch;
-  const int segs_per_row = patch / CR_PX;
-  const int iy = sp / segs_per_row, ix0 = (sp % segs_per_row) * CR_PX;
-  const int oy = (p / gp) * patch + iy, ox0 = (p % gp) * patch + ix0;
+  int p, iy, ix0, oy, ox0;
+  if (rowmap) {
+    // row order: a warp covers 256 consecutive pixels of one or two OUTPUT rows, so its taps fall into two to four
+    // source rows (a handful of cache lines per load instruction) instead of the 16 rows of a patch
+    const int segs_per_orow = out / CR_PX;
+    oy = t / segs_per_orow;
+    ox0 = (t - oy * segs_per_orow) * CR_PX;
+    p = (oy / patch) * gp + ox0 / patch;
+    iy = oy % patch;
+    ix0 = ox0 % patch;
+  } else {
+    p = t / segs_per_patch;
+    const int sp = t % segs_per_patch, segs_per_row = patch / CR_PX;
+    iy = sp / segs_per_row, ix0 = (sp % segs_per_row) * CR_PX;
+    oy = (p / gp) * patch + iy, ox0 = (p % gp) * patch + ix0;
+  }
 
   const int4 bx = crop_box[crop];
   const int cw = bx.z - bx.x, ch = bx.w - bx.y;
@@ -432,10 +447,12 @@ YV_EXPORT int yv_crop_resize(const uint8_t *images, int B, int H, int W, const i
   // aligned word loads need a 4-byte-aligned image base (any CUDA allocation); otherwise byte loads
   const size_t total = (size_t)B * H * W * 3;
   const bool words = ((uintptr_t)images % 4) == 0;
+  // thread order inside a crop: output rows (default; measured 0.47 against 0.72 ms per 1072 crops) or YV_CROP_MAP=patch
+  static const int rowmap = []() { const char *e = getenv("YV_CROP_MAP"); return e ? (e[0] != 'p') : 1; }();
 #define YV_CR(I, L)                                                                                              \
   do {                                                                                                           \
-    if (words) crop_resize_kernel<I, L, true><<<grid, CR_T, 0, s>>>(images, H, W, cb, crop_img, n, n_dev, out_size, patch, total, out); \
-    else crop_resize_kernel<I, L, false><<<grid, CR_T, 0, s>>>(images, H, W, cb, crop_img, n, n_dev, out_size, patch, total, out);      \
+    if (words) crop_resize_kernel<I, L, true><<<grid, CR_T, 0, s>>>(images, H, W, cb, crop_img, n, n_dev, out_size, patch, total, out, rowmap); \
+    else crop_resize_kernel<I, L, false><<<grid, CR_T, 0, s>>>(images, H, W, cb, crop_img, n, n_dev, out_size, patch, total, out, rowmap); \
   } while (0)
   if (interp == YV_INTERP_NEAREST) {
     if (layout == YV_LAYOUT_PATCH_BF16) YV_CR(YV_INTERP_NEAREST, YV_LAYOUT_PATCH_BF16);
