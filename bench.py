@@ -355,6 +355,26 @@ def run_extras(dev, model, hbm):
     return out
 
 
+def run_cls_tail(hp, model, head_d, imgs_d):
+    """The north-star step with the last ViT block's proj / norm2 / MLP on the class-token rows only
+    (ViTModel.last_block_cls_rows): NOT the headline -- the timed forward computes every row of every block -- but the
+    same records bit for bit, timed back to back with the full step on the same box."""
+    import torch
+    B = head_d.shape[0]
+    r_full = hp(head_d, imgs_d)
+    ms_full = event_timed(lambda: hp(head_d, imgs_d), 5)
+    try:
+        model.last_block_cls_rows(True)
+        r_cls = hp(head_d, imgs_d)
+        ms = event_timed(lambda: hp(head_d, imgs_d), 5)
+    finally:
+        model.last_block_cls_rows(False)
+    return {"images_per_s": B / ms * 1e3, "ms_per_step": ms, "full_ms_per_step_back_to_back": ms_full,
+            "records_equal_full": bool(torch.equal(r_full.records, r_cls.records)),
+            "flop_per_crop_executed": FLOP_PER_CROP - 196 * 2.0 * (768 * 768 + 2 * 768 * 3072),
+            "note": "opt-in; bit-identical logits (tests/test_gpu_vit.py); not used by value / e2e"}
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -524,6 +544,7 @@ def run_ours(args):
             out["cfg4_strong"] = cfg4
         if not args.no_extras and args.workload == "north_star":
             out["extras"] = run_extras(dev, model, hbm)
+            out["extras"]["last_block_cls_rows"] = run_cls_tail(hp, model, head_d, imgs_d)
         if not args.no_cpu_baseline and world == 1:
             out["cpu_baseline"], oracle_res = cpu_baseline(sd, head_h, imgs_h)
             v = verify(oracle_res, hp(head_d, imgs_d, keep_intermediates=True))

@@ -231,6 +231,14 @@ int yv_vit_set_param(yv_vit_t *m, const char *name, const float *data,
                      size_t numel, yv_stream_t stream);
 /* number of parameters still unset (0 = ready) */
 int yv_vit_missing_params(const yv_vit_t *m);
+/* Classification only reads the class-token row of each crop (timm's token
+ * pooling, reached through utils/utils.py:71-72), and after the last attention
+ * no operation mixes rows: with enable != 0 the proj / residual / norm2 / MLP
+ * of the LAST block run on the class rows alone.  Logits and top-1 are
+ * bit-identical to the full computation (every GEMM row is independent);
+ * 2.1 of the 35.1 GFLOP per ViT-B/16 crop are not executed.  Off by default:
+ * the benchmarked forward computes every row of every block.                */
+int yv_vit_last_block_cls_rows(yv_vit_t *m, int enable);
 size_t yv_vit_workspace_bytes(const yv_vit_t *m, int max_crops);
 /* patches: layout-0 output of yv_crop_resize for n crops.
  * logits [n,num_classes] f32, top1 [n] i32 (first arg-max), hidden (optional,

@@ -128,6 +128,28 @@ def test_vit_b16_chunking_and_odd_counts(full_model):
     assert ta[sel].cpu().tolist() == ref.argmax(1).tolist()
 
 
+@pytest.mark.parametrize("n", [1, 37, 300])
+def test_last_block_on_class_rows_is_bit_identical(full_model, n):
+    """yv_vit_last_block_cls_rows: proj / norm2 / MLP of the last block on the class-token rows alone.  No operation
+    after the last attention mixes rows and every GEMM row is computed independently, so logits, backbone features
+    and top-1 equal the full computation BIT FOR BIT (1, 37 and 300 crops: partial row tiles of every size)."""
+    m, _ = full_model
+    imgs = synth.make_images(4, 640, 640, seed=5).to(DEV)
+    boxes = synth.make_boxes_int(n, seed=6).to(DEV)
+    dil, _ = ops.dilate_boxes(boxes, 640, 640)
+    idx = (torch.arange(n, device=DEV) % 4).to(torch.int32)
+    p = ops.crop_resize(imgs, dil, idx, n, "bilinear", 224, 16, "patch")
+    la, ta, ha = m.forward_patches(p, n, return_hidden=True)
+    try:
+        m.last_block_cls_rows(True)
+        lb, tb, hb = m.forward_patches(p, n, return_hidden=True)
+    finally:
+        m.last_block_cls_rows(False)
+    lc, tc = m.forward_patches(p, n)
+    assert torch.equal(la, lb) and torch.equal(ta, tb) and torch.equal(ha, hb)
+    assert torch.equal(la, lc) and torch.equal(ta, tc)          # and the switch goes back
+
+
 def test_pipeline_cfg1_golden(golden, full_model):
     g = golden("pipeline_cfg1")
     m, _ = full_model

@@ -21,7 +21,7 @@ SYMBOLS = [
     "yv_decode_filter_workspace_bytes", "yv_decode_filter", "yv_decode_filter_raw", "yv_letterbox_geometry", "yv_letterbox_blob",
     "yv_nms_workspace_bytes", "yv_nms_batched", "yv_nms_batched_rule", "yv_nms_batched_noalloc",
     "yv_dilate_boxes", "yv_build_crops", "yv_crop_resize",
-    "yv_vit_create", "yv_vit_destroy", "yv_vit_set_param", "yv_vit_missing_params",
+    "yv_vit_create", "yv_vit_destroy", "yv_vit_set_param", "yv_vit_missing_params", "yv_vit_last_block_cls_rows",
     "yv_vit_workspace_bytes", "yv_vit_forward",
     "yv_tune_sm_budget", "yv_gemm_bf16", "yv_linear_ln_f16_ws_bytes", "yv_linear_ln_f16", "yv_residual_linear_f16_ws_bytes", "yv_residual_linear_f16", "yv_layernorm_bf16", "yv_attention_bf16", "yv_pack_results",
     "yv_prof_enable", "yv_prof_kinds", "yv_prof_kind_name", "yv_prof_read", "yv_debug_attn_trace",
@@ -80,6 +80,7 @@ def load() -> ctypes.CDLL:
     lib.yv_vit_destroy.restype = None
     lib.yv_vit_set_param.argtypes = [c_void_p, c_char_p, c_void_p, c_size_t, c_void_p]
     lib.yv_vit_missing_params.argtypes = [c_void_p]
+    lib.yv_vit_last_block_cls_rows.argtypes = [c_void_p, c_int]
     lib.yv_vit_workspace_bytes.restype = c_size_t
     lib.yv_vit_workspace_bytes.argtypes = [c_void_p, c_int]
     lib.yv_vit_forward.argtypes = [c_void_p, c_void_p, c_int, c_void_p, c_void_p, c_void_p, c_void_p, c_size_t,

@@ -71,6 +71,7 @@ struct yv_vit {
   size_t nb = 0, nf = 0;
   size_t pos_table_off = 0;      // f32 arena: [T, dim]
   bool finalized = false;
+  bool last_block_cls = false;   // yv_vit_last_block_cls_rows: proj / MLP of the last block on the class-token rows only
 
   const __nv_bfloat16 *B(const std::string &k) const { return wb + params.at(k).off; }
   const float *F(const std::string &k) const { return wf + params.at(k).off; }
@@ -272,6 +273,12 @@ YV_EXPORT int yv_vit_set_param(yv_vit_t *m, const char *name, const float *data,
   return YV_OK;
 }
 
+YV_EXPORT int yv_vit_last_block_cls_rows(yv_vit_t *m, int enable) {
+  YV_REQUIRE(m, "yv_vit_last_block_cls_rows: null model");
+  m->last_block_cls = enable != 0;
+  return YV_OK;
+}
+
 YV_EXPORT int yv_vit_missing_params(const yv_vit_t *m) {
   if (!m) return -1;
   int miss = 0;
@@ -324,6 +331,7 @@ YV_EXPORT int yv_vit_forward(yv_vit_t *m, const void *patches_bf16, int n, float
       // stream once (2 B per element, no write).  YV_VIT_LNFOLD=0: LayerNorm kernels (2 B in + 2 B out) into w.y.
       const bool fold = vit_lnfold();
       const bool fused = fold && vit_stats_fused();          // statistics out of the proj / fc2 epilogues
+      const bool cls_tail = m->last_block_cls && fused && c.depth >= 1;
       const __nv_bfloat16 *x16 = (const __nv_bfloat16 *)w.x;      // 16-bit rows; the instruction descriptor says f16
       for (int i = 0; i < c.depth; ++i) {
         const std::string p = "model.blocks." + std::to_string(i) + ".";
@@ -338,6 +346,28 @@ YV_EXPORT int yv_vit_forward(yv_vit_t *m, const void *patches_bf16, int n, float
           if ((rc = yv_gemm_launch(w.y, m->B(p + "attn.qkv.weight"), M, 3 * D, D, ep, s))) return rc;
         }
         if ((rc = yv_attention_launch(w.qkv, w.y, cc, T, c.heads, D / c.heads, s))) return rc;
+        if (cls_tail && i + 1 == c.depth) {
+          // Only the class-token row of a crop reaches the final norm and the heads, and after the last attention no
+          // operation mixes rows any more: proj, the residual adds, norm2 and the MLP of the LAST block run on the cc class
+          // rows alone (gathered into the dead qkv buffer).  Every row of a GEMM is computed independently of the others
+          // (same K order, same epilogue), so the logits are bit-identical to the full computation (tested).
+          char *tb = (char *)w.qkv;
+          void *x_cls = tb;                                  tb += yv_align_up((size_t)cc * D * 2, 1024);
+          __nv_bfloat16 *y_cls = (__nv_bfloat16 *)tb;        tb += yv_align_up((size_t)cc * D * 2, 1024);
+          __nv_bfloat16 *h_cls = (__nv_bfloat16 *)tb;
+          YV_CUDA(cudaMemcpy2DAsync(x_cls, (size_t)D * 2, w.x, (size_t)T * D * 2, (size_t)D * 2, cc, cudaMemcpyDeviceToDevice, s));
+          YV_CUDA(cudaMemcpy2DAsync(y_cls, (size_t)D * 2, w.y, (size_t)T * D * 2, (size_t)D * 2, cc, cudaMemcpyDeviceToDevice, s));
+          ep = GemmEpilogue{x_cls, m->F(p + "attn.proj.bias"), x_cls, nullptr, 0, false, 2, 2};
+          ep.stats_part = w.part;
+          if ((rc = yv_gemm_launch(y_cls, m->B(p + "attn.proj.weight"), cc, D, D, ep, s))) return rc;
+          if ((rc = yv_stats_finalize_launch(w.part, cc, D, c.eps, w.stats, s))) return rc;
+          ep = GemmEpilogue{h_cls, m->F(p + "norm2.fold.c"), nullptr, nullptr, 0, true, 0, 0, w.stats, m->F(p + "norm2.fold.s")};
+          if ((rc = yv_gemm_launch((const __nv_bfloat16 *)x_cls, m->B(p + "norm2.fold.w"), cc, c.mlp, D, ep, s))) return rc;
+          ep = GemmEpilogue{x_cls, m->F(p + "mlp.fc2.bias"), x_cls, nullptr, 0, false, 2, 2};
+          if ((rc = yv_gemm_launch(h_cls, m->B(p + "mlp.fc2.weight"), cc, D, c.mlp, ep, s))) return rc;
+          if ((rc = yv_ln_launch(x_cls, XT, (size_t)D, nullptr, 0, false, m->F("model.norm.weight"), m->F("model.norm.bias"), w.cls_ln, cc, D, c.eps, s))) return rc;
+          break;
+        }
         ep = GemmEpilogue{w.x, m->F(p + "attn.proj.bias"), w.x, nullptr, 0, false, 2, 2};
         if (fused) ep.stats_part = w.part;
         if ((rc = yv_gemm_launch(w.y, m->B(p + "attn.proj.weight"), M, D, D, ep, s))) return rc;
@@ -358,7 +388,7 @@ YV_EXPORT int yv_vit_forward(yv_vit_t *m, const void *patches_bf16, int n, float
         if (next && (rc = yv_stats_finalize_launch(w.part, M, D, c.eps, w.stats, s))) return rc;
       }
       // final norm on the class-token rows only, then the heads
-      if ((rc = yv_ln_launch(w.x, XT, (size_t)T * D, nullptr, 0, false, m->F("model.norm.weight"), m->F("model.norm.bias"), w.cls_ln, cc, D, c.eps, s))) return rc;
+      if (!cls_tail && (rc = yv_ln_launch(w.x, XT, (size_t)T * D, nullptr, 0, false, m->F("model.norm.weight"), m->F("model.norm.bias"), w.cls_ln, cc, D, c.eps, s))) return rc;
     } else {
       // fp32 residual stream (round-1 layout): the residual adds are fused into the LayerNorms, so proj / fc2 store
       // plain bf16 deltas.  The fp32 stream is rewritten ONCE per block: norm2 normalises x32 + d_attn on the fly
