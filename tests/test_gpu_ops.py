@@ -141,6 +141,34 @@ def test_crop_cfg3_random_boxes_bit_exact():
             assert np.array_equal(got[i].numpy(), ref), (interp, i)
 
 
+def test_crop_patch_order_mode_is_bit_identical():
+    """YV_CROP_MAP=patch keeps the round-1 thread order of the crop kernel (by patch instead of by output row) for A/B
+    timing; only the order of the work changes, so both layouts and both interpolations must equal the oracle there too.
+    Child process: the switch is read once."""
+    import os, subprocess, sys
+    code = r"""
+import sys, numpy as np, torch
+sys.path.insert(0, %r)
+from oracle import hotpath as O
+from yolov8_vit_b200 import ops, synth
+imgs = synth.make_images(4, 640, 640, seed=synth.SEED0 + 3)
+boxes = synth.make_boxes_int(24, seed=synth.SEED0 + 7)
+dil, _ = ops.dilate_boxes(boxes.cuda(), 640, 640)
+idx = (torch.arange(24) %% 4).to(torch.int32)
+for interp in ("bilinear", "nearest"):
+    chw = ops.crop_resize(imgs.cuda(), dil, idx.cuda(), 24, interp, 224, 16, "chw").cpu()
+    pm = ops.crop_resize(imgs.cuda(), dil, idx.cuda(), 24, interp, 224, 16, "patch").cpu()
+    for i in range(24):
+        ref = O.crop_resize_norm(imgs[idx[i]].numpy(), dil[i].cpu().numpy(), 224, interp)
+        assert np.array_equal(chw[i].numpy(), ref), (interp, i)
+        assert torch.equal(pm[i * 196:(i + 1) * 196], O.patchify(torch.from_numpy(ref)[None], 16).to(torch.bfloat16)), (interp, i)
+print('patch order ok')
+""" % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", code], env=dict(os.environ, YV_CROP_MAP="patch"), capture_output=True,
+                       text=True, timeout=280)
+    assert r.returncode == 0 and "patch order ok" in r.stdout, r.stdout + r.stderr
+
+
 def test_crop_image_reference_surface():
     img = synth.make_images(1, 200, 300, seed=5)[0].numpy()
     t = U.crop_image(img, 50, 40, 150, 120)
