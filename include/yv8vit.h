@@ -237,7 +237,10 @@ int yv_vit_missing_params(const yv_vit_t *m);
  * of the LAST block run on the class rows alone.  Logits and top-1 are
  * bit-identical to the full computation (every GEMM row is independent);
  * 2.1 of the 35.1 GFLOP per ViT-B/16 crop are not executed.  Off by default:
- * the benchmarked forward computes every row of every block.                */
+ * the benchmarked forward computes every row of every block.  A per-model
+ * flag read at the start of yv_vit_forward: set it before forwards are issued,
+ * not concurrently with one (default stream / LayerNorm modes only; the fp32-
+ * stream and LayerNorm-kernel A/B modes ignore it and compute every row).    */
 int yv_vit_last_block_cls_rows(yv_vit_t *m, int enable);
 size_t yv_vit_workspace_bytes(const yv_vit_t *m, int max_crops);
 /* patches: layout-0 output of yv_crop_resize for n crops.

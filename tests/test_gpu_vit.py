@@ -230,6 +230,11 @@ def test_vit_b8_reference_literal_model(depth):
     got = m(x.to(DEV)).cpu()
     assert rel_err(got, ref) <= REL_TOL
     assert got.argmax(1).tolist() == ref.argmax(1).tolist()
+    try:                                            # the class-rows-only last block at 785 tokens: bit-identical
+        got2 = m.last_block_cls_rows(True)(x.to(DEV)).cpu()
+    finally:
+        m.last_block_cls_rows(False)
+    assert torch.equal(got, got2)
 
 
 def test_fp32_residual_stream_mode_parity():
